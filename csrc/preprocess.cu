@@ -1,0 +1,287 @@
+// Input pipeline on the device (SURVEY W11 + W12): uint8 32x32x3 -> normalised bf16 NHWC 224x224.
+//
+// Reference behaviour replaced (cifar10_mpi_mobilenet_224.py:72-89, :174): seven PIL transforms per
+// image in DataLoader worker processes, then a blocking 77 MB fp32 H2D copy per step.  Here 393 KB
+// of raw bytes cross PCIe and one kernel composes, per output pixel:
+//   Resize(224) bilinear -> RandomResizedCrop box + bilinear resize -> HFlip -> ColorJitter (4 ops in
+//   the sample's own order) -> Rotation (nearest, zero fill) -> ToTensor -> Normalize(ImageNet).
+// The random draws arrive as one 12-float row per sample (data/transforms.py), so the CPU
+// implementation (apply_pipeline_torch) and this kernel consume identical parameters.
+//
+// Augmenting kernel: one CTA per image.  Phase 0 builds the 224x224x3 resized image in shared
+// memory (147 KB of the 227 KB), phase 1 reduces the grey mean the contrast op needs, phase 2
+// writes the output.  Plain (test-time) kernel: a flat grid, 4-tap bilinear straight from a
+// shared-memory copy of the 3 KB source image.
+#include "common.cuh"
+
+namespace b200dp {
+namespace {
+
+constexpr int SRC = 32;
+constexpr int NP = B200DP_AUG_NPARAM;
+__constant__ float c_mean[3] = {0.485f * 255.f, 0.456f * 255.f, 0.406f * 255.f};
+__constant__ float c_istd[3] = {1.f / (0.229f * 255.f), 1.f / (0.224f * 255.f), 1.f / (0.225f * 255.f)};
+// lexicographic permutations of (brightness, contrast, saturation, hue) -- same table as transforms._PERMS
+__constant__ unsigned char c_perm[24][4] = {
+    {0, 1, 2, 3}, {0, 1, 3, 2}, {0, 2, 1, 3}, {0, 2, 3, 1}, {0, 3, 1, 2}, {0, 3, 2, 1},
+    {1, 0, 2, 3}, {1, 0, 3, 2}, {1, 2, 0, 3}, {1, 2, 3, 0}, {1, 3, 0, 2}, {1, 3, 2, 0},
+    {2, 0, 1, 3}, {2, 0, 3, 1}, {2, 1, 0, 3}, {2, 1, 3, 0}, {2, 3, 0, 1}, {2, 3, 1, 0},
+    {3, 0, 1, 2}, {3, 0, 2, 1}, {3, 1, 0, 2}, {3, 1, 2, 0}, {3, 2, 0, 1}, {3, 2, 1, 0}};
+
+__device__ __forceinline__ float round_u8(float v) { return fminf(fmaxf(floorf(v + 0.5f), 0.f), 255.f); }
+
+// torch/PIL bilinear upsampling with half-pixel centres, source clamped to [0, 31]
+__device__ __forceinline__ void src_tap(int d, float scale, int& i0, int& i1, float& f) {
+  float s = fmaxf(((float)d + 0.5f) * scale - 0.5f, 0.f);
+  i0 = (int)s;
+  if (i0 > SRC - 1) i0 = SRC - 1;
+  i1 = min(i0 + 1, SRC - 1);
+  f = s - (float)i0;
+}
+
+__device__ __forceinline__ float3 resized_px(const unsigned char* s_src, int y, int x, float scale) {
+  int y0, y1, x0, x1;
+  float fy, fx;
+  src_tap(y, scale, y0, y1, fy);
+  src_tap(x, scale, x0, x1, fx);
+  const unsigned char* p00 = s_src + (y0 * SRC + x0) * 3;
+  const unsigned char* p01 = s_src + (y0 * SRC + x1) * 3;
+  const unsigned char* p10 = s_src + (y1 * SRC + x0) * 3;
+  const unsigned char* p11 = s_src + (y1 * SRC + x1) * 3;
+  float r[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    // same association as ATen's upsample_bilinear2d: rows blended first, then columns
+    const float top = (float)p00[c] * (1.f - fx) + (float)p01[c] * fx;
+    const float bot = (float)p10[c] * (1.f - fx) + (float)p11[c] * fx;
+    r[c] = round_u8(top * (1.f - fy) + bot * fy);
+  }
+  return make_float3(r[0], r[1], r[2]);
+}
+
+template <int OC>
+__device__ __forceinline__ void store_px(__nv_bfloat16* out, size_t pix, float3 v) {
+  const float a = (v.x - c_mean[0]) * c_istd[0];
+  const float b = (v.y - c_mean[1]) * c_istd[1];
+  const float c = (v.z - c_mean[2]) * c_istd[2];
+  if constexpr (OC == 4) {
+    *reinterpret_cast<uint2*>(out + pix * 4) = make_uint2(pack_bf16x2(a, b), pack_bf16x2(c, 0.f));
+  } else {
+    __nv_bfloat16* o = out + pix * 3;
+    o[0] = __float2bfloat16(a);
+    o[1] = __float2bfloat16(b);
+    o[2] = __float2bfloat16(c);
+  }
+}
+
+template <int OC>
+__global__ void __launch_bounds__(256)
+preprocess_plain_kernel(const uint8_t* __restrict__ images, __nv_bfloat16* __restrict__ out, int size,
+                        int rows_per_cta) {
+  __shared__ unsigned char s_src[SRC * SRC * 3];
+  const int img = blockIdx.y;
+  const uint32_t* g = reinterpret_cast<const uint32_t*>(images + (size_t)img * SRC * SRC * 3);
+  for (int i = threadIdx.x; i < SRC * SRC * 3 / 4; i += blockDim.x)
+    reinterpret_cast<uint32_t*>(s_src)[i] = g[i];
+  __syncthreads();
+  const float scale = (float)SRC / (float)size;
+  const int y_lo = blockIdx.x * rows_per_cta;
+  const int y_hi = min(y_lo + rows_per_cta, size);
+  for (int p = y_lo * size + threadIdx.x; p < y_hi * size; p += blockDim.x) {
+    const int y = p / size, x = p - y * size;
+    store_px<OC>(out, (size_t)img * size * size + p, resized_px(s_src, y, x, scale));
+  }
+}
+
+// ---- colour ops on 0..255 floats (match data/transforms.py) -------------------------------------
+__device__ __forceinline__ float gray_of(float3 v) { return 0.299f * v.x + 0.587f * v.y + 0.114f * v.z; }
+__device__ __forceinline__ float clamp255(float v) { return fminf(fmaxf(v, 0.f), 255.f); }
+__device__ __forceinline__ float3 blend(float3 a, float3 b, float f) {
+  return make_float3(clamp255(a.x + f * (b.x - a.x)), clamp255(a.y + f * (b.y - a.y)),
+                     clamp255(a.z + f * (b.z - a.z)));
+}
+
+__device__ __forceinline__ float3 hue_shift(float3 v, float dh) {
+  const float r = v.x, g = v.y, b = v.z;
+  const float mx = fmaxf(fmaxf(r, g), b), mn = fminf(fminf(r, g), b);
+  const float d = mx - mn;
+  const float s = mx > 0.f ? d / fmaxf(mx, 1e-12f) : 0.f;
+  const float dz = fmaxf(d, 1e-12f);
+  float h;
+  if (mx == r) {
+    h = (g - b) / dz;
+    h = h - 6.f * floorf(h / 6.f);
+  } else if (mx == g) {
+    h = (b - r) / dz + 2.f;
+  } else {
+    h = (r - g) / dz + 4.f;
+  }
+  h = d > 0.f ? h / 6.f : 0.f;
+  h += dh;
+  h = h - floorf(h);
+  const float h6 = h * 6.f;
+  const float fi = floorf(h6);
+  const float f = h6 - fi;
+  const float p = mx * (1.f - s), q = mx * (1.f - s * f), t = mx * (1.f - s * (1.f - f));
+  int i = ((int)fi) % 6;
+  switch (i) {
+    case 0: return make_float3(mx, t, p);
+    case 1: return make_float3(q, mx, p);
+    case 2: return make_float3(p, mx, t);
+    case 3: return make_float3(p, q, mx);
+    case 4: return make_float3(t, p, mx);
+    default: return make_float3(mx, p, q);
+  }
+}
+
+struct AugP {
+  float top, left, h, w, flip, fb, fc, fs, fh, angle;
+  int order;
+};
+
+// crop-resize sample of the resized image held in shared memory
+__device__ __forceinline__ float3 crop_px(const unsigned char* s_res, int S, const AugP& a, int v, int u) {
+  if (a.flip > 0.f) u = S - 1 - u;
+  float py = a.top + ((float)v + 0.5f) * (a.h / (float)S) - 0.5f;
+  float px = a.left + ((float)u + 0.5f) * (a.w / (float)S) - 0.5f;
+  const float ylo = a.top, yhi = a.top + a.h - 1.f, xlo = a.left, xhi = a.left + a.w - 1.f;
+  py = fminf(fmaxf(py, ylo), yhi);
+  px = fminf(fmaxf(px, xlo), xhi);
+  const float y0f = floorf(py), x0f = floorf(px);
+  const float fy = py - y0f, fx = px - x0f;
+  const int y0 = (int)y0f, x0 = (int)x0f;
+  const int y1 = (int)fminf(y0f + 1.f, yhi), x1 = (int)fminf(x0f + 1.f, xhi);
+  const unsigned char* p00 = s_res + (y0 * S + x0) * 3;
+  const unsigned char* p01 = s_res + (y0 * S + x1) * 3;
+  const unsigned char* p10 = s_res + (y1 * S + x0) * 3;
+  const unsigned char* p11 = s_res + (y1 * S + x1) * 3;
+  float r[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const float top = (float)p00[c] * (1.f - fx) + (float)p01[c] * fx;
+    const float bot = (float)p10[c] * (1.f - fx) + (float)p11[c] * fx;
+    r[c] = round_u8(top * (1.f - fy) + bot * fy);
+  }
+  return make_float3(r[0], r[1], r[2]);
+}
+
+// run the colour chain; `upto` = number of leading ops to apply (4 = all).  `mean` is the grey mean
+// used by the contrast op.
+__device__ __forceinline__ float3 color_chain(float3 v, const AugP& a, int upto, float mean) {
+  for (int pos = 0; pos < upto; ++pos) {
+    const int op = c_perm[a.order][pos];
+    if (op == 0) {
+      v = make_float3(clamp255(v.x * a.fb), clamp255(v.y * a.fb), clamp255(v.z * a.fb));
+    } else if (op == 1) {
+      v = blend(make_float3(mean, mean, mean), v, a.fc);
+    } else if (op == 2) {
+      const float g = gray_of(v);
+      v = blend(make_float3(g, g, g), v, a.fs);
+    } else {
+      v = hue_shift(v, a.fh);
+    }
+  }
+  return v;
+}
+
+template <int OC>
+__global__ void __launch_bounds__(1024)
+preprocess_aug_kernel(const uint8_t* __restrict__ images, const float* __restrict__ params,
+                      __nv_bfloat16* __restrict__ out, int S) {
+  extern __shared__ unsigned char smem[];
+  unsigned char* s_src = smem;                      // 3072 B
+  unsigned char* s_res = smem + SRC * SRC * 3;      // S*S*3 B
+  __shared__ float s_red[32];
+  __shared__ float s_mean;
+  const int img = blockIdx.x;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const uint32_t* g = reinterpret_cast<const uint32_t*>(images + (size_t)img * SRC * SRC * 3);
+  for (int i = tid; i < SRC * SRC * 3 / 4; i += nt) reinterpret_cast<uint32_t*>(s_src)[i] = g[i];
+  const float* pr = params + (size_t)img * NP;
+  AugP a;
+  a.top = pr[0]; a.left = pr[1]; a.h = pr[2]; a.w = pr[3]; a.flip = pr[4];
+  a.fb = pr[5]; a.fc = pr[6]; a.fs = pr[7]; a.fh = pr[8];
+  a.order = min(max((int)pr[9], 0), 23);
+  a.angle = pr[10];
+  const bool enabled = pr[11] > 0.f;
+  __syncthreads();
+  const float scale = (float)SRC / (float)S;
+  const int npx = S * S;
+  if (!enabled) {  // test-transform row inside an augmenting batch
+    for (int p = tid; p < npx; p += nt)
+      store_px<OC>(out, (size_t)img * npx + p, resized_px(s_src, p / S, p % S, scale));
+    return;
+  }
+  // phase 0: resized image -> shared memory
+  for (int p = tid; p < npx; p += nt) {
+    const float3 v = resized_px(s_src, p / S, p % S, scale);
+    s_res[p * 3 + 0] = (unsigned char)v.x;
+    s_res[p * 3 + 1] = (unsigned char)v.y;
+    s_res[p * 3 + 2] = (unsigned char)v.z;
+  }
+  __syncthreads();
+  // phase 1: grey mean of the image as it enters the contrast op
+  int cpos = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (c_perm[a.order][i] == 1) cpos = i;
+  float part = 0.f;
+  for (int p = tid; p < npx; p += nt)
+    part += gray_of(color_chain(crop_px(s_res, S, a, p / S, p % S), a, cpos, 0.f));
+  part = warp_sum(part);
+  if ((tid & 31) == 0) s_red[tid >> 5] = part;
+  __syncthreads();
+  if (tid < 32) {
+    float t = tid < (nt >> 5) ? s_red[tid] : 0.f;
+    t = warp_sum(t);
+    if (tid == 0) s_mean = floorf(t / (float)npx + 0.5f);
+  }
+  __syncthreads();
+  const float mean = s_mean;
+  // phase 2: rotate (inverse map, nearest, zero fill) -> crop/flip -> colour -> normalise
+  const float ang = -a.angle * 0.017453292519943295f;
+  const float ca = cosf(ang), sa = sinf(ang);
+  const float cx = (float)S * 0.5f;
+  const float ra = ca, rb = sa, rd = -sa, re = ca;
+  const float rc = cx - (ra * cx + rb * cx);
+  const float rf = cx - (rd * cx + re * cx);
+  for (int p = tid; p < npx; p += nt) {
+    const int y = p / S, x = p - y * S;
+    const float xin = ra * ((float)x + 0.5f) + rb * ((float)y + 0.5f) + rc;
+    const float yin = rd * ((float)x + 0.5f) + re * ((float)y + 0.5f) + rf;
+    const int u = (int)floorf(xin), v = (int)floorf(yin);
+    float3 val = make_float3(0.f, 0.f, 0.f);
+    if (u >= 0 && u < S && v >= 0 && v < S) val = color_chain(crop_px(s_res, S, a, v, u), a, 4, mean);
+    store_px<OC>(out, (size_t)img * npx + p, val);
+  }
+}
+
+}  // namespace
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_preprocess(const uint8_t* images, const float* params, void* out_bf16, int batch,
+                                 int size, int out_channels, void* stream) {
+  B200DP_REQUIRE(images && out_bf16 && batch > 0, "preprocess: bad arguments");
+  B200DP_REQUIRE(out_channels == 3 || out_channels == 4, "preprocess: out_channels must be 3 or 4");
+  B200DP_REQUIRE(size >= 32 && size <= 256, "preprocess: size %d unsupported", size);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  __nv_bfloat16* out = static_cast<__nv_bfloat16*>(out_bf16);
+  if (params == nullptr) {
+    const int rows = 16;
+    dim3 grid((size + rows - 1) / rows, batch);
+    if (out_channels == 4) preprocess_plain_kernel<4><<<grid, 256, 0, s>>>(images, out, size, rows);
+    else preprocess_plain_kernel<3><<<grid, 256, 0, s>>>(images, out, size, rows);
+    B200DP_CHECK_LAUNCH();
+    return B200DP_OK;
+  }
+  const size_t smem = SRC * SRC * 3 + (size_t)size * size * 3;
+  // per-device attribute; cheap enough to set on every call
+  B200DP_CUDA(cudaFuncSetAttribute(preprocess_aug_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  B200DP_CUDA(cudaFuncSetAttribute(preprocess_aug_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  if (out_channels == 4) preprocess_aug_kernel<4><<<batch, 1024, smem, s>>>(images, params, out, size);
+  else preprocess_aug_kernel<3><<<batch, 1024, smem, s>>>(images, params, out, size);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}

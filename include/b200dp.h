@@ -1,0 +1,135 @@
+/* b200dp native library -- C ABI.
+ *
+ * Everything the Python layer calls goes through these `extern "C"` entry points (ctypes;
+ * no torch headers, so the library builds in seconds with plain nvcc for sm_100a).  All
+ * pointers are device pointers unless said otherwise; `stream` is a `cudaStream_t` passed
+ * as `void*`.  Every function returns 0 on success or a negative B200DP_E* code and records a
+ * message retrievable with b200dp_last_error().  None of them synchronises the device unless
+ * documented.
+ *
+ * The reference project has no native code at all; each entry point cites the
+ * reference *behaviour* it implements (file:line in /root/reference).
+ */
+#ifndef B200DP_H_
+#define B200DP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200DP_OK 0
+#define B200DP_EINVAL (-1)
+#define B200DP_ECUDA (-2)
+#define B200DP_ENOMEM (-3)
+#define B200DP_ESTATE (-4)
+
+#define B200DP_MAX_WORLD 16
+#define B200DP_COMM_MAX_BLOCKS 256
+#define B200DP_AUG_NPARAM 12
+
+const char* b200dp_last_error(void);
+int b200dp_version(void);
+/* Number of kernels this library has launched in this process (bench.py's "gpu_launches"). */
+unsigned long long b200dp_launch_count(void);
+void b200dp_reset_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Device memory arenas shared between ranks of one node.
+ * A rank allocates an arena, exports a 64-byte IPC handle, and opens its peers' handles; the
+ * kernels below then load/store peer memory directly over NVLink / NVSwitch.
+ * (Replaces the NCCL communicator DDP builds at cifar10_mpi_mobilenet_224.py:142-145.)
+ * ------------------------------------------------------------------------------------------- */
+int b200dp_arena_alloc(size_t bytes, void** out_ptr);           /* cudaMalloc + zero fill (synchronises) */
+int b200dp_arena_free(void* ptr);
+int b200dp_ipc_export(void* ptr, unsigned char handle_out[64]);
+int b200dp_ipc_open(const unsigned char handle[64], void** out_ptr);
+int b200dp_ipc_close(void* ptr);
+int b200dp_enable_peer_access(int peer_device);                 /* same-process multi-GPU (tests) */
+
+/* ---------------------------------------------------------------------------------------------
+ * Fused gradient all-reduce + 1/W average + Adam (K-C5 + K12 + K13).
+ *   reference: loss.backward() -> DDP bucketed ncclAllReduce, then optimizer.step(), then
+ *   optimizer.zero_grad()  (cifar10_mpi_mobilenet_224.py:176-180)
+ *
+ * One kernel per step.  Every rank's gradient vector lives in a peer-mapped arena; after a
+ * flag barrier each rank reads all W copies in rank order 0..W-1 (bit-identical sums on every
+ * rank), scales, runs Adam on its fp32 master weights / moments, optionally refreshes a bf16
+ * working copy, then (after a second flag barrier) zeroes its own gradient vector.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200dp_comm_adam {
+  int world;                                /* number of ranks (1..B200DP_MAX_WORLD) */
+  int rank;
+  long long numel;                          /* elements; must be a multiple of 4 */
+  int grad_dtype;                           /* 0 = fp32 gradients, 1 = bf16 gradients */
+  int algo;                                 /* 0 = one-shot (every rank reduces everything),
+                                               1 = two-shot (rank r reduces + updates slice r, then
+                                                   stores the new weights into every peer) */
+  const void* grads[B200DP_MAX_WORLD];      /* grads[r] = rank r's gradient vector as mapped HERE */
+  uint32_t* flags[B200DP_MAX_WORLD];        /* flags[r] = rank r's flag pad as mapped HERE
+                                               (B200DP_COMM_MAX_BLOCKS * B200DP_MAX_WORLD uint32) */
+  float* params[B200DP_MAX_WORLD];          /* two-shot only: every rank's master weights as mapped
+                                               HERE; one-shot uses params[rank] only */
+  void* work_bf16[B200DP_MAX_WORLD];        /* optional bf16 working copies (same indexing); NULL = none */
+  float* m;                                 /* Adam first moment  (local) */
+  float* v;                                 /* Adam second moment (local) */
+  const float* lr;                          /* device scalar: learning rate for this step */
+  int* step_state;                          /* device int[B200DP_COMM_MAX_BLOCKS]: completed Adam steps */
+  uint32_t* epoch_state;                    /* device uint32[B200DP_COMM_MAX_BLOCKS]: barrier epochs */
+  int* error_flag;                          /* device int: set non-zero if a barrier spin timed out */
+  float beta1, beta2, eps, weight_decay;
+  int zero_grads;                           /* zero this rank's gradient vector at the end */
+  int apply_adam;                           /* 0 = plain all-reduce: the averaged gradient is written
+                                               to out_avg instead (bus-bandwidth sweep, tests) */
+  float* out_avg;                           /* apply_adam == 0: fp32 output vector (local) */
+  unsigned long long spin_limit;            /* polls before a barrier gives up (0 = default) */
+  int max_blocks;                           /* 0 = default grid */
+} b200dp_comm_adam;
+
+/* Launch the fused step on `stream`.  All ranks must call it the same number of times with the
+ * same numel/algo.  With world == 1 no flags are touched. */
+int b200dp_comm_adam_step(const b200dp_comm_adam* args, void* stream);
+/* Grid the call above will use for these arguments (every rank must agree; exposed for tests). */
+int b200dp_comm_adam_grid(const b200dp_comm_adam* args);
+
+/* Device-side barrier across ranks with the same flag protocol. */
+int b200dp_comm_barrier(const b200dp_comm_adam* args, void* stream);
+
+/* Rank `root` stores `numel` fp32 values into every peer's `dst` (K-C3, K-C4:
+ * DDP's parameter broadcast at construction and buffer broadcast, ref :142, :177). */
+int b200dp_comm_broadcast(const b200dp_comm_adam* args, int root, float* const* dst_by_rank,
+                          const float* src, long long numel, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Input pipeline (P1-P7, K14).
+ *   reference: transforms.Compose([...]) on PIL images in DataLoader workers, then a 77 MB fp32
+ *   H2D copy per step (cifar10_mpi_mobilenet_224.py:72-89, :174)
+ * uint8 [B,32,32,3] -> normalised bf16 NHWC [B,size,size,out_channels] (out_channels 3 or 4; the
+ * 4th channel is zero).  params == NULL selects the test transform; otherwise one row of
+ * B200DP_AUG_NPARAM floats per sample (data/transforms.py documents the columns).
+ * ------------------------------------------------------------------------------------------- */
+int b200dp_preprocess(const uint8_t* images, const float* params, void* out_bf16, int batch,
+                      int size, int out_channels, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Classifier head (K7-K11, K15).
+ *   reference: adaptive_avg_pool2d -> Dropout(0.2) -> Linear(1280,10) -> CrossEntropyLoss ->
+ *   argmax / correct count / loss.item()  (torchvision mobilenetv2.py:166-171;
+ *   cifar10_mpi_mobilenet_224.py:178-184)
+ * ------------------------------------------------------------------------------------------- */
+/* logits fp32 [B,C], labels int64 [B] -> per-sample loss (optional), dlogits (optional, already
+ * divided by `mean_over`), and metrics[3] += {sum of losses, correct count, B} as doubles. */
+int b200dp_softmax_xent(const float* logits, const int64_t* labels, float* loss_out,
+                        float* dlogits_out, double* metrics, int batch, int classes,
+                        float mean_over, void* stream);
+/* probs = softmax(logits) and top-k (values, indices) per row -- predict_cifar10_image,
+ * cifar10_128batch.py:170-172. */
+int b200dp_softmax_topk(const float* logits, float* probs_out, float* topv_out, int32_t* topi_out,
+                        int batch, int classes, int k, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DP_H_ */

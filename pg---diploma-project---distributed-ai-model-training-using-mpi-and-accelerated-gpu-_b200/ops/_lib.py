@@ -1,0 +1,116 @@
+"""ctypes binding of ``lib/libb200dp.so`` (C ABI in ``include/b200dp.h``).
+
+The library is built in-tree by ``build_native.py`` and loaded from the package directory, never
+from site-packages.  On a machine with a GPU a missing library is an error (``require()``), not a
+silent fallback to ATen.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+MAX_WORLD = 16
+COMM_MAX_BLOCKS = 256
+AUG_NPARAM = 12
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG_DIR, "lib", "libb200dp.so")
+
+_lib: Optional[C.CDLL] = None
+_load_error: Optional[str] = None
+
+
+class CommAdamArgs(C.Structure):
+    _fields_ = [
+        ("world", C.c_int), ("rank", C.c_int), ("numel", C.c_longlong),
+        ("grad_dtype", C.c_int), ("algo", C.c_int),
+        ("grads", C.c_void_p * MAX_WORLD),
+        ("flags", C.c_void_p * MAX_WORLD),
+        ("params", C.c_void_p * MAX_WORLD),
+        ("work_bf16", C.c_void_p * MAX_WORLD),
+        ("m", C.c_void_p), ("v", C.c_void_p), ("lr", C.c_void_p),
+        ("step_state", C.c_void_p), ("epoch_state", C.c_void_p), ("error_flag", C.c_void_p),
+        ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("weight_decay", C.c_float),
+        ("zero_grads", C.c_int), ("apply_adam", C.c_int),
+        ("out_avg", C.c_void_p),
+        ("spin_limit", C.c_ulonglong),
+        ("max_blocks", C.c_int),
+    ]
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, i, ll, f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+    lib.b200dp_last_error.restype = C.c_char_p
+    lib.b200dp_version.restype = i
+    lib.b200dp_launch_count.restype = C.c_ulonglong
+    lib.b200dp_reset_launch_count.restype = None
+    sigs = {
+        "b200dp_arena_alloc": [C.c_size_t, C.POINTER(vp)],
+        "b200dp_arena_free": [vp],
+        "b200dp_ipc_export": [vp, C.c_char_p],
+        "b200dp_ipc_open": [C.c_char_p, C.POINTER(vp)],
+        "b200dp_ipc_close": [vp],
+        "b200dp_enable_peer_access": [i],
+        "b200dp_comm_adam_step": [C.POINTER(CommAdamArgs), vp],
+        "b200dp_comm_adam_grid": [C.POINTER(CommAdamArgs)],
+        "b200dp_comm_barrier": [C.POINTER(CommAdamArgs), vp],
+        "b200dp_comm_broadcast": [C.POINTER(CommAdamArgs), i, C.POINTER(vp), vp, ll, vp],
+        "b200dp_preprocess": [vp, vp, vp, i, i, i, vp],
+        "b200dp_softmax_xent": [vp, vp, vp, vp, vp, i, i, f, vp],
+        "b200dp_softmax_topk": [vp, vp, vp, vp, i, i, i, vp],
+    }
+    for name, args in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = i
+
+
+def load() -> Optional[C.CDLL]:
+    """Load the library once; returns None (and remembers why) if it is not built."""
+    global _lib, _load_error
+    if _lib is not None or _load_error is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        _load_error = f"{LIB_PATH} not found -- run `python build_native.py`"
+        return None
+    try:
+        lib = C.CDLL(LIB_PATH)
+        _declare(lib)
+        for extra in _EXTRA_DECLS:
+            extra(lib)
+        _lib = lib
+    except (OSError, AttributeError) as e:
+        _load_error = f"cannot load {LIB_PATH}: {e}"
+    return _lib
+
+
+_EXTRA_DECLS = []   # other binding modules register their own declarations here
+
+
+def load_error() -> Optional[str]:
+    return _load_error
+
+
+def require() -> C.CDLL:
+    lib = load()
+    if lib is None:
+        raise RuntimeError(f"b200dp native library unavailable: {_load_error}")
+    return lib
+
+
+def check(rc: int) -> int:
+    if rc < 0:
+        msg = require().b200dp_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"b200dp native call failed ({rc}): {msg}")
+    return rc
+
+
+def ptr(t) -> int:
+    """Device (or host) address of a torch tensor, 0 for None."""
+    return 0 if t is None else t.data_ptr()
+
+
+def current_stream() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
