@@ -1,0 +1,175 @@
+#!/usr/bin/env python
+"""Headline benchmark: MobileNetV2@224 training throughput (images/sec, max over ranks).
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+           --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the unmodified reference scripts (baseline/_ref)
+
+Config (BASELINE.json): MobileNetV2 with a 10-class head, 224x224 input upsampled on the device
+from synthetic CIFAR-10-shaped uint8 32x32x3 data, per-rank batch 128 (weak scaling), bf16 compute
+with fp32 master weights, Adam lr 1e-4, random-init weights, full train step = preprocess +
+forward + loss + backward + gradient all-reduce + Adam.
+
+Two numbers come out of one run:
+* ``value``  -- device-timed: inputs already resident, K steps bracketed by barrier +
+  synchronize and CUDA events, max over ranks;
+* ``e2e``    -- the same K steps through the public loader -> engine path: each step copies its
+  uint8 batch, labels and augmentation parameters from pinned host memory and reads the running
+  loss back to the host.
+Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BASELINE_IMAGES_PER_SEC = {1: 94.6, 2: 197.0}   # upper bound on the reference's logged train images/sec (V100)
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200dp", choices=["b200dp", "reference"])
+    ap.add_argument("--engine", default="auto", choices=["auto", "native", "torch"])
+    ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def run_b200dp(ns) -> dict:
+    import torch
+
+    from b200dp import ops
+    from b200dp.config import TrainConfig
+    from b200dp.data.datasets import SyntheticCIFAR10
+    from b200dp.data.loader import Batch, BatchLoader
+    from b200dp.parallel.bootstrap import RankInfo, barrier, cleanup, discover_rank_world, setup_distributed
+    from b200dp.parallel.sampler import PartitionSampler
+    from b200dp.trainer import make_engine
+    from b200dp.utils.clocks import ClockSampler
+    from b200dp.utils.timers import max_over_ranks
+
+    info = discover_rank_world()
+    if info.world_size != ns.gpus:
+        if info.world_size == 1 and ns.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+        ns.gpus = info.world_size
+    mode = "ddp" if info.world_size > 1 else "gpu"
+    cfg = TrainConfig(mode=mode, engine=ns.engine, comm=ns.comm, batch_size=ns.batch, dataset="synthetic")
+    ctx = setup_distributed(cfg.master_addr, cfg.master_port, "auto", info=info)
+    if ctx.device.type != "cuda":
+        raise SystemExit("bench.py needs a CUDA device")
+    W, K, B, N = ns.warmup, ns.steps, ns.batch, ctx.world_size
+    if W < 3:
+        W = 3
+    per_rank = (W + K) * B
+    ds = SyntheticCIFAR10(per_rank * N, train=True)
+    ds.pin()
+    engine = make_engine(cfg, ctx)
+    lr = cfg.lr
+
+    # ---------------- device-timed arm: inputs resident ------------------------------------
+    sampler = PartitionSampler(len(ds), N, ctx.rank, shuffle=True)
+    loader = BatchLoader(ds, sampler, B, ctx.device, train=True, augment=True, seed=cfg.seed)
+    resident = []
+    for b in loader:
+        b.wait()
+        resident.append(Batch(b.images.clone(), b.labels.clone(), b.params.clone(), b.n))
+    torch.cuda.synchronize()
+    for i in range(W):
+        engine.train_step(resident[i], lr)
+    torch.cuda.synchronize()
+    barrier(ctx)
+    torch.cuda.synchronize()
+    ops.reset_launch_count()
+    clocks = ClockSampler(ctx.device.index).start() if ctx.is_main else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        engine.train_step(resident[W + i], lr)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(ctx)
+    launches = ops.launch_count()
+    clock_summary = clocks.stop() if clocks is not None else {}
+    ms = max_over_ranks(e0.elapsed_time(e1), ctx.device)
+    value = N * K * B / (ms / 1e3)
+    loss_sum, correct, count = engine.read_metrics()
+
+    # ---------------- end-to-end arm: pinned host -> device every step, loss read back --------
+    e2e = None
+    if not ns.no_e2e:
+        loader2 = BatchLoader(ds, sampler, B, ctx.device, train=True, augment=True, seed=cfg.seed + 1)
+        sampler.set_epoch(1)
+        it = iter(loader2)
+        for _ in range(W):
+            engine.train_step(next(it), lr)
+            engine.read_metrics(reset=False)
+        torch.cuda.synchronize()
+        barrier(ctx)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            engine.train_step(next(it), lr)
+            engine.read_metrics(reset=False)          # device -> host read of the running loss, every step
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0, ctx.device)
+        for _ in it:
+            pass
+        e2e = {"value": N * K * B / dt, "unit": "images/sec",
+               "h2d_bytes_per_step": loader2.h2d_bytes_per_batch(B), "d2h_bytes_per_step": 3 * 8}
+    barrier(ctx)
+    act_bytes = 13.4e6 * B * 2           # bf16 conv outputs written once per step, a lower bound
+    out = {
+        "metric": "MobileNetV2@224 train images/sec (max over ranks)",
+        "value": value, "unit": "images/sec", "n_gpus": N, "steps": K, "warmup": W,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": (value / BASELINE_IMAGES_PER_SEC[N]) if N in BASELINE_IMAGES_PER_SEC else None,
+        "dtype": "bf16", "data": "synthetic CIFAR-10-shaped uint8 32x32x3, random-init weights",
+        "impl": "b200dp", "engine": engine.name, "comm": cfg.comm,
+        "config": {"model": "MobileNetV2 (10-class head) @224", "global_batch": B * N, "per_rank_batch": B,
+                   "seq_len": None, "image": "224x224x3", "parallelism": f"dp{N}",
+                   "optimizer": "Adam lr=1e-4, fp32 master weights",
+                   "l2_policy": f"working set per step ~{act_bytes / 1e9:.1f} GB of activations >> {L2_BYTES >> 20} MB L2; "
+                                "every step uses a different input batch"},
+        "clocks": {"sm_mhz": clock_summary.get("sm_mhz"), "sm_max_mhz": clock_summary.get("sm_max_mhz"),
+                   "reasons": clock_summary.get("reasons", []), "power_w_max": clock_summary.get("power_w_max")},
+        "e2e": e2e, "gpu_launches": int(launches),
+        "final_train_loss": loss_sum / max(count, 1),
+    }
+    engine.close()
+    cleanup(ctx)
+    return out if ctx.is_main else {}
+
+
+def run_reference(ns) -> dict:
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import run_reference
+    except Exception as e:  # harness missing
+        return {"impl": "reference", "unavailable": f"baseline harness not importable: {e}"}
+    return run_reference.main(ns)
+
+
+def main() -> int:
+    ns = parse_args()
+    out = run_reference(ns) if ns.impl == "reference" else run_b200dp(ns)
+    if out:
+        print(json.dumps(out), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -99,11 +99,11 @@ __device__ __forceinline__ void zero_grad(void* base, long long i4) {
   }
 }
 
-__device__ __forceinline__ void adam1(float g, float& p, float& m, float& v, float b1, float b2, float eps,
-                                      float wd, float step_size, float isb2) {
+__device__ __forceinline__ void adam1(float g, float& p, float& m, float& v, float b1, float b2, float ob1,
+                                      float ob2, float eps, float wd, float step_size, float isb2) {
   g = fmaf(wd, p, g);
-  m = fmaf(b1, m, (1.0f - b1) * g);
-  v = fmaf(b2, v, (1.0f - b2) * g * g);
+  m = fmaf(b1, m, ob1 * g);
+  v = fmaf(b2, v, ob2 * g * g);
   const float denom = fmaf(sqrtf(v), isb2, eps);
   p = p - step_size * __fdividef(m, denom);
 }
@@ -121,8 +121,8 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
 
   if (threadIdx.x == 0) {
     const double t = (double)(step + 1);
-    const double bc1 = 1.0 - pow((double)P.beta1, t);
-    const double bc2 = 1.0 - pow((double)P.beta2, t);
+    const double bc1 = 1.0 - pow(P.beta1, t);
+    const double bc2 = 1.0 - pow(P.beta2, t);
     s_scal[0] = (float)((double)(*P.lr) / bc1);
     s_scal[1] = (float)(1.0 / sqrt(bc2));
   }
@@ -132,7 +132,8 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
     __syncthreads();
   }
   const float step_size = s_scal[0], isb2 = s_scal[1];
-  const float b1 = P.beta1, b2 = P.beta2, eps = P.eps, wd = P.weight_decay;
+  const float b1 = (float)P.beta1, b2 = (float)P.beta2, eps = P.eps, wd = P.weight_decay;
+  const float ob1 = (float)(1.0 - P.beta1), ob2 = (float)(1.0 - P.beta2);
   const float scale = 1.0f / (float)W;
 
   const long long n4 = P.numel >> 2;
@@ -172,10 +173,10 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
     float4 p = *reinterpret_cast<const float4*>(myp + i * 4);
     float4 m = *reinterpret_cast<const float4*>(mm + i * 4);
     float4 v = *reinterpret_cast<const float4*>(vv + i * 4);
-    adam1(acc.x, p.x, m.x, v.x, b1, b2, eps, wd, step_size, isb2);
-    adam1(acc.y, p.y, m.y, v.y, b1, b2, eps, wd, step_size, isb2);
-    adam1(acc.z, p.z, m.z, v.z, b1, b2, eps, wd, step_size, isb2);
-    adam1(acc.w, p.w, m.w, v.w, b1, b2, eps, wd, step_size, isb2);
+    adam1(acc.x, p.x, m.x, v.x, b1, b2, ob1, ob2, eps, wd, step_size, isb2);
+    adam1(acc.y, p.y, m.y, v.y, b1, b2, ob1, ob2, eps, wd, step_size, isb2);
+    adam1(acc.z, p.z, m.z, v.z, b1, b2, ob1, ob2, eps, wd, step_size, isb2);
+    adam1(acc.w, p.w, m.w, v.w, b1, b2, ob1, ob2, eps, wd, step_size, isb2);
     *reinterpret_cast<float4*>(mm + i * 4) = m;
     *reinterpret_cast<float4*>(vv + i * 4) = v;
     const uint32_t w01 = pack_bf16x2(p.x, p.y), w23 = pack_bf16x2(p.z, p.w);

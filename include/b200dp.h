@@ -79,7 +79,8 @@ typedef struct b200dp_comm_adam {
   int* step_state;                          /* device int[B200DP_COMM_MAX_BLOCKS]: completed Adam steps */
   uint32_t* epoch_state;                    /* device uint32[B200DP_COMM_MAX_BLOCKS]: barrier epochs */
   int* error_flag;                          /* device int: set non-zero if a barrier spin timed out */
-  float beta1, beta2, eps, weight_decay;
+  double beta1, beta2;                      /* doubles: (1 - beta) and the bias corrections match torch.optim.Adam exactly */
+  float eps, weight_decay;
   int zero_grads;                           /* zero this rank's gradient vector at the end */
   int apply_adam;                           /* 0 = plain all-reduce: the averaged gradient is written
                                                to out_avg instead (bus-bandwidth sweep, tests) */

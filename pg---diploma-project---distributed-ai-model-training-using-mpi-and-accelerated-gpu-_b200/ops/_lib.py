@@ -31,7 +31,7 @@ class CommAdamArgs(C.Structure):
         ("work_bf16", C.c_void_p * MAX_WORLD),
         ("m", C.c_void_p), ("v", C.c_void_p), ("lr", C.c_void_p),
         ("step_state", C.c_void_p), ("epoch_state", C.c_void_p), ("error_flag", C.c_void_p),
-        ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("weight_decay", C.c_float),
+        ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_float), ("weight_decay", C.c_float),
         ("zero_grads", C.c_int), ("apply_adam", C.c_int),
         ("out_avg", C.c_void_p),
         ("spin_limit", C.c_ulonglong),

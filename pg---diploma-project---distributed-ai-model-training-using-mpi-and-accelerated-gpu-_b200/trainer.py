@@ -31,7 +31,10 @@ from .utils.watchdog import Watchdog
 def make_engine(cfg: TrainConfig, ctx: DistContext):
     engine = cfg.engine
     if engine == "auto":
-        engine = "native" if ctx.device.type == "cuda" else "torch"
+        engine = "torch"
+        if ctx.device.type == "cuda":
+            from . import engine_native
+            engine = "native" if engine_native.available() else "torch"
     if engine == "native":
         if ctx.device.type != "cuda":
             raise RuntimeError("engine=native needs a CUDA device (mode gpu or ddp)")
