@@ -1,0 +1,499 @@
+// Pointwise (1x1) convolution as a persistent, warp-specialised tcgen05 GEMM.
+//
+//   Out[M, N] (bf16) = Aeff[M, K] (bf16) * W[N, K]^T,  fp32 accumulation in TMEM.
+//
+// M = batch*H*W rows of an NHWC activation, K / N = input / output channels.  The same kernel
+// serves the forward convolutions and the data gradients (weights pre-transposed), selected by
+//   AMODE  how the A operand reaches shared memory
+//     A_TMA     TMA loads the bf16 tile as is                      (expand conv fwd, project dgrad)
+//     A_BNRELU  producer warps load the *raw* output of the previous conv, apply its BatchNorm
+//               scale/shift (+ReLU6) in registers, store the swizzled tile   (project conv fwd)
+//     A_BNGRAD  producer warps combine (dz, x) into the BatchNorm input gradient
+//               ca*dz + cb*x + cc in registers                                (expand conv dgrad)
+//   EMODE  what the epilogue does besides the bf16 store
+//     E_PLAIN      nothing
+//     E_STATS      per-channel sum and sum of squares (the training-mode BatchNorm statistics of THIS
+//                  conv's output -- no separate batch-norm pass ever reads the tensor)
+//     E_MASKSTATS  ReLU6 backward mask recomputed from the raw forward activation, plus the two
+//                  per-channel sums BatchNorm backward needs (sum dz, sum dz*x)
+//
+// Reference behaviour replaced: cuDNN 1x1 convolution + cuDNN batch-norm + ATen hardtanh kernels,
+// each a full read+write of the activation (torchvision mobilenetv2.py via
+// cifar10_mpi_mobilenet_224.py:177, :179).
+//
+// Roles (one CTA per SM, static round-robin over 128 x BLOCK_N tiles):
+//   warp 0      TMA producer: weight tile (and the A tile in A_TMA mode) per 64-wide K chunk
+//   warp 1      MMA issuer: one elected thread issues tcgen05.mma (M=128, N=BLOCK_N, K=16)
+//   warp 2      TMEM allocator (2 accumulator stages x 128 columns)
+//   warps 4-7   epilogue: tcgen05.ld -> bf16 -> swizzled smem -> coalesced pass (stats / mask) -> TMA store
+//   warps 8-15  A producers (only in A_BNRELU / A_BNGRAD)
+// Pipelines: smem full/empty mbarriers per stage, TMEM full/empty per accumulator stage.
+#include "common.cuh"
+#include "pw_gemm.h"
+#include "sm100.cuh"
+
+namespace b200dp {
+
+namespace {
+
+using namespace sm100;
+
+constexpr int BM = 128;
+constexpr int KCH = 64;
+constexpr int A_STAGE = BM * 128;       // bytes
+constexpr int OUT_CHUNK = BM * 128;     // one 64-column block of the output tile, bytes
+constexpr int ACC_COLS = 128;           // TMEM columns per accumulator stage
+constexpr int TMEM_COLS = 256;
+constexpr int EPI_THREADS = 128;
+constexpr int PROD_THREADS = 256;
+constexpr int MAX_STAGES = 8;
+
+struct Smem {
+  uint8_t* stage_a[MAX_STAGES];
+  uint8_t* stage_b[MAX_STAGES];
+};
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                    pack_bf16x2(f[6], f[7]));
+}
+__device__ __forceinline__ void sts16(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ uint4 lds16(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr)
+               : "memory");
+  return v;
+}
+
+template <int AMODE, int EMODE>
+__global__ void __launch_bounds__(AMODE == A_TMA ? 256 : 512, 1)
+pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ PwGemmParams P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // ---- carve shared memory (tile buffers 1024-byte aligned for the 128-byte swizzle) ------------
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stages = P.stages;
+  const int b_stage = P.block_n * 128;
+  const int nch = (P.block_n + 63) >> 6;
+  uint8_t* stage_a = base;
+  uint8_t* stage_b = stage_a + (size_t)stages * A_STAGE;
+  uint8_t* out_buf = stage_b + (size_t)stages * b_stage;          // 2 x nch x 16 KB
+  float* s_acoef = reinterpret_cast<float*>(out_buf + 2 * (size_t)nch * OUT_CHUNK);
+  const int n_acoef = (AMODE == A_BNRELU ? 2 : (AMODE == A_BNGRAD ? 3 : 0)) * P.K;
+  float* s_ecoef = s_acoef + n_acoef;
+  const int n_ecoef = (EMODE == E_MASKSTATS ? 2 : 0) * P.N;
+  float* s_stats = s_ecoef + n_ecoef;                              // [2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stats + 2 * 128);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + MAX_STAGES;
+  uint64_t* tmem_full = bars + 2 * MAX_STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = P.m_tiles * P.n_tiles;
+
+  // ---- one-time set-up ---------------------------------------------------------------------------
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmO);
+    if (AMODE == A_TMA) prefetch_tmap(&tmA);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full[s], AMODE == A_TMA ? 1 : 1 + PROD_THREADS);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], EPI_THREADS);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) s_acoef[i] = P.acoef[i];
+  for (int i = threadIdx.x; i < n_ecoef; i += blockDim.x) s_ecoef[i] = P.ecoef[i];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) s_stats[i] = 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    if (lane == 0) {
+      const uint32_t tx = (AMODE == A_TMA ? A_STAGE : 0) + b_stage;
+      int s = 0;
+      uint32_t ph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m0 = (t / P.n_tiles) * BM, n0 = (t % P.n_tiles) * P.block_n;
+        for (int kc = 0; kc < P.kc; ++kc) {
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_arrive_expect_tx(&full[s], tx);
+          if (AMODE == A_TMA) tma_load_2d(stage_a + (size_t)s * A_STAGE, &tmA, &full[s], kc * KCH, m0);
+          tma_load_2d(stage_b + (size_t)s * b_stage, &tmB, &full[s], kc * KCH, n0);
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(BM, P.block_n, 0, 0);
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        const int as = it & 1;
+        mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * ACC_COLS;
+        for (int kc = 0; kc < P.kc; ++kc) {
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint64_t da = umma_desc_kmajor_sw128(smem_u32(stage_a + (size_t)s * A_STAGE));
+          const uint64_t db = umma_desc_kmajor_sw128(smem_u32(stage_b + (size_t)s * b_stage));
+          const int rem = P.K - kc * KCH;
+          const int ksteps = rem >= KCH ? 4 : (rem >> 4);
+          for (int k = 0; k < ksteps; ++k)
+            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kc | k) != 0);
+          umma_commit(&empty[s]);   // smem slot reusable once these MMAs have read it
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&tmem_full[as]);  // accumulator complete
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // =========================== epilogue ===========================
+    const int et = threadIdx.x - 128;          // 0..127
+    const int q = warp & 3;                    // TMEM lane quadrant this warp may read
+    const int row = q * 32 + lane;
+    const int p = et & 7, rbase = et >> 3;     // pass-2 mapping: 16-byte piece p of rows rbase + 16 i
+    float s0[2][8], s1[2][8];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s0[c][j] = s1[c][j] = 0.f;
+    float esc[2][8], esh[2][8];
+    int prev_n = -1;
+    int it = 0;
+
+    auto flush = [&](int n0) {
+      if (EMODE == E_PLAIN) return;
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = s0[c][j], b = s1[c][j];
+          a += __shfl_xor_sync(0xffffffffu, a, 8);
+          a += __shfl_xor_sync(0xffffffffu, a, 16);
+          b += __shfl_xor_sync(0xffffffffu, b, 8);
+          b += __shfl_xor_sync(0xffffffffu, b, 16);
+          if (lane < 8) {
+            atomicAdd(&s_stats[c * 64 + lane * 8 + j], a);
+            atomicAdd(&s_stats[128 + c * 64 + lane * 8 + j], b);
+          }
+          s0[c][j] = s1[c][j] = 0.f;
+        }
+      named_bar_sync(1, EPI_THREADS);
+      if (et < P.block_n && n0 + et < P.N) {
+        atomicAdd(P.stats + n0 + et, s_stats[et]);
+        atomicAdd(P.stats + P.stats_stride + n0 + et, s_stats[128 + et]);
+      }
+      s_stats[et] = 0.f;
+      s_stats[128 + et] = 0.f;
+      named_bar_sync(1, EPI_THREADS);
+    };
+
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int m0 = (t / P.n_tiles) * BM, n0 = (t % P.n_tiles) * P.block_n;
+      if (n0 != prev_n) {
+        if (prev_n >= 0) flush(prev_n);
+        prev_n = n0;
+        if (EMODE == E_MASKSTATS) {
+#pragma unroll
+          for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int col = n0 + c * 64 + p * 8 + j;
+              esc[c][j] = col < P.N ? s_ecoef[col] : 0.f;
+              esh[c][j] = col < P.N ? s_ecoef[P.N + col] : 0.f;
+            }
+        }
+      }
+      const int as = it & 1;
+      uint8_t* ob = out_buf + (size_t)(it & 1) * nch * OUT_CHUNK;
+      const uint32_t ob_u32 = smem_u32(ob);
+      mbar_wait(&tmem_full[as], (it >> 1) & 1);
+      tc_fence_after();
+      // the TMA store issued from this staging buffer two tiles ago must have finished reading it
+      if (et == 0) tma_store_wait_read<1>();
+      named_bar_sync(1, EPI_THREADS);
+      // ---- pass 1: TMEM -> registers -> bf16 -> swizzled staging tile (one row per thread)
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * ACC_COLS;
+      for (int c16 = 0; c16 < (P.block_n >> 4); ++c16) {
+        uint32_t r[16];
+        tmem_ld_x16(taddr + c16 * 16, r);
+        tmem_ld_wait();
+        const uint4 lo = make_uint4(pack_bf16x2(__uint_as_float(r[0]), __uint_as_float(r[1])),
+                                    pack_bf16x2(__uint_as_float(r[2]), __uint_as_float(r[3])),
+                                    pack_bf16x2(__uint_as_float(r[4]), __uint_as_float(r[5])),
+                                    pack_bf16x2(__uint_as_float(r[6]), __uint_as_float(r[7])));
+        const uint4 hi = make_uint4(pack_bf16x2(__uint_as_float(r[8]), __uint_as_float(r[9])),
+                                    pack_bf16x2(__uint_as_float(r[10]), __uint_as_float(r[11])),
+                                    pack_bf16x2(__uint_as_float(r[12]), __uint_as_float(r[13])),
+                                    pack_bf16x2(__uint_as_float(r[14]), __uint_as_float(r[15])));
+        const uint32_t rowaddr = ob_u32 + (c16 >> 2) * OUT_CHUNK + row * 128;
+        const int pc = (c16 & 3) * 2;
+        sts16(rowaddr + (((pc) ^ (row & 7)) << 4), lo);
+        sts16(rowaddr + (((pc + 1) ^ (row & 7)) << 4), hi);
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[as]);   // accumulator stage free for the MMA warp
+      named_bar_sync(1, EPI_THREADS);
+      // ---- pass 2: coalesced sweep over the staged tile: statistics (and ReLU6 mask)
+      if (EMODE != E_PLAIN) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          if (c < nch) {
+            const int col0 = n0 + c * 64 + p * 8;
+            const bool colok = col0 < P.N && (c * 64 + p * 8) < P.block_n;
+            if (!colok) continue;   // staging columns past the tile hold no data
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int r = rbase + 16 * i;
+              const uint32_t addr = ob_u32 + c * OUT_CHUNK + r * 128 + ((p ^ (r & 7)) << 4);
+              float x[8];
+              unpack8(lds16(addr), x);
+              if (EMODE == E_STATS) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  s0[c][j] += x[j];
+                  s1[c][j] = fmaf(x[j], x[j], s1[c][j]);
+                }
+              } else {
+                const int gm = m0 + r;
+                float a[8];
+                uint4 av = make_uint4(0u, 0u, 0u, 0u);
+                if (gm < P.M) av = ldg_stream(P.aux + (size_t)gm * P.ldo + col0);
+                unpack8(av, a);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float z = fmaf(a[j], esc[c][j], esh[c][j]);
+                  const float o = (z > 0.f && z < 6.f) ? x[j] : 0.f;
+                  x[j] = o;
+                  s0[c][j] += o;
+                  s1[c][j] = fmaf(o, a[j], s1[c][j]);
+                }
+                sts16(addr, pack8(x));
+              }
+            }
+          }
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, EPI_THREADS);
+      } else {
+        fence_proxy_async_smem();
+        named_bar_sync(1, EPI_THREADS);
+      }
+      if (et == 0) {
+        for (int c = 0; c < nch; ++c) tma_store_2d(&tmO, ob + (size_t)c * OUT_CHUNK, n0 + c * 64, m0);
+        tma_store_commit();
+      }
+    }
+    if (prev_n >= 0) flush(prev_n);
+    if (et == 0) tma_store_wait_all<0>();
+  } else if (AMODE != A_TMA && warp >= 8) {
+    // =========================== A producers (register path) ===========================
+    const int pt = threadIdx.x - 256;          // 0..255
+    const int p = pt & 7, rb = pt >> 3;        // 16-byte piece p of rows rb + 32 i
+    int s = 0;
+    uint32_t ph = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int m0 = (t / P.n_tiles) * BM;
+      for (int kc = 0; kc < P.kc; ++kc) {
+        const int col = kc * KCH + p * 8;
+        const bool colok = col < P.K;
+        uint4 v0[4], v1[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int gm = m0 + rb + 32 * i;
+          v0[i] = make_uint4(0u, 0u, 0u, 0u);
+          v1[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (colok && gm < P.M) {
+            v0[i] = ldg_stream(P.a0 + (size_t)gm * P.lda + col);
+            if (AMODE == A_BNGRAD) v1[i] = ldg_stream(P.a1 + (size_t)gm * P.lda + col);
+          }
+        }
+        float c0[8], c1[8], c2[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          c0[j] = colok ? s_acoef[col + j] : 0.f;
+          c1[j] = colok ? s_acoef[P.K + col + j] : 0.f;
+          c2[j] = (AMODE == A_BNGRAD && colok) ? s_acoef[2 * P.K + col + j] : 0.f;
+        }
+        mbar_wait(&empty[s], ph ^ 1);
+        const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = rb + 32 * i;
+          const bool ok = colok && (m0 + r) < P.M;
+          float x[8], y[8];
+          unpack8(v0[i], x);
+          if (AMODE == A_BNRELU) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float z = fmaf(x[j], c0[j], c1[j]);
+              if (P.a_relu6) z = relu6f(z);
+              y[j] = ok ? z : 0.f;
+            }
+          } else {
+            float g[8];
+            unpack8(v1[i], g);   // v0 = dz, v1 = raw activation
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y[j] = ok ? fmaf(c0[j], x[j], fmaf(c1[j], g[j], c2[j])) : 0.f;
+          }
+          sts16(sa + r * 128 + ((p ^ (r & 7)) << 4), pack8(y));
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&full[s]);
+        if (++s == stages) { s = 0; ph ^= 1; }
+      }
+    }
+  }
+
+  // ---- teardown -------------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+template <int AMODE, int EMODE>
+int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
+  auto kern = pw_gemm_kernel<AMODE, EMODE>;
+  B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+  kern<<<pl.grid, AMODE == A_TMA ? 256 : 512, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmO, pl.p);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+}  // namespace
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_cols, uint32_t box_rows) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                               const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                               CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (encode == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    B200DP_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || fn == nullptr) {
+      set_error("cuTensorMapEncodeTiled not available from the driver");
+      return B200DP_ECUDA;
+    }
+    encode = reinterpret_cast<EncodeFn>(fn);
+  }
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) for rows=%llu cols=%llu ld=%llu box=%ux%u base=%p", (int)r,
+              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_cols, box_rows, base);
+    return B200DP_ECUDA;
+  }
+  return B200DP_OK;
+}
+
+int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, const void* a_tma, int lda,
+                 const void* a0, const void* a1, const float* acoef, int a_relu6, const void* w, void* out, int ldo,
+                 const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas) {
+  B200DP_REQUIRE(M > 0 && N > 0 && K > 0 && (N % 16) == 0 && (K % 16) == 0, "pw_gemm: M=%d N=%d K=%d invalid", M, N, K);
+  B200DP_REQUIRE((lda % 8) == 0 && (ldo % 8) == 0, "pw_gemm: row pitches must be multiples of 8 elements");
+  B200DP_REQUIRE(amode >= 0 && amode <= 2 && emode >= 0 && emode <= 2, "pw_gemm: bad mode");
+  PwGemmParams& p = pl->p;
+  p = PwGemmParams{};
+  p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldo = ldo;
+  p.block_n = N < 128 ? N : 128;
+  p.n_tiles = (N + p.block_n - 1) / p.block_n;
+  p.m_tiles = (M + BM - 1) / BM;
+  p.kc = (K + KCH - 1) / KCH;
+  p.a0 = static_cast<const __nv_bfloat16*>(a0);
+  p.a1 = static_cast<const __nv_bfloat16*>(a1);
+  p.acoef = acoef; p.a_relu6 = a_relu6;
+  p.aux = static_cast<const __nv_bfloat16*>(aux);
+  p.ecoef = ecoef; p.stats = stats; p.stats_stride = stats_stride;
+  if (amode == A_TMA) B200DP_REQUIRE(a_tma != nullptr, "pw_gemm: A pointer missing");
+  if (amode != A_TMA) B200DP_REQUIRE(a0 != nullptr && acoef != nullptr, "pw_gemm: register-path A needs a0 + acoef");
+  if (amode == A_BNGRAD) B200DP_REQUIRE(a1 != nullptr, "pw_gemm: A_BNGRAD needs a1");
+  if (emode != E_PLAIN) B200DP_REQUIRE(stats != nullptr, "pw_gemm: stats pointer missing");
+  if (emode == E_MASKSTATS) B200DP_REQUIRE(aux != nullptr && ecoef != nullptr, "pw_gemm: E_MASKSTATS needs aux + ecoef");
+  const int nch = (p.block_n + 63) / 64;
+  const size_t fixed = 2 * (size_t)nch * OUT_CHUNK + ((amode == A_BNRELU ? 2 : amode == A_BNGRAD ? 3 : 0) * (size_t)K +
+                       (emode == E_MASKSTATS ? 2 : 0) * (size_t)N + 256) * 4 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024;
+  const size_t per_stage = A_STAGE + (size_t)p.block_n * 128;
+  const size_t budget = 220 * 1024;
+  B200DP_REQUIRE(fixed + 2 * per_stage <= budget, "pw_gemm: shared memory budget exceeded (K=%d N=%d)", K, N);
+  int stages = (int)((budget - fixed) / per_stage);
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  p.stages = stages;
+  pl->smem_bytes = fixed + stages * per_stage;
+  pl->amode = amode; pl->emode = emode;
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int cap = max_ctas > 0 ? max_ctas : num_sms();
+  pl->grid = tiles < cap ? tiles : cap;
+  if (amode == A_TMA) {
+    if (int rc = make_tmap_2d_bf16(&pl->tmA, a_tma, M, K, lda, KCH, BM)) return rc;
+  } else {
+    pl->tmA = CUtensorMap{};
+  }
+  if (int rc = make_tmap_2d_bf16(&pl->tmB, w, N, K, K, KCH, p.block_n)) return rc;
+  if (int rc = make_tmap_2d_bf16(&pl->tmO, out, M, N, ldo, 64, BM)) return rc;
+  return B200DP_OK;
+}
+
+int pw_gemm_launch(const PwGemmPlan& pl, cudaStream_t s) {
+  switch (pl.amode * 3 + pl.emode) {
+    case 0: return launch_t<A_TMA, E_PLAIN>(pl, s);
+    case 1: return launch_t<A_TMA, E_STATS>(pl, s);
+    case 2: return launch_t<A_TMA, E_MASKSTATS>(pl, s);
+    case 3: return launch_t<A_BNRELU, E_PLAIN>(pl, s);
+    case 4: return launch_t<A_BNRELU, E_STATS>(pl, s);
+    case 5: return launch_t<A_BNRELU, E_MASKSTATS>(pl, s);
+    case 6: return launch_t<A_BNGRAD, E_PLAIN>(pl, s);
+    case 7: return launch_t<A_BNGRAD, E_STATS>(pl, s);
+    default: return launch_t<A_BNGRAD, E_MASKSTATS>(pl, s);
+  }
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+// Stand-alone entry point (tests, micro-benchmarks): builds the plan (tensor maps) and launches once.
+extern "C" int b200dp_pw_gemm(int amode, int emode, int M, int N, int K, const void* a_tma, int lda,
+                              const void* a0, const void* a1, const float* acoef, int a_relu6, const void* w,
+                              void* out, int ldo, const void* aux, const float* ecoef, float* stats,
+                              int stats_stride, int max_ctas, void* stream) {
+  PwGemmPlan pl;
+  if (int rc = pw_gemm_plan(&pl, amode, emode, M, N, K, a_tma, lda, a0, a1, acoef, a_relu6, w, out, ldo, aux, ecoef,
+                            stats, stats_stride, max_ctas))
+    return rc;
+  return pw_gemm_launch(pl, static_cast<cudaStream_t>(stream));
+}

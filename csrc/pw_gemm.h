@@ -1,0 +1,40 @@
+// Internal interface of the tcgen05 pointwise-convolution GEMM (csrc/pw_gemm.cu).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+namespace b200dp {
+
+enum { A_TMA = 0, A_BNRELU = 1, A_BNGRAD = 2 };
+enum { E_PLAIN = 0, E_STATS = 1, E_MASKSTATS = 2 };
+
+struct PwGemmParams {
+  int M, N, K;                  // rows, output channels, input channels (channels are multiples of 16)
+  int lda, ldo;                 // row pitches (elements) of the register-path A sources / of out and aux
+  int block_n, n_tiles, m_tiles, kc, stages;
+  const __nv_bfloat16* a0;      // A_BNRELU: raw activation          A_BNGRAD: dz
+  const __nv_bfloat16* a1;      //                                    A_BNGRAD: raw activation x
+  const float* acoef;           // A_BNRELU: [2][K] scale, shift      A_BNGRAD: [3][K] ca, cb, cc
+  int a_relu6;                  // A_BNRELU: clamp to [0, 6] after the affine
+  const __nv_bfloat16* aux;     // E_MASKSTATS: raw forward activation of the tensor being differentiated [M][ldo]
+  const float* ecoef;           // E_MASKSTATS: [2][N] scale, shift of that activation's BatchNorm
+  float* stats;                 // E_STATS: sum y, sum y^2   E_MASKSTATS: sum dz, sum dz*aux   ([2] x stats_stride)
+  int stats_stride;
+};
+
+struct PwGemmPlan {
+  CUtensorMap tmA, tmB, tmO;
+  PwGemmParams p;
+  int amode, emode, grid;
+  size_t smem_bytes;
+};
+
+int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, const void* a_tma, int lda,
+                 const void* a0, const void* a1, const float* acoef, int a_relu6, const void* w, void* out, int ldo,
+                 const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas);
+int pw_gemm_launch(const PwGemmPlan& pl, cudaStream_t s);
+
+}  // namespace b200dp

@@ -89,3 +89,54 @@ def softmax_topk(logits: torch.Tensor, k: int = 3) -> Tuple[torch.Tensor, torch.
     ti = torch.empty((B, k), dtype=torch.int32, device=logits.device)
     check(lib.b200dp_softmax_topk(ptr(logits), ptr(probs), ptr(tv), ptr(ti), B, Cn, k, current_stream()))
     return probs, tv, ti
+
+
+A_TMA, A_BNRELU, A_BNGRAD = 0, 1, 2
+E_PLAIN, E_STATS, E_MASKSTATS = 0, 1, 2
+
+
+def pw_gemm(w: torch.Tensor, *, a: Optional[torch.Tensor] = None, a_raw: Optional[torch.Tensor] = None,
+            a_dz: Optional[torch.Tensor] = None, acoef: Optional[torch.Tensor] = None, relu6: bool = True,
+            emode: int = E_PLAIN, aux: Optional[torch.Tensor] = None, ecoef: Optional[torch.Tensor] = None,
+            stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, max_ctas: int = 0
+            ) -> torch.Tensor:
+    """Pointwise-conv GEMM ``out[M,N] = Aeff[M,K] @ w[N,K]^T`` on tcgen05 (csrc/pw_gemm.cu).
+
+    A operand: ``a`` (bf16 [M,K], TMA path), or ``a_raw`` + ``acoef`` [2,K] (BatchNorm scale/shift
+    [+ReLU6] applied on load), or ``a_dz`` + ``a_raw`` + ``acoef`` [3,K] (BatchNorm input gradient
+    ``ca*dz + cb*x + cc`` formed on load).  ``emode``: E_STATS accumulates ``stats[0] += sum(out)``,
+    ``stats[1] += sum(out^2)`` per channel; E_MASKSTATS masks with ReLU6'(ecoef[0]*aux + ecoef[1]) and
+    accumulates ``sum(out)``, ``sum(out*aux)``.
+    """
+    lib = _lib.require()
+    _chk(w, torch.bfloat16, "w")
+    N, K = w.shape
+    if a is not None:
+        amode, src = A_TMA, _chk(a, torch.bfloat16, "a")
+    elif a_dz is not None:
+        amode, src = A_BNGRAD, _chk(a_dz, torch.bfloat16, "a_dz")
+        _chk(a_raw, torch.bfloat16, "a_raw")
+    else:
+        amode, src = A_BNRELU, _chk(a_raw, torch.bfloat16, "a_raw")
+    M = src.shape[0]
+    if src.shape[1] != K:
+        raise ValueError(f"A has {src.shape[1]} channels, weights expect {K}")
+    if amode != A_TMA:
+        _chk(acoef, torch.float32, "acoef")
+        if tuple(acoef.shape) != ((3 if amode == A_BNGRAD else 2), K):
+            raise ValueError("acoef shape")
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=w.device)
+    if emode != E_PLAIN:
+        _chk(stats, torch.float32, "stats")
+        if tuple(stats.shape) != (2, N):
+            raise ValueError("stats must be [2, N]")
+    if emode == E_MASKSTATS:
+        _chk(aux, torch.bfloat16, "aux")
+        _chk(ecoef, torch.float32, "ecoef")
+    a0 = a_dz if amode == A_BNGRAD else a_raw
+    a1 = a_raw if amode == A_BNGRAD else None
+    check(lib.b200dp_pw_gemm(amode, emode, M, N, K, ptr(a), K, ptr(a0), ptr(a1), ptr(acoef), 1 if relu6 else 0,
+                             ptr(w), ptr(out), N, ptr(aux), ptr(ecoef), ptr(stats), N, max_ctas,
+                             current_stream()))
+    return out

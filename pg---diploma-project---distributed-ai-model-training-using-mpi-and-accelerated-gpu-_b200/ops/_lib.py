@@ -59,6 +59,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_preprocess": [vp, vp, vp, i, i, i, vp],
         "b200dp_softmax_xent": [vp, vp, vp, vp, vp, i, i, f, vp],
         "b200dp_softmax_topk": [vp, vp, vp, vp, i, i, i, vp],
+        "b200dp_pw_gemm": [i, i, i, i, i, vp, i, vp, vp, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
