@@ -1,0 +1,250 @@
+// BatchNorm plumbing and the small elementwise passes over the *bottleneck* tensors (K4, K6).
+//
+// Training-mode BatchNorm never runs as a pass over an expanded activation here: producers emit per-channel
+// sums from their epilogues and consumers apply scale/shift (+ReLU6) while loading.  What remains are
+//   * per-channel finalisation kernels (C <= 1280 values): sums -> mean / inv-std / scale / shift / running
+//     statistics (forward), sums -> (ca, cb, cc, dgamma, dbeta) (backward);
+//   * passes over the narrow block outputs (16..320 channels, 8.6 % of the activation volume):
+//     y = scale*p_raw + shift (+ residual)            block output (linear bottleneck, K6 residual add)
+//     dout = g1 (+ g2), sums for the projection BN     gradient join of the residual branch
+//     dp = ca*dout + cb*p_raw + cc                     BatchNorm backward of the projection conv
+// Reference behaviour replaced: cuDNN batch-norm forward/backward and ATen add kernels.
+#include "common.cuh"
+
+namespace b200dp {
+namespace {
+
+// ---- forward finalisation -----------------------------------------------------------------------------
+__global__ void bn_fwd_finalize_kernel(const float* __restrict__ sums, int stride, const float* __restrict__ gamma,
+                                       const float* __restrict__ beta, float count, float eps, float momentum,
+                                       float* __restrict__ rmean, float* __restrict__ rvar,
+                                       float* __restrict__ coef /*[2][C] scale, shift*/,
+                                       float* __restrict__ saved /*[2][C] mean, invstd*/, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = sums[c] / count;
+  const float var = fmaxf(sums[stride + c] / count - mean * mean, 0.f);
+  const float inv = rsqrtf(var + eps);
+  const float sc = gamma[c] * inv;
+  coef[c] = sc;
+  coef[C + c] = beta[c] - mean * sc;
+  saved[c] = mean;
+  saved[C + c] = inv;
+  if (rmean != nullptr) {   // torch: running = (1-m) running + m batch, variance unbiased
+    rmean[c] = (1.f - momentum) * rmean[c] + momentum * mean;
+    const float unb = count > 1.f ? var * count / (count - 1.f) : var;
+    rvar[c] = (1.f - momentum) * rvar[c] + momentum * unb;
+  }
+}
+
+__global__ void bn_eval_coef_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                                    const float* __restrict__ rmean, const float* __restrict__ rvar, float eps,
+                                    float* __restrict__ coef, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float sc = gamma[c] * rsqrtf(rvar[c] + eps);
+  coef[c] = sc;
+  coef[C + c] = beta[c] - rmean[c] * sc;
+}
+
+// ---- backward finalisation ----------------------------------------------------------------------------
+// sums = (sum dz, sum dz*x) over the batch.  dx = ca*dz + cb*x + cc.
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ sums, int stride, const float* __restrict__ saved,
+                                       const float* __restrict__ gamma, float count, float* __restrict__ coef3,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mean = saved[c], r = saved[C + c], g = gamma[c];
+  const float db = sums[c];
+  const float dg = r * (sums[stride + c] - mean * db);
+  const float gr = g * r;
+  coef3[c] = gr;
+  const float cb = -gr * r * dg / count;
+  coef3[C + c] = cb;
+  coef3[2 * C + c] = -gr * db / count - cb * mean;
+  dgamma[c] += dg;
+  dbeta[c] += db;
+}
+
+// ---- passes over bottleneck tensors -------------------------------------------------------------------
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                    pack_bf16x2(f[6], f[7]));
+}
+
+// out = c0*a + c1 (+ res)            (forward block output)
+// out = c0*a + c1*b + c2             (three = 1: BatchNorm backward apply)
+__global__ void __launch_bounds__(256)
+affine_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+              const float* __restrict__ coef, int three, __nv_bfloat16* __restrict__ out, long long rows, int C) {
+  const int CG = C >> 3;
+  const long long total = rows * CG;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CG);
+    const int c0 = cg * 8;
+    float x[8], y[8], o[8];
+    unpack8(ldg_stream(a + i * 8), x);
+    const bool hasb = b != nullptr;
+    if (hasb) unpack8(ldg_stream(b + i * 8), y);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float k0 = __ldg(coef + c0 + j), k1 = __ldg(coef + C + c0 + j);
+      if (three) o[j] = fmaf(k0, x[j], fmaf(k1, y[j], __ldg(coef + 2 * C + c0 + j)));
+      else o[j] = fmaf(k0, x[j], k1) + (hasb ? y[j] : 0.f);
+    }
+    stg_stream(out + i * 8, pack8(o));
+  }
+}
+
+// dout = g1 (+ g2) [written only when g2 != null], sums += (sum dout, sum dout*x) per channel.
+// Each thread keeps one 8-channel group for its whole life (grid stride is a multiple of CG).
+__global__ void __launch_bounds__(256)
+grad_join_stats_kernel(const __nv_bfloat16* __restrict__ g1, const __nv_bfloat16* __restrict__ g2,
+                       const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dout,
+                       float* __restrict__ sums, int stride, long long rows, int C) {
+  extern __shared__ float s_red[];   // [2][C]
+  const int CG = C >> 3;
+  const int ipb = blockDim.x / CG;
+  const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+  if (ti < ipb) {
+    float s0[8], s1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
+    for (long long r = (long long)blockIdx.x * ipb + ti; r < rows; r += (long long)gridDim.x * ipb) {
+      const long long off = r * C + cg * 8;
+      float a[8], xv[8];
+      unpack8(ldg_stream(g1 + off), a);
+      unpack8(ldg_stream(x + off), xv);
+      if (g2 != nullptr) {
+        float b[8];
+        unpack8(ldg_stream(g2 + off), b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] += b[j];
+        const uint4 pk = pack8(a);
+        stg_stream(dout + off, pk);
+        unpack8(pk, a);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s0[j] += a[j]; s1[j] = fmaf(a[j], xv[j], s1[j]); }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s_red[cg * 8 + j], s0[j]);
+      atomicAdd(&s_red[C + cg * 8 + j], s1[j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(sums + i, s_red[i]);
+    atomicAdd(sums + stride + i, s_red[C + i]);
+  }
+}
+
+// Weight preparation: fp32 master [N][K] -> bf16 [N][K] and bf16 transposed [K][N] for every pointwise conv.
+struct WPrepEntry { long long off; int n, k; };
+
+__global__ void __launch_bounds__(256)
+weight_prep_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt,
+                   const WPrepEntry* __restrict__ table) {
+  const WPrepEntry e = table[blockIdx.y];
+  const int total = e.n * e.k;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int n = i / e.k, k = i - n * e.k;
+    const __nv_bfloat16 v = __float2bfloat16(master[e.off + i]);
+    if (w != nullptr) w[e.off + i] = v;
+    wt[e.off + (long long)k * e.n + n] = v;
+  }
+}
+
+}  // namespace
+
+int bn_fwd_finalize_launch(const float* sums, int stride, const float* gamma, const float* beta, float count,
+                           float eps, float momentum, float* rmean, float* rvar, float* coef, float* saved, int C,
+                           cudaStream_t s) {
+  bn_fwd_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(sums, stride, gamma, beta, count, eps, momentum, rmean, rvar,
+                                                         coef, saved, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int bn_eval_coef_launch(const float* gamma, const float* beta, const float* rmean, const float* rvar, float eps,
+                        float* coef, int C, cudaStream_t s) {
+  bn_eval_coef_kernel<<<(C + 127) / 128, 128, 0, s>>>(gamma, beta, rmean, rvar, eps, coef, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int bn_bwd_finalize_launch(const float* sums, int stride, const float* saved, const float* gamma, float count,
+                           float* coef3, float* dgamma, float* dbeta, int C, cudaStream_t s) {
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(sums, stride, saved, gamma, count, coef3, dgamma, dbeta, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int affine_launch(const void* a, const void* b, const float* coef, int three, void* out, long long rows, int C,
+                  cudaStream_t s) {
+  B200DP_REQUIRE(C % 8 == 0, "affine: C must be a multiple of 8");
+  const long long total = rows * (C / 8);
+  long long blocks = (total + 255) / 256;
+  const long long cap = (long long)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  affine_kernel<<<(int)blocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b),
+                                            coef, three, static_cast<__nv_bfloat16*>(out), rows, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int grad_join_stats_launch(const void* g1, const void* g2, const void* x, void* dout, float* sums, int stride,
+                           long long rows, int C, cudaStream_t s) {
+  B200DP_REQUIRE(C % 8 == 0 && C / 8 <= 256, "grad_join: C=%d unsupported", C);
+  const int CG = C / 8;
+  const int threads = (256 / CG) * CG;
+  const int ipb = threads / CG;
+  long long blocks = (rows + ipb - 1) / ipb;
+  const long long cap = (long long)num_sms() * 4;
+  if (blocks > cap) blocks = cap;
+  grad_join_stats_kernel<<<(int)blocks, threads, 2 * C * sizeof(float), s>>>(
+      static_cast<const __nv_bfloat16*>(g1), static_cast<const __nv_bfloat16*>(g2),
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(dout), sums, stride, rows, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int weight_prep_launch(const float* master, void* w, void* wt, const void* table_dev, int nlayers, cudaStream_t s) {
+  dim3 grid(32, nlayers);
+  weight_prep_kernel<<<grid, 256, 0, s>>>(master, static_cast<__nv_bfloat16*>(w), static_cast<__nv_bfloat16*>(wt),
+                                          static_cast<const WPrepEntry*>(table_dev));
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_bn_fwd_finalize(const float* sums, int stride, const float* gamma, const float* beta,
+                                      float count, float eps, float momentum, float* rmean, float* rvar, float* coef,
+                                      float* saved, int C, void* stream) {
+  return bn_fwd_finalize_launch(sums, stride, gamma, beta, count, eps, momentum, rmean, rvar, coef, saved, C,
+                                static_cast<cudaStream_t>(stream));
+}
+extern "C" int b200dp_bn_bwd_finalize(const float* sums, int stride, const float* saved, const float* gamma,
+                                      float count, float* coef3, float* dgamma, float* dbeta, int C, void* stream) {
+  return bn_bwd_finalize_launch(sums, stride, saved, gamma, count, coef3, dgamma, dbeta, C,
+                                static_cast<cudaStream_t>(stream));
+}
+extern "C" int b200dp_affine(const void* a, const void* b, const float* coef, int three, void* out, long long rows,
+                             int C, void* stream) {
+  return affine_launch(a, b, coef, three, out, rows, C, static_cast<cudaStream_t>(stream));
+}
+extern "C" int b200dp_grad_join_stats(const void* g1, const void* g2, const void* x, void* dout, float* sums,
+                                      int stride, long long rows, int C, void* stream) {
+  return grad_join_stats_launch(g1, g2, x, dout, sums, stride, rows, C, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,616 @@
+// Native executor: builds the MobileNetV2 layer plan, owns the activation / statistics workspace, and runs a
+// whole training or evaluation step as one sequence of hand-written kernels -- captured into a CUDA graph
+// per batch size, so a step costs one graph launch on the host.
+//
+// Reference behaviour replaced: the Python hot loop zero_grad -> forward -> loss -> backward of
+// cifar10_mpi_mobilenet_224.py:173-184 with ~700 ATen/cuDNN kernel launches and two host syncs per step.
+// The optimiser / gradient all-reduce is NOT in here: gradients are left in the caller's flat fp32 arena
+// (which lives in peer-mapped memory) and the fused all-reduce + Adam kernel (comm_adam.cu) consumes them.
+//
+// Data flow per inverted-residual block (training):
+//   x (finished, bf16) --expand GEMM [TMA A, stats epilogue]--> e_raw --dw conv [BN+ReLU6 on load, stats]--> d_raw
+//     --project GEMM [BN+ReLU6 prologue, stats epilogue]--> p_raw --affine (+x)--> next x
+// and the mirror image backwards; every expanded tensor is written once and read once per direction.
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+extern "C" int b200dp_preprocess(const uint8_t* images, const float* params, void* out_bf16, int batch, int size,
+                                 int out_channels, void* stream);
+extern "C" int b200dp_softmax_xent(const float* logits, const int64_t* labels, float* loss_out, float* dlogits_out,
+                                   double* metrics, int batch, int classes, float mean_over, void* stream);
+
+namespace b200dp {
+namespace {
+
+inline int pad16(int c) { return (c + 15) / 16 * 16; }
+
+struct Conv {
+  int kind;            // 0 stem, 1 dw, 2 pw
+  int role;            // 0 stem, 1 expand, 2 dw, 3 project, 4 last
+  int cin, cout, cinp, coutp, stride, hin, hout, block;
+  long long off_w, off_g, off_b, off_rm, off_rv;    // element offsets: params arena (w, gamma, beta), buffer arena
+  // workspace
+  __nv_bfloat16* raw = nullptr;                      // raw conv output [B, hout, hout, coutp]
+  float *sums_f = nullptr, *sums_b = nullptr, *coef_f = nullptr, *saved = nullptr, *coef_b = nullptr;
+};
+
+struct Block {
+  int index, cin, cout, cinp, coutp, stride, expand, hin, hout;
+  bool use_res;
+  int ce, cd, cp;      // conv indices (ce = -1 when expand == 1)
+  __nv_bfloat16* xout = nullptr;   // finished block output [B, hout, hout, coutp]
+};
+
+struct WPrepEntry { long long off; int n, k; };
+
+struct Plans {            // per batch size
+  int n = 0;
+  std::vector<PwGemmPlan> fwd, fwd_eval, dgrad;    // indexed by conv
+  cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
+  int train_aug = -1;      // augmentation flag the train graph was captured with
+};
+
+}  // namespace
+
+struct Engine {
+  int B, S, classes;
+  float p_drop, eps, momentum;
+  uint32_t seed;
+  std::vector<Conv> convs;
+  std::vector<Block> blocks;
+  long long off_fcw, off_fcb, param_total, buffer_total;
+  float *params, *grads, *buffers;
+  // workspace
+  char* ws = nullptr;
+  size_t ws_bytes = 0;
+  uint8_t* in_images = nullptr;
+  int64_t* in_labels = nullptr;
+  float* in_aug = nullptr;
+  __nv_bfloat16 *x0 = nullptr, *w_bf16 = nullptr, *wt_bf16 = nullptr;
+  __nv_bfloat16 *dzd = nullptr, *dze = nullptr, *dp = nullptr, *gx[2] = {nullptr, nullptr}, *dout[2] = {nullptr, nullptr};
+  float *sums_all = nullptr;
+  size_t sums_bytes = 0;
+  float *pooled = nullptr, *drop = nullptr, *logits = nullptr, *dlogits = nullptr, *dpool = nullptr;
+  double *metrics_train = nullptr, *metrics_eval = nullptr;
+  int* step_dev = nullptr;
+  WPrepEntry* wprep_dev = nullptr;
+  int n_pw = 0;
+  bool use_graphs = true;
+  cudaStream_t cap_stream = nullptr;   // graphs are captured here (the caller's stream may be the legacy default stream)
+  bool eval_coef_valid = false;
+  std::map<int, Plans> plans;
+  // profiling
+  bool profiling = false;
+  std::vector<std::pair<std::string, cudaEvent_t>> prof_events;
+};
+
+namespace {
+
+#define ENG_TRY(call)            \
+  do {                           \
+    int rc__ = (call);           \
+    if (rc__ != B200DP_OK) return rc__; \
+  } while (0)
+
+void build_spec(Engine& e, const long long* off) {
+  static const int setting[7][4] = {{1, 16, 1, 1}, {6, 24, 2, 2}, {6, 32, 3, 2}, {6, 64, 4, 2},
+                                    {6, 96, 3, 1}, {6, 160, 3, 2}, {6, 320, 1, 1}};
+  auto add = [&](int kind, int role, int cin, int cout, int stride, int hin, int block) {
+    Conv c{};
+    c.kind = kind; c.role = role; c.cin = cin; c.cout = cout; c.cinp = pad16(cin); c.coutp = pad16(cout);
+    c.stride = stride; c.hin = hin; c.hout = (hin - 1) / stride + 1; c.block = block;
+    const int i = (int)e.convs.size();
+    c.off_w = off[i * 5 + 0]; c.off_g = off[i * 5 + 1]; c.off_b = off[i * 5 + 2];
+    c.off_rm = off[i * 5 + 3]; c.off_rv = off[i * 5 + 4];
+    e.convs.push_back(c);
+    return i;
+  };
+  int h = e.S;
+  add(0, 0, 3, 32, 2, h, 0);
+  h = e.convs[0].hout;
+  int cin = 32, feat = 1;
+  for (auto& st : setting) {
+    for (int i = 0; i < st[2]; ++i) {
+      const int stride = i == 0 ? st[3] : 1;
+      const int hidden = cin * st[0];
+      Block b{};
+      b.index = feat; b.cin = cin; b.cout = st[1]; b.cinp = pad16(cin); b.coutp = pad16(st[1]);
+      b.stride = stride; b.expand = st[0]; b.hin = h; b.hout = (h - 1) / stride + 1;
+      b.use_res = stride == 1 && cin == st[1];
+      b.ce = st[0] != 1 ? add(2, 1, cin, hidden, 1, h, feat) : -1;
+      b.cd = add(1, 2, hidden, hidden, stride, h, feat);
+      b.cp = add(2, 3, hidden, st[1], 1, b.hout, feat);
+      e.blocks.push_back(b);
+      cin = st[1];
+      h = b.hout;
+      ++feat;
+    }
+  }
+  add(2, 4, cin, 1280, 1, h, feat);
+  const int nc = (int)e.convs.size();
+  e.off_fcw = off[nc * 5];
+  e.off_fcb = off[nc * 5 + 1];
+}
+
+template <typename T>
+T* carve(char*& p, size_t count) {
+  T* r = reinterpret_cast<T*>(p);
+  p += (count * sizeof(T) + 255) / 256 * 256;
+  return r;
+}
+
+size_t layout_workspace(Engine& e, char* base) {
+  char* p = base;
+  const size_t B = e.B;
+  e.in_images = carve<uint8_t>(p, B * 32 * 32 * 3);
+  e.in_labels = carve<int64_t>(p, B);
+  e.in_aug = carve<float>(p, B * B200DP_AUG_NPARAM);
+  e.x0 = carve<__nv_bfloat16>(p, B * e.S * e.S * 4);
+  e.w_bf16 = carve<__nv_bfloat16>(p, e.param_total);
+  e.wt_bf16 = carve<__nv_bfloat16>(p, e.param_total);
+  size_t max_d = 0, max_e = 0, max_x = 0;
+  // statistics region first (one memset per step)
+  char* sums0 = p;
+  for (auto& c : e.convs) {
+    c.sums_f = carve<float>(p, 2 * c.coutp);
+    c.sums_b = carve<float>(p, 2 * c.coutp);
+  }
+  e.sums_all = reinterpret_cast<float*>(sums0);
+  e.sums_bytes = (size_t)(p - sums0);
+  for (auto& c : e.convs) {
+    c.coef_f = carve<float>(p, 2 * c.coutp);
+    c.saved = carve<float>(p, 2 * c.coutp);
+    c.coef_b = carve<float>(p, 3 * c.coutp);
+    const size_t elems = B * c.hout * c.hout * c.coutp;
+    c.raw = carve<__nv_bfloat16>(p, elems);
+    if (c.role == 2) max_d = elems > max_d ? elems : max_d;
+    if (c.role == 1 || c.role == 0 || c.role == 4) max_e = elems > max_e ? elems : max_e;
+  }
+  for (auto& b : e.blocks) {
+    const size_t elems = B * b.hout * b.hout * b.coutp;
+    b.xout = carve<__nv_bfloat16>(p, elems);
+    max_x = elems > max_x ? elems : max_x;
+    const size_t ein = B * b.hin * b.hin * b.cinp;
+    max_x = ein > max_x ? ein : max_x;
+  }
+  e.dzd = carve<__nv_bfloat16>(p, max_d);
+  e.dze = carve<__nv_bfloat16>(p, max_e);
+  e.dp = carve<__nv_bfloat16>(p, max_x);
+  for (int i = 0; i < 2; ++i) {
+    e.gx[i] = carve<__nv_bfloat16>(p, max_x);
+    e.dout[i] = carve<__nv_bfloat16>(p, max_x);
+  }
+  e.pooled = carve<float>(p, B * 1280);
+  e.drop = carve<float>(p, B * 1280);
+  e.dpool = carve<float>(p, B * 1280);
+  e.logits = carve<float>(p, B * e.classes);
+  e.dlogits = carve<float>(p, B * e.classes);
+  e.metrics_train = carve<double>(p, 4);
+  e.metrics_eval = carve<double>(p, 4);
+  e.step_dev = carve<int>(p, 4);
+  e.wprep_dev = carve<WPrepEntry>(p, 64);
+  return (size_t)(p - base);
+}
+
+// profiling hook: call after each launch
+void mark(Engine& e, cudaStream_t s, const char* name, int conv = -1) {
+  if (!e.profiling) return;
+  cudaEvent_t ev;
+  cudaEventCreate(&ev);
+  cudaEventRecord(ev, s);
+  std::string label = name;
+  if (conv >= 0) label += "#" + std::to_string(conv);
+  e.prof_events.emplace_back(label, ev);
+}
+
+int build_plans(Engine& e, Plans& pl, int n) {
+  pl.n = n;
+  const int nc = (int)e.convs.size();
+  pl.fwd.assign(nc, PwGemmPlan{});
+  pl.fwd_eval.assign(nc, PwGemmPlan{});
+  pl.dgrad.assign(nc, PwGemmPlan{});
+  for (auto& b : e.blocks) {
+    const Conv& cp = e.convs[b.cp];
+    const Conv& cd = e.convs[b.cd];
+    const int Mout = n * b.hout * b.hout;
+    const int Min = n * b.hin * b.hin;
+    const __nv_bfloat16* xin = b.index == 1 ? nullptr : e.blocks[b.index - 2].xout;
+    if (b.ce >= 0) {
+      const Conv& ce = e.convs[b.ce];
+      for (int ev = 0; ev < 2; ++ev)
+        ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[b.ce] : &pl.fwd[b.ce], A_TMA, ev ? E_PLAIN : E_STATS, Min, ce.coutp,
+                             ce.cinp, xin, ce.cinp, nullptr, nullptr, nullptr, 0, e.w_bf16 + ce.off_w, ce.raw, ce.coutp,
+                             nullptr, nullptr, ce.sums_f, ce.coutp, 0));
+      // dgrad: dx[M, cin] = BNgrad(dze, e_raw)[M, hidden] * W[hidden, cin]   (weights transposed: [cin][hidden])
+      ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp, e.dze, ce.raw,
+                           ce.coef_b, 0, e.wt_bf16 + ce.off_w, e.gx[0], ce.cinp, nullptr, nullptr, nullptr, 0, 0));
+    }
+    for (int ev = 0; ev < 2; ++ev)
+      ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[b.cp] : &pl.fwd[b.cp], A_BNRELU, ev ? E_PLAIN : E_STATS, Mout, cp.coutp,
+                           cp.cinp, nullptr, cp.cinp, cd.raw, nullptr, cd.coef_f, 1, e.w_bf16 + cp.off_w, cp.raw,
+                           cp.coutp, nullptr, nullptr, cp.sums_f, cp.coutp, 0));
+    // project dgrad: dzd[M, hidden] = mask(dp[M, cout] * W[cout, hidden])   (weights transposed: [hidden][cout])
+    ENG_TRY(pw_gemm_plan(&pl.dgrad[b.cp], A_TMA, E_MASKSTATS, Mout, cp.cinp, cp.coutp, e.dp, cp.coutp, nullptr, nullptr,
+                         nullptr, 0, e.wt_bf16 + cp.off_w, e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, 0));
+  }
+  {
+    const int li = nc - 1;
+    const Conv& cl = e.convs[li];
+    const Block& lb = e.blocks.back();
+    const int M = n * cl.hin * cl.hin;
+    for (int ev = 0; ev < 2; ++ev)
+      ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[li] : &pl.fwd[li], A_TMA, ev ? E_PLAIN : E_STATS, M, cl.coutp, cl.cinp,
+                           lb.xout, cl.cinp, nullptr, nullptr, nullptr, 0, e.w_bf16 + cl.off_w, cl.raw, cl.coutp, nullptr,
+                           nullptr, cl.sums_f, cl.coutp, 0));
+    ENG_TRY(pw_gemm_plan(&pl.dgrad[li], A_BNGRAD, E_PLAIN, M, cl.cinp, cl.coutp, nullptr, cl.coutp, e.dze, cl.raw,
+                         cl.coef_b, 0, e.wt_bf16 + cl.off_w, e.gx[0], cl.cinp, nullptr, nullptr, nullptr, 0, 0));
+  }
+  return B200DP_OK;
+}
+
+// A dgrad plan writes to a fixed output buffer chosen at plan time; the executor alternates gx[0]/gx[1], so the
+// output tensor map is re-encoded when the target changes (cheap; host only).
+int retarget_out(PwGemmPlan& pl, void* out) {
+  return make_tmap_2d_bf16(&pl.tmO, out, (uint64_t)pl.p.M, (uint64_t)pl.p.N, (uint64_t)pl.p.ldo, 64, 128);
+}
+
+int bn_fin_f(Engine& e, Conv& c, float count, cudaStream_t s) {
+  return bn_fwd_finalize_launch(c.sums_f, c.coutp, e.params + c.off_g, e.params + c.off_b, count, e.eps, e.momentum,
+                                e.buffers + c.off_rm, e.buffers + c.off_rv, c.coef_f, c.saved, c.coutp, s);
+}
+int bn_fin_b(Engine& e, Conv& c, float count, cudaStream_t s) {
+  return bn_bwd_finalize_launch(c.sums_b, c.coutp, c.saved, e.params + c.off_g, count, c.coef_b, e.grads + c.off_g,
+                                e.grads + c.off_b, c.coutp, s);
+}
+
+int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t s) {
+  ENG_TRY(weight_prep_launch(e.params, e.w_bf16, e.wt_bf16, e.wprep_dev, e.n_pw, s));
+  mark(e, s, "weight_prep");
+  if (train) {
+    B200DP_CUDA(cudaMemsetAsync(e.sums_all, 0, e.sums_bytes, s));
+  } else if (!e.eval_coef_valid) {
+    for (auto& c : e.convs)
+      ENG_TRY(bn_eval_coef_launch(e.params + c.off_g, e.params + c.off_b, e.buffers + c.off_rm, e.buffers + c.off_rv,
+                                  e.eps, c.coef_f, c.coutp, s));
+    mark(e, s, "bn_eval_coef");
+  }
+  ENG_TRY(b200dp_preprocess(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0, n, e.S, 4, s));
+  mark(e, s, "preprocess");
+  Conv& st = e.convs[0];
+  ENG_TRY(stem_fwd_launch(e.x0, e.params + st.off_w, st.raw, train ? st.sums_f : nullptr, st.coutp, n, e.S, e.S, s));
+  mark(e, s, "stem_fwd", 0);
+  if (train) ENG_TRY(bn_fin_f(e, st, (float)n * st.hout * st.hout, s));
+  for (auto& b : e.blocks) {
+    Conv& cd = e.convs[b.cd];
+    Conv& cp = e.convs[b.cp];
+    Conv* cin_raw = &st;
+    if (b.ce >= 0) {
+      Conv& ce = e.convs[b.ce];
+      ENG_TRY(pw_gemm_launch(train ? pl.fwd[b.ce] : pl.fwd_eval[b.ce], s));
+      mark(e, s, "pw_fwd_expand", b.ce);
+      if (train) ENG_TRY(bn_fin_f(e, ce, (float)n * ce.hout * ce.hout, s));
+      cin_raw = &ce;
+    }
+    ENG_TRY(dw_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w, cd.raw,
+                          train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, cd.stride, s));
+    mark(e, s, "dw_fwd", b.cd);
+    if (train) ENG_TRY(bn_fin_f(e, cd, (float)n * cd.hout * cd.hout, s));
+    ENG_TRY(pw_gemm_launch(train ? pl.fwd[b.cp] : pl.fwd_eval[b.cp], s));
+    mark(e, s, "pw_fwd_project", b.cp);
+    if (train) ENG_TRY(bn_fin_f(e, cp, (float)n * cp.hout * cp.hout, s));
+    const void* res = b.use_res ? e.blocks[b.index - 2].xout : nullptr;
+    ENG_TRY(affine_launch(cp.raw, res, cp.coef_f, 0, b.xout, (long long)n * b.hout * b.hout, cp.coutp, s));
+    mark(e, s, "block_out", b.cp);
+  }
+  const int li = (int)e.convs.size() - 1;
+  Conv& cl = e.convs[li];
+  ENG_TRY(pw_gemm_launch(train ? pl.fwd[li] : pl.fwd_eval[li], s));
+  mark(e, s, "pw_fwd_last", li);
+  if (train) ENG_TRY(bn_fin_f(e, cl, (float)n * cl.hout * cl.hout, s));
+  const int HW = cl.hout * cl.hout;
+  ENG_TRY(head_pool_launch(cl.raw, cl.coef_f, e.pooled, train ? e.drop : nullptr, n, HW, cl.coutp, train ? e.p_drop : 0.f,
+                           e.seed, e.step_dev, s));
+  ENG_TRY(head_fc_launch(e.pooled, e.params + e.off_fcw, e.params + e.off_fcb, e.logits, n, cl.coutp, e.classes, s));
+  ENG_TRY(b200dp_softmax_xent(e.logits, e.in_labels, nullptr, train ? e.dlogits : nullptr,
+                              train ? e.metrics_train : e.metrics_eval, n, e.classes, (float)n, s));
+  mark(e, s, "head_fwd");
+  return B200DP_OK;
+}
+
+__global__ void bump_step_kernel(int* step) { *step += 1; }
+
+int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
+  const int li = (int)e.convs.size() - 1;
+  Conv& cl = e.convs[li];
+  const int HW = cl.hout * cl.hout;
+  ENG_TRY(head_bwd_launch(e.dlogits, e.pooled, e.drop, e.params + e.off_fcw, e.dpool, e.grads + e.off_fcw,
+                          e.grads + e.off_fcb, cl.raw, cl.coef_f, e.dze, cl.sums_b, cl.coutp, n, HW, cl.coutp,
+                          e.classes, s));
+  mark(e, s, "head_bwd");
+  ENG_TRY(bn_fin_b(e, cl, (float)n * HW, s));
+  Block& lb = e.blocks.back();
+  const int Ml = n * HW;
+  ENG_TRY(pw_wgrad_launch(0, Ml, cl.coutp, cl.cinp, lb.xout, cl.cinp, e.dze, cl.raw, cl.coutp, cl.coef_b,
+                          e.grads + cl.off_w, cl.cinp, 0, s));
+  mark(e, s, "pw_wgrad_last", li);
+  int gxi = 0, doi = 0;
+  ENG_TRY(retarget_out(pl.dgrad[li], e.gx[gxi]));
+  ENG_TRY(pw_gemm_launch(pl.dgrad[li], s));
+  mark(e, s, "pw_dgrad_last", li);
+  const __nv_bfloat16* g1 = e.gx[gxi];         // gradient arriving from the consumer's data-gradient
+  const __nv_bfloat16* dnext = nullptr;        // dout of the next block (valid when that block has a residual)
+  bool next_res = false;
+  for (int bi = (int)e.blocks.size() - 1; bi >= 0; --bi) {
+    Block& b = e.blocks[bi];
+    Conv& cd = e.convs[b.cd];
+    Conv& cp = e.convs[b.cp];
+    const long long rows_out = (long long)n * b.hout * b.hout;
+    // ---- gradient w.r.t. this block's output: consumer dgrad (+ residual path of the next block)
+    const __nv_bfloat16* dcur = g1;
+    if (next_res) {
+      ENG_TRY(grad_join_stats_launch(g1, dnext, cp.raw, e.dout[doi], cp.sums_b, cp.coutp, rows_out, cp.coutp, s));
+      dcur = e.dout[doi];
+      doi ^= 1;
+    } else {
+      ENG_TRY(grad_join_stats_launch(g1, nullptr, cp.raw, nullptr, cp.sums_b, cp.coutp, rows_out, cp.coutp, s));
+    }
+    mark(e, s, "grad_join", b.cp);
+    ENG_TRY(bn_fin_b(e, cp, (float)rows_out, s));
+    ENG_TRY(affine_launch(dcur, cp.raw, cp.coef_b, 1, e.dp, rows_out, cp.coutp, s));
+    mark(e, s, "bn_bwd_apply", b.cp);
+    // ---- projection conv: weight gradient, then data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
+    ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, e.dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
+                            e.grads + cp.off_w, cp.cinp, 0, s));
+    mark(e, s, "pw_wgrad_project", b.cp);
+    ENG_TRY(pw_gemm_launch(pl.dgrad[b.cp], s));
+    mark(e, s, "pw_dgrad_project", b.cp);
+    ENG_TRY(bn_fin_b(e, cd, (float)rows_out, s));
+    // ---- depthwise conv backward (data + weight gradient, mask, statistics for the producer's BatchNorm)
+    Conv& cin_raw = b.ce >= 0 ? e.convs[b.ce] : e.convs[0];
+    ENG_TRY(dw_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
+                          e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                          cd.hin, cd.coutp, cd.stride, s));
+    mark(e, s, "dw_bwd", b.cd);
+    const long long rows_in = (long long)n * b.hin * b.hin;
+    ENG_TRY(bn_fin_b(e, cin_raw, (float)rows_in, s));
+    if (b.ce >= 0) {
+      Conv& ce = e.convs[b.ce];
+      const __nv_bfloat16* xin = e.blocks[bi - 1].xout;
+      ENG_TRY(pw_wgrad_launch(0, (int)rows_in, ce.coutp, ce.cinp, xin, ce.cinp, e.dze, ce.raw, ce.coutp, ce.coef_b,
+                              e.grads + ce.off_w, ce.cinp, 0, s));
+      mark(e, s, "pw_wgrad_expand", b.ce);
+      gxi ^= 1;
+      ENG_TRY(retarget_out(pl.dgrad[b.ce], e.gx[gxi]));
+      ENG_TRY(pw_gemm_launch(pl.dgrad[b.ce], s));
+      mark(e, s, "pw_dgrad_expand", b.ce);
+      g1 = e.gx[gxi];
+      dnext = dcur;
+      next_res = b.use_res;
+    } else {
+      Conv& st = e.convs[0];
+      ENG_TRY(stem_wgrad_launch(e.x0, e.dze, st.raw, st.coef_b, e.grads + st.off_w, n, e.S, e.S, s));
+      mark(e, s, "stem_wgrad", 0);
+    }
+  }
+  bump_step_kernel<<<1, 1, 0, s>>>(e.step_dev);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int stage_inputs(Engine& e, const uint8_t* images, const int64_t* labels, const float* aug, int n, cudaStream_t s) {
+  if (images != e.in_images)
+    B200DP_CUDA(cudaMemcpyAsync(e.in_images, images, (size_t)n * 3072, cudaMemcpyDeviceToDevice, s));
+  if (labels != e.in_labels)
+    B200DP_CUDA(cudaMemcpyAsync(e.in_labels, labels, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
+  if (aug != nullptr && aug != e.in_aug)
+    B200DP_CUDA(cudaMemcpyAsync(e.in_aug, aug, (size_t)n * B200DP_AUG_NPARAM * 4, cudaMemcpyDeviceToDevice, s));
+  return B200DP_OK;
+}
+
+int get_plans(Engine& e, int n, Plans** out) {
+  auto it = e.plans.find(n);
+  if (it == e.plans.end()) {
+    Plans pl;
+    ENG_TRY(build_plans(e, pl, n));
+    it = e.plans.emplace(n, std::move(pl)).first;
+  }
+  *out = &it->second;
+  return B200DP_OK;
+}
+
+}  // namespace
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" {
+
+int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, const long long* offsets, int n_offsets,
+                         long long param_total, long long buffer_total, float* params, float* grads, float* buffers,
+                         float dropout, float bn_eps, float bn_momentum, unsigned seed, int use_graphs) {
+  B200DP_REQUIRE(out && offsets && params && grads && buffers, "engine_create: null argument");
+  B200DP_REQUIRE(batch >= 1 && batch <= 1024 && img_size % 32 == 0 && img_size >= 32 && img_size <= 256,
+                 "engine_create: batch=%d img_size=%d unsupported", batch, img_size);
+  B200DP_REQUIRE(n_offsets == 52 * 5 + 2, "engine_create: offsets table has %d entries, expected %d", n_offsets, 52 * 5 + 2);
+  Engine* e = new Engine();
+  e->B = batch; e->S = img_size; e->classes = num_classes;
+  e->p_drop = dropout; e->eps = bn_eps; e->momentum = bn_momentum; e->seed = seed;
+  e->params = params; e->grads = grads; e->buffers = buffers;
+  e->param_total = param_total; e->buffer_total = buffer_total;
+  e->use_graphs = use_graphs != 0;
+  build_spec(*e, offsets);
+  e->ws_bytes = layout_workspace(*e, nullptr) + 1024;
+  cudaError_t err = cudaMalloc(&e->ws, e->ws_bytes);
+  if (err != cudaSuccess) {
+    set_error("engine_create: cudaMalloc(%zu MB) failed: %s", e->ws_bytes >> 20, cudaGetErrorString(err));
+    delete e;
+    return B200DP_ENOMEM;
+  }
+  B200DP_CUDA(cudaMemset(e->ws, 0, e->ws_bytes));
+  layout_workspace(*e, e->ws);
+  std::vector<WPrepEntry> table;
+  for (auto& c : e->convs)
+    if (c.kind == 2) table.push_back(WPrepEntry{c.off_w, c.coutp, c.cinp});
+  e->n_pw = (int)table.size();
+  B200DP_CUDA(cudaMemcpy(e->wprep_dev, table.data(), table.size() * sizeof(WPrepEntry), cudaMemcpyHostToDevice));
+  B200DP_CUDA(cudaStreamCreateWithFlags(&e->cap_stream, cudaStreamNonBlocking));
+  B200DP_CUDA(cudaDeviceSynchronize());
+  *out = e;
+  return B200DP_OK;
+}
+
+int b200dp_engine_destroy(void* h) {
+  Engine* e = static_cast<Engine*>(h);
+  if (!e) return B200DP_OK;
+  cudaDeviceSynchronize();
+  for (auto& kv : e->plans) {
+    if (kv.second.train_graph) cudaGraphExecDestroy(kv.second.train_graph);
+    if (kv.second.eval_graph) cudaGraphExecDestroy(kv.second.eval_graph);
+  }
+  if (e->cap_stream) cudaStreamDestroy(e->cap_stream);
+  if (e->ws) cudaFree(e->ws);
+  delete e;
+  return B200DP_OK;
+}
+
+size_t b200dp_engine_workspace_bytes(void* h) { return static_cast<Engine*>(h)->ws_bytes; }
+
+// Pointers into the engine's workspace: static input staging buffers, logits, metric accumulators
+// (double[3]: loss sum, correct, count).  which: 0 images u8, 1 labels i64, 2 aug params f32, 3 logits f32,
+// 4 train metrics f64, 5 eval metrics f64, 6 pre-processed input bf16 [B,S,S,4]
+void* b200dp_engine_buffer(void* h, int which) {
+  Engine* e = static_cast<Engine*>(h);
+  switch (which) {
+    case 0: return e->in_images;
+    case 1: return e->in_labels;
+    case 2: return e->in_aug;
+    case 3: return e->logits;
+    case 4: return e->metrics_train;
+    case 5: return e->metrics_eval;
+    case 6: return e->x0;
+    default: return nullptr;
+  }
+}
+
+// Activation / gradient taps for tests: raw conv output (what=0), forward coef (1), saved mean/invstd (2),
+// block output (3, index = block 0..16).
+void* b200dp_engine_tap(void* h, int what, int index) {
+  Engine* e = static_cast<Engine*>(h);
+  if (what == 3) return (index >= 0 && index < (int)e->blocks.size()) ? e->blocks[index].xout : nullptr;
+  if (index < 0 || index >= (int)e->convs.size()) return nullptr;
+  Conv& c = e->convs[index];
+  switch (what) {
+    case 0: return c.raw;
+    case 1: return c.coef_f;
+    case 2: return c.saved;
+    default: return nullptr;
+  }
+}
+
+// One training step: forward + loss + backward.  Gradients are ACCUMULATED into the grads arena given at create
+// time (it must be zero on entry -- the fused optimiser kernel zeroes it after consuming it).  `aug` may be null
+// (no augmentation).  Metrics accumulate into the train metric buffer.
+int b200dp_engine_train_step(void* h, const uint8_t* images, const int64_t* labels, const float* aug, int n,
+                             void* stream) {
+  Engine* e = static_cast<Engine*>(h);
+  B200DP_REQUIRE(e && n >= 1 && n <= e->B, "train_step: batch %d outside [1, %d]", n, e ? e->B : 0);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  ENG_TRY(stage_inputs(*e, images, labels, aug, n, s));
+  Plans* pl;
+  ENG_TRY(get_plans(*e, n, &pl));
+  e->eval_coef_valid = false;
+  const bool has_aug = aug != nullptr;
+  if (!e->use_graphs || e->profiling) {
+    ENG_TRY(forward(*e, *pl, n, true, has_aug, s));
+    return backward(*e, *pl, n, s);
+  }
+  cudaGraphExec_t& g = pl->train_graph;
+  if (g == nullptr || pl->train_aug != (int)has_aug) {
+    if (g) { cudaGraphExecDestroy(g); g = nullptr; }
+    cudaGraph_t graph;
+    cudaStream_t cs = e->cap_stream;
+    B200DP_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    int rc = forward(*e, *pl, n, true, has_aug, cs);
+    if (rc == B200DP_OK) rc = backward(*e, *pl, n, cs);
+    cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+    if (rc != B200DP_OK) { if (ce == cudaSuccess) cudaGraphDestroy(graph); return rc; }
+    B200DP_CUDA(ce);
+    B200DP_CUDA(cudaGraphInstantiate(&g, graph, 0));
+    cudaGraphDestroy(graph);
+    pl->train_aug = (int)has_aug;
+  }
+  B200DP_CUDA(cudaGraphLaunch(g, s));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return B200DP_OK;
+}
+
+// Evaluation step (running statistics, no dropout): logits stay in buffer 3, metrics accumulate into buffer 5.
+int b200dp_engine_eval_step(void* h, const uint8_t* images, const int64_t* labels, int n, void* stream) {
+  Engine* e = static_cast<Engine*>(h);
+  B200DP_REQUIRE(e && n >= 1 && n <= e->B, "eval_step: batch %d outside [1, %d]", n, e ? e->B : 0);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  ENG_TRY(stage_inputs(*e, images, labels, nullptr, n, s));
+  Plans* pl;
+  ENG_TRY(get_plans(*e, n, &pl));
+  if (!e->use_graphs || e->profiling || !e->eval_coef_valid) {
+    ENG_TRY(forward(*e, *pl, n, false, false, s));
+    e->eval_coef_valid = true;
+    return B200DP_OK;
+  }
+  cudaGraphExec_t& g = pl->eval_graph;
+  if (g == nullptr) {
+    cudaGraph_t graph;
+    cudaStream_t cs = e->cap_stream;
+    B200DP_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    int rc = forward(*e, *pl, n, false, false, cs);
+    cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+    if (rc != B200DP_OK) { if (ce == cudaSuccess) cudaGraphDestroy(graph); return rc; }
+    B200DP_CUDA(ce);
+    B200DP_CUDA(cudaGraphInstantiate(&g, graph, 0));
+    cudaGraphDestroy(graph);
+  }
+  B200DP_CUDA(cudaGraphLaunch(g, s));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return B200DP_OK;
+}
+
+// Tell the engine that parameters / running statistics were changed from outside (load_state_dict, broadcast).
+int b200dp_engine_invalidate(void* h) {
+  static_cast<Engine*>(h)->eval_coef_valid = false;
+  return B200DP_OK;
+}
+
+// Per-kernel timing of one un-graphed training step: fills `names` (newline separated) and `ms`.
+int b200dp_engine_profile_step(void* h, const uint8_t* images, const int64_t* labels, const float* aug, int n,
+                               char* names, int names_cap, float* ms, int ms_cap, int* count, void* stream) {
+  Engine* e = static_cast<Engine*>(h);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  e->profiling = true;
+  e->prof_events.clear();
+  mark(*e, s, "start");
+  int rc = b200dp_engine_train_step(h, images, labels, aug, n, stream);
+  mark(*e, s, "end");
+  e->profiling = false;
+  if (rc != B200DP_OK) return rc;
+  B200DP_CUDA(cudaStreamSynchronize(s));
+  std::string all;
+  int k = 0;
+  for (size_t i = 1; i < e->prof_events.size(); ++i) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, e->prof_events[i - 1].second, e->prof_events[i].second);
+    if (k < ms_cap) ms[k] = t;
+    all += e->prof_events[i].first + "\n";
+    ++k;
+  }
+  for (auto& pe : e->prof_events) cudaEventDestroy(pe.second);
+  e->prof_events.clear();
+  snprintf(names, names_cap, "%s", all.c_str());
+  *count = k < ms_cap ? k : ms_cap;
+  return B200DP_OK;
+}
+
+}  // extern "C"

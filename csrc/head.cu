@@ -113,7 +113,185 @@ softmax_topk_kernel(const float* __restrict__ logits, float* __restrict__ probs,
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------------
+// Fused classifier head for the native engine.
+//   pool:    pooled[b][c] = drop[b][c] * mean_pos relu6(scale[c]*raw[b][pos][c] + shift[c])
+//            (BatchNorm + ReLU6 of features.18 applied on load; dropout mask from a counter-based hash)
+//   fc:      logits[b][j] = pooled[b] . W[j] + bias[j]
+//   bwd_fc:  dpool[b][c] = drop[b][c]/HW * sum_j dlogits[b][j] W[j][c];  dW[j][c] += sum_b dlogits[b][j] pooled[b][c]
+//   bwd_mask: dz[b][pos][c] = dpool[b][c] * [0 < scale*raw+shift < 6]  (+ per-channel sum dz, sum dz*raw)
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+head_pool_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ coef, float* __restrict__ pooled,
+                 float* __restrict__ drop, int B, int HW, int C, float p_drop, uint32_t seed, const int* step) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (c >= C) return;
+  const float sc = coef[c], sh = coef[C + c];
+  const __nv_bfloat16* src = raw + (size_t)b * HW * C + c;
+  float acc = 0.f;
+  for (int p = 0; p < HW; ++p) acc += relu6f(fmaf(__bfloat162float(src[(size_t)p * C]), sc, sh));
+  acc /= (float)HW;
+  float keep = 1.f;
+  if (drop != nullptr) {
+    if (p_drop > 0.f) {
+      const uint32_t st = step != nullptr ? (uint32_t)(*step) : 0u;
+      const uint32_t h = hash32(hash32(seed ^ (st * 0x9e3779b9u)) ^ (uint32_t)(b * C + c));
+      keep = ((float)(h >> 8) * (1.f / 16777216.f)) >= p_drop ? 1.f / (1.f - p_drop) : 0.f;
+    }
+    drop[(size_t)b * C + c] = keep;
+  }
+  pooled[(size_t)b * C + c] = acc * keep;
+}
+
+__global__ void __launch_bounds__(512)
+head_fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w, const float* __restrict__ bias,
+               float* __restrict__ logits, int C, int classes) {
+  const int b = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int j = warp; j < classes; j += blockDim.x >> 5) {
+    float acc = 0.f;
+    for (int c = lane; c < C; c += 32) acc = fmaf(pooled[(size_t)b * C + c], w[(size_t)j * C + c], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) logits[(size_t)b * classes + j] = acc + bias[j];
+  }
+}
+
+constexpr int HEAD_MAX_CLASSES = 16;
+
+__global__ void __launch_bounds__(128)
+head_bwd_fc_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, const float* __restrict__ drop,
+                   const float* __restrict__ w, float* __restrict__ dpool, float* __restrict__ dw,
+                   float* __restrict__ dbias, int B, int HW, int C, int classes) {
+  extern __shared__ float s_dl[];    // [B][classes]
+  for (int i = threadIdx.x; i < B * classes; i += blockDim.x) s_dl[i] = dlogits[i];
+  __syncthreads();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) {
+    float wc[HEAD_MAX_CLASSES], gw[HEAD_MAX_CLASSES];
+#pragma unroll
+    for (int j = 0; j < HEAD_MAX_CLASSES; ++j) { wc[j] = j < classes ? w[(size_t)j * C + c] : 0.f; gw[j] = 0.f; }
+    const float inv = 1.f / (float)HW;
+    for (int b = 0; b < B; ++b) {
+      const float pv = pooled[(size_t)b * C + c];
+      float dp = 0.f;
+#pragma unroll
+      for (int j = 0; j < HEAD_MAX_CLASSES; ++j) {
+        if (j < classes) {
+          const float d = s_dl[b * classes + j];
+          dp = fmaf(d, wc[j], dp);
+          gw[j] = fmaf(d, pv, gw[j]);
+        }
+      }
+      dpool[(size_t)b * C + c] = dp * drop[(size_t)b * C + c] * inv;
+    }
+#pragma unroll
+    for (int j = 0; j < HEAD_MAX_CLASSES; ++j)
+      if (j < classes) dw[(size_t)j * C + c] += gw[j];
+  }
+  if (blockIdx.x == 0 && threadIdx.x < classes) {
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += s_dl[b * classes + threadIdx.x];
+    dbias[threadIdx.x] += s;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+head_bwd_mask_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ coef,
+                     const float* __restrict__ dpool, __nv_bfloat16* __restrict__ dz, float* __restrict__ sums,
+                     int stride, int B, int HW, int C) {
+  extern __shared__ float s_red[];   // [2][C]
+  const int CG = C >> 3;
+  const int ipb = blockDim.x / CG;
+  const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+  if (ti < ipb) {
+    float sc[8], sh[8], s0[8], s1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { sc[j] = coef[cg * 8 + j]; sh[j] = coef[C + cg * 8 + j]; s0[j] = s1[j] = 0.f; }
+    const long long rows = (long long)B * HW;
+    for (long long r = (long long)blockIdx.x * ipb + ti; r < rows; r += (long long)gridDim.x * ipb) {
+      const int b = (int)(r / HW);
+      const uint4 v = ldg_stream(raw + r * C + cg * 8);
+      const float x[8] = {bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y),
+                          bf16_lo(v.z), bf16_hi(v.z), bf16_lo(v.w), bf16_hi(v.w)};
+      const float4 d0 = *reinterpret_cast<const float4*>(dpool + (size_t)b * C + cg * 8);
+      const float4 d1 = *reinterpret_cast<const float4*>(dpool + (size_t)b * C + cg * 8 + 4);
+      const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float z = fmaf(x[j], sc[j], sh[j]);
+        o[j] = (z > 0.f && z < 6.f) ? d[j] : 0.f;
+      }
+      const uint4 pk = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                                  pack_bf16x2(o[6], o[7]));
+      stg_stream(dz + r * C + cg * 8, pk);
+      const float q[8] = {bf16_lo(pk.x), bf16_hi(pk.x), bf16_lo(pk.y), bf16_hi(pk.y),
+                          bf16_lo(pk.z), bf16_hi(pk.z), bf16_lo(pk.w), bf16_hi(pk.w)};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s0[j] += q[j]; s1[j] = fmaf(q[j], x[j], s1[j]); }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&s_red[cg * 8 + j], s0[j]);
+      atomicAdd(&s_red[C + cg * 8 + j], s1[j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(sums + i, s_red[i]);
+    atomicAdd(sums + stride + i, s_red[C + i]);
+  }
+}
+
 }  // namespace
+
+int head_pool_launch(const void* raw, const float* coef, float* pooled, float* drop, int B, int HW, int C,
+                     float p_drop, uint32_t seed, const int* step, cudaStream_t s) {
+  dim3 grid((C + 255) / 256, B);
+  head_pool_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(raw), coef, pooled, drop, B, HW, C, p_drop,
+                                        seed, step);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int head_fc_launch(const float* pooled, const float* w, const float* bias, float* logits, int B, int C, int classes,
+                   cudaStream_t s) {
+  head_fc_kernel<<<B, 32 * (classes < 16 ? classes : 16), 0, s>>>(pooled, w, bias, logits, C, classes);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int head_bwd_launch(const float* dlogits, const float* pooled, const float* drop, const float* w, float* dpool,
+                    float* dw, float* dbias, const void* raw, const float* coef, void* dz, float* sums, int stride,
+                    int B, int HW, int C, int classes, cudaStream_t s) {
+  B200DP_REQUIRE(classes <= HEAD_MAX_CLASSES, "head: at most %d classes", HEAD_MAX_CLASSES);
+  B200DP_REQUIRE((size_t)B * classes * 4 <= 48 * 1024, "head: batch too large for the shared dlogits tile");
+  head_bwd_fc_kernel<<<(C + 127) / 128, 128, (size_t)B * classes * sizeof(float), s>>>(dlogits, pooled, drop, w, dpool,
+                                                                                       dw, dbias, B, HW, C, classes);
+  B200DP_CHECK_LAUNCH();
+  const int CG = C / 8;
+  B200DP_REQUIRE(C % 8 == 0 && CG <= 256, "head: C=%d unsupported", C);
+  const int threads = (256 / CG) * CG;
+  const int ipb = threads / CG;
+  const long long rows = (long long)B * HW;
+  long long blocks = (rows + ipb - 1) / ipb;
+  const long long cap = (long long)num_sms() * 4;
+  if (blocks > cap) blocks = cap;
+  head_bwd_mask_kernel<<<(int)blocks, threads, 2 * C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(raw), coef,
+                                                                          dpool, static_cast<__nv_bfloat16*>(dz), sums,
+                                                                          stride, B, HW, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
 }  // namespace b200dp
 
 using namespace b200dp;

@@ -382,7 +382,9 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 template <int AMODE, int EMODE>
 int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
   auto kern = pw_gemm_kernel<AMODE, EMODE>;
-  B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes));
+  // always the architectural maximum: the attribute is function-global state, and CUDA-graph replays must not
+  // depend on which layer set it last
+  B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   kern<<<pl.grid, AMODE == A_TMA ? 256 : 512, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmO, pl.p);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;

@@ -37,4 +37,8 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
                  const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas);
 int pw_gemm_launch(const PwGemmPlan& pl, cudaStream_t s);
 
+// 2-D bf16 row-major tensor map [rows][cols] (row pitch `ld` elements), box {box_cols, box_rows}, 128-byte swizzle.
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_cols, uint32_t box_rows);
+
 }  // namespace b200dp

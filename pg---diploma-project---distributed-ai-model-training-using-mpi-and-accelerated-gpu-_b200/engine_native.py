@@ -1,7 +1,270 @@
 """Native engine: the whole train / eval step runs in hand-written sm_100a kernels driven by the
-C++ executor (csrc/engine.cpp).  Placeholder until the executor lands; ``available()`` gates it."""
+C++ executor (csrc/engine.cu), and gradient sync + Adam is the fused peer-memory kernel.
+
+What the reference does per step (cifar10_mpi_mobilenet_224.py:173-184) and what happens here:
+
+* ``imgs.to(device)`` 77 MB fp32                   -> 393 KB of uint8 (+labels, +12 floats/sample)
+* ``zero_grad``                                    -> fused into the optimiser kernel
+* ``ddp_model(imgs)`` (~160 cuDNN/ATen kernels)    -> ``b200dp_engine_train_step`` (one CUDA-graph launch:
+  ``criterion`` / ``backward`` (~500 kernels)         preprocess, stem, tcgen05 pointwise GEMMs, depthwise
+                                                      stencils, head, and the mirror-image backward)
+* DDP bucket all-reduce + ``optimizer.step``       -> ``FusedAllReduceAdam.step`` (one kernel)
+* ``loss.item()`` / ``.sum().item()``              -> device-side double accumulators, read once per epoch
+
+Parameters live in one flat fp32 arena (``models/arena.py``); ``state_dict`` / ``load_state_dict``
+convert to / from the torchvision layout so checkpoints interchange with the reference.
+"""
 from __future__ import annotations
+
+import ctypes as C
+from collections import OrderedDict
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from .models.arena import ArenaLayout
+from .models.mobilenetv2 import build_model
+from .models.spec import BN_EPS, BN_MOMENTUM, build_spec
+from .ops import _lib
+from .ops._lib import check
+from .optim import AdamHyper
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, i, ll = C.c_void_p, C.c_int, C.c_longlong
+    lib.b200dp_engine_create.argtypes = [C.POINTER(vp), i, i, i, C.POINTER(ll), i, ll, ll, vp, vp, vp,
+                                         C.c_float, C.c_float, C.c_float, C.c_uint, i]
+    lib.b200dp_engine_create.restype = i
+    lib.b200dp_engine_destroy.argtypes = [vp]
+    lib.b200dp_engine_destroy.restype = i
+    lib.b200dp_engine_workspace_bytes.argtypes = [vp]
+    lib.b200dp_engine_workspace_bytes.restype = C.c_size_t
+    lib.b200dp_engine_buffer.argtypes = [vp, i]
+    lib.b200dp_engine_buffer.restype = vp
+    lib.b200dp_engine_tap.argtypes = [vp, i, i]
+    lib.b200dp_engine_tap.restype = vp
+    lib.b200dp_engine_train_step.argtypes = [vp, vp, vp, vp, i, vp]
+    lib.b200dp_engine_train_step.restype = i
+    lib.b200dp_engine_eval_step.argtypes = [vp, vp, vp, i, vp]
+    lib.b200dp_engine_eval_step.restype = i
+    lib.b200dp_engine_invalidate.argtypes = [vp]
+    lib.b200dp_engine_invalidate.restype = i
+    lib.b200dp_engine_profile_step.argtypes = [vp, vp, vp, vp, i, C.c_char_p, i, C.POINTER(C.c_float), i,
+                                               C.POINTER(i), vp]
+    lib.b200dp_engine_profile_step.restype = i
+
+
+_lib.register_decls(_declare)
 
 
 def available() -> bool:
-    return False
+    if not torch.cuda.is_available():
+        return False
+    lib = _lib.load()
+    return lib is not None and hasattr(lib, "b200dp_engine_create")
+
+
+class _DevView:
+    """torch view of raw device memory owned by the native engine."""
+
+    def __init__(self, owner, ptr: int, numel: int, typestr: str) -> None:
+        self._owner = owner
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+class NativeCore:
+    """Owns the parameter / buffer arenas and the C++ executor; shared by training and inference."""
+
+    def __init__(self, device: torch.device, batch: int, img_size: int, num_classes: int, dropout: float,
+                 seed: int, grads: Optional[torch.Tensor] = None, use_graphs: bool = True) -> None:
+        self.lib = _lib.require()
+        self.device = device
+        self.batch = batch
+        self.layout = ArenaLayout(build_spec(img_size, num_classes))
+        L = self.layout
+        self.params = torch.zeros(L.total, dtype=torch.float32, device=device)
+        self.buffers = torch.zeros(L.buffer_total, dtype=torch.float32, device=device)
+        self.grads = grads if grads is not None else torch.zeros(L.total, dtype=torch.float32, device=device)
+        self.num_batches_tracked = 0
+        table = L.offsets_table()
+        arr = (C.c_longlong * len(table))(*table)
+        h = C.c_void_p()
+        check(self.lib.b200dp_engine_create(C.byref(h), batch, img_size, num_classes, arr, len(table), L.total,
+                                            L.buffer_total, self.params.data_ptr(), self.grads.data_ptr(),
+                                            self.buffers.data_ptr(), dropout, BN_EPS, BN_MOMENTUM, seed & 0xFFFFFFFF,
+                                            1 if use_graphs else 0))
+        self.h = h
+        self.num_classes = num_classes
+        self.metrics_train = self._view(4, 3, "<f8")
+        self.metrics_eval = self._view(5, 3, "<f8")
+        self.logits = self._view(3, batch * num_classes, "<f4").view(batch, num_classes)
+
+    def _view(self, which: int, numel: int, typestr: str) -> torch.Tensor:
+        p = self.lib.b200dp_engine_buffer(self.h, which)
+        return torch.as_tensor(_DevView(self, int(p), numel, typestr), device=self.device)
+
+    def tap(self, what: int, index: int, numel: int, typestr: str = "<u2") -> torch.Tensor:
+        p = self.lib.b200dp_engine_tap(self.h, what, index)
+        t = torch.as_tensor(_DevView(self, int(p), numel, typestr), device=self.device)
+        return t.view(torch.bfloat16) if typestr == "<u2" else t
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        p, b, nbt = self.layout.import_state_dict(sd)
+        self.params.copy_(p)
+        self.buffers.copy_(b)
+        self.num_batches_tracked = nbt
+        self.lib.b200dp_engine_invalidate(self.h)
+
+    def state_dict(self) -> "OrderedDict[str, torch.Tensor]":
+        return self.layout.export_state_dict(self.params, self.buffers, self.num_batches_tracked)
+
+    def train_step(self, images: torch.Tensor, labels: torch.Tensor, aug: Optional[torch.Tensor], n: int) -> None:
+        check(self.lib.b200dp_engine_train_step(self.h, images.data_ptr(), labels.data_ptr(),
+                                                aug.data_ptr() if aug is not None else None, n,
+                                                _lib.current_stream()))
+        self.num_batches_tracked += 1
+
+    def eval_step(self, images: torch.Tensor, labels: torch.Tensor, n: int) -> None:
+        check(self.lib.b200dp_engine_eval_step(self.h, images.data_ptr(), labels.data_ptr(), n, _lib.current_stream()))
+
+    def profile_step(self, images, labels, aug, n) -> List[Tuple[str, float]]:
+        names = C.create_string_buffer(1 << 16)
+        ms = (C.c_float * 1024)()
+        cnt = C.c_int()
+        check(self.lib.b200dp_engine_profile_step(self.h, images.data_ptr(), labels.data_ptr(),
+                                                  aug.data_ptr() if aug is not None else None, n, names, 1 << 16,
+                                                  ms, 1024, C.byref(cnt), _lib.current_stream()))
+        labels_ = names.value.decode().strip().split("\n")
+        return list(zip(labels_, [ms[i] for i in range(cnt.value)]))
+
+    def close(self) -> None:
+        if self.h:
+            self.lib.b200dp_engine_destroy(self.h)
+            self.h = None
+
+
+class NativeEngine:
+    name = "native"
+
+    def __init__(self, cfg, ctx) -> None:
+        from .parallel.comm import FusedAllReduceAdam
+        self.cfg, self.ctx = cfg, ctx
+        self.device = ctx.device
+        torch.manual_seed(cfg.seed)
+        layout = ArenaLayout(build_spec(cfg.img_size, cfg.num_classes))
+        hyper = AdamHyper(cfg.lr, cfg.beta1, cfg.beta2, cfg.eps, cfg.weight_decay)
+        self.nccl = cfg.comm == "nccl"
+        # gradients live in the peer-mapped comm arena; the executor accumulates straight into it
+        self.fused = FusedAllReduceAdam(ctx, layout.total, hyper)
+        self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
+                               cfg.seed + 7919 * ctx.rank, grads=self.fused.grads)
+        # the fused kernel updates the executor's master weights in place
+        self.fused.params = self.core.params
+        self.fused.args.params[ctx.rank] = self.core.params.data_ptr()
+        init = build_model(cfg.num_classes, cfg.dropout, cfg.img_size, cfg.pretrained)
+        self.core.load_state_dict(init.state_dict())
+        del init
+        self.broadcast_parameters()
+        self.steps = 0
+        if self.nccl:
+            from .optim import FlatAdam
+            self.adam = FlatAdam(layout.total, self.device, hyper)
+
+    # ---- replica consistency ---------------------------------------------------------------------
+    def broadcast_parameters(self) -> None:
+        import torch.distributed as dist
+        if self.ctx.initialized:
+            dist.broadcast(self.core.params, src=0)     # K-C3: DDP's constructor broadcast
+            self.sync_buffers()
+
+    def sync_buffers(self) -> None:
+        import torch.distributed as dist
+        if self.ctx.initialized:
+            dist.broadcast(self.core.buffers, src=0)    # K-C4: rank 0's running statistics are authoritative
+            self.core.lib.b200dp_engine_invalidate(self.core.h)
+
+    # ---- steps -------------------------------------------------------------------------------------
+    def train_step(self, batch, lr: float) -> None:
+        batch.wait()
+        aug = batch.params if self.cfg.augment else None
+        self.core.train_step(batch.images, batch.labels, aug, batch.n)
+        if self.nccl:     # comparison baseline: NCCL all-reduce + separate Adam
+            import torch.distributed as dist
+            if self.ctx.initialized:
+                dist.all_reduce(self.core.grads)
+            self.adam.step_torch(self.core.params, self.core.grads, lr, grad_scale=1.0 / self.ctx.world_size)
+            self.core.grads.zero_()
+        else:
+            self.fused.step(lr)
+        self.steps += 1
+
+    def eval_step(self, batch) -> None:
+        batch.wait()
+        self.core.eval_step(batch.images, batch.labels, batch.n)
+
+    @torch.no_grad()
+    def predict_logits(self, images_u8: torch.Tensor) -> torch.Tensor:
+        n = images_u8.shape[0]
+        labels = torch.zeros(n, dtype=torch.int64, device=self.device)
+        keep = self.core.metrics_eval.clone()
+        self.core.eval_step(images_u8.to(self.device).contiguous(), labels, n)
+        out = self.core.logits[:n].clone()
+        self.core.metrics_eval.copy_(keep)
+        return out
+
+    # ---- metrics / state -------------------------------------------------------------------------
+    def read_metrics(self, reset: bool = True) -> Tuple[float, float, float]:
+        m = (self.core.metrics_train + self.core.metrics_eval).tolist()
+        if reset:
+            self.core.metrics_train.zero_()
+            self.core.metrics_eval.zero_()
+        return m[0], m[1], m[2]
+
+    def state_dict(self):
+        return self.core.state_dict()
+
+    def load_state_dict(self, sd) -> None:
+        self.core.load_state_dict(sd)
+
+    def optimizer_state(self):
+        return self.adam.state_dict() if self.nccl else self.fused.state_dict()
+
+    def load_optimizer_state(self, sd) -> None:
+        (self.adam if self.nccl else self.fused).load_state_dict(sd)
+
+    def parameter_count(self) -> int:
+        return int(self.core.layout.trainable_mask().sum().item())
+
+    def param_hash(self) -> float:
+        return float(self.core.params.double().sum().item())
+
+    def close(self) -> None:
+        torch.cuda.synchronize()
+        self.fused.close()
+        self.core.close()
+
+
+class NativeInference:
+    """Eval-mode forward on the native kernels (BatchNorm folded into scale/shift on load)."""
+
+    def __init__(self, num_classes: int, device: torch.device, state_dict: Optional[dict], batch: int = 256) -> None:
+        if not available():
+            raise RuntimeError("native engine unavailable")
+        self.device = device
+        self.core = NativeCore(device, batch, 224, num_classes, 0.0, 0)
+        if state_dict is None:
+            state_dict = build_model(num_classes).state_dict()
+        self.core.load_state_dict(state_dict)
+        self.batch = batch
+
+    @torch.no_grad()
+    def logits(self, images_u8: torch.Tensor) -> torch.Tensor:
+        outs = []
+        for s in range(0, images_u8.shape[0], self.batch):
+            chunk = images_u8[s: s + self.batch].contiguous()
+            n = chunk.shape[0]
+            labels = torch.zeros(n, dtype=torch.int64, device=self.device)
+            self.core.eval_step(chunk, labels, n)
+            outs.append(self.core.logits[:n].clone())
+        return torch.cat(outs)

@@ -140,3 +140,62 @@ def pw_gemm(w: torch.Tensor, *, a: Optional[torch.Tensor] = None, a_raw: Optiona
                              ptr(w), ptr(out), N, ptr(aux), ptr(ecoef), ptr(stats), N, max_ctas,
                              current_stream()))
     return out
+
+
+def pw_wgrad(dw: torch.Tensor, *, a: Optional[torch.Tensor] = None, dz: Optional[torch.Tensor] = None,
+             y_raw: Optional[torch.Tensor] = None, g: Optional[torch.Tensor] = None,
+             a_raw: Optional[torch.Tensor] = None, coef: torch.Tensor = None, max_ctas: int = 0) -> torch.Tensor:
+    """``dw[N,K] += G^T @ A`` on tcgen05 with MN-major operands (csrc/pw_wgrad.cu).
+    mode 0: ``a`` pure [M,K], G = coef[0]*dz + coef[1]*y_raw + coef[2] ([M,N]);
+    mode 1: ``g`` pure [M,N], A = relu6(coef[0]*a_raw + coef[1]) ([M,K])."""
+    lib = _lib.require()
+    _chk(dw, torch.float32, "dw")
+    N, K = dw.shape
+    if a is not None:
+        mode, pure, t0, t1, ldp, ldt = 0, _chk(a, torch.bfloat16, "a"), _chk(dz, torch.bfloat16, "dz"), \
+            _chk(y_raw, torch.bfloat16, "y_raw"), K, N
+    else:
+        mode, pure, t0, t1, ldp, ldt = 1, _chk(g, torch.bfloat16, "g"), _chk(a_raw, torch.bfloat16, "a_raw"), None, N, K
+    M = pure.shape[0]
+    _chk(coef, torch.float32, "coef")
+    check(lib.b200dp_pw_wgrad(mode, M, N, K, ptr(pure), ldp, ptr(t0), ptr(t1), ldt, ptr(coef), ptr(dw), K, max_ctas,
+                              current_stream()))
+    return dw
+
+
+def dw_fwd(x: torch.Tensor, coef: torch.Tensor, w: torch.Tensor, stride: int,
+           stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Depthwise 3x3 on NHWC bf16 ``x`` [B,H,W,C] with relu6(coef[0]*x+coef[1]) applied on load; ``w`` fp32 [9,C]."""
+    lib = _lib.require()
+    _chk(x, torch.bfloat16, "x"); _chk(coef, torch.float32, "coef"); _chk(w, torch.float32, "w")
+    B, H, W, Cn = x.shape
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    y = torch.empty((B, Ho, Wo, Cn), dtype=torch.bfloat16, device=x.device)
+    check(lib.b200dp_dw_fwd(ptr(x), ptr(coef), coef.data_ptr() + 4 * Cn, ptr(w), ptr(y), ptr(stats), Cn, B, H, W, Cn,
+                            stride, current_stream()))
+    return y
+
+
+def dw_bwd(e_raw: torch.Tensor, ecoef: torch.Tensor, dzd: torch.Tensor, d_raw: torch.Tensor, dcoef: torch.Tensor,
+           w: torch.Tensor, stride: int, stats: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
+    lib = _lib.require()
+    B, H, W, Cn = e_raw.shape
+    dze = torch.empty_like(e_raw)
+    check(lib.b200dp_dw_bwd(ptr(e_raw), ptr(ecoef), ecoef.data_ptr() + 4 * Cn, ptr(dzd), ptr(d_raw), ptr(dcoef), ptr(w),
+                            ptr(dze), ptr(stats), Cn, ptr(dw), B, H, W, Cn, stride, current_stream()))
+    return dze
+
+
+def stem_fwd(x4: torch.Tensor, w: torch.Tensor, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+    lib = _lib.require()
+    B, H, W, _ = x4.shape
+    y = torch.empty((B, (H - 1) // 2 + 1, (W - 1) // 2 + 1, 32), dtype=torch.bfloat16, device=x4.device)
+    check(lib.b200dp_stem_fwd(ptr(x4), ptr(w), ptr(y), ptr(stats), 32, B, H, W, current_stream()))
+    return y
+
+
+def stem_wgrad(x4: torch.Tensor, dz: torch.Tensor, yraw: torch.Tensor, coef: torch.Tensor, dw: torch.Tensor):
+    lib = _lib.require()
+    B, H, W, _ = x4.shape
+    check(lib.b200dp_stem_wgrad(ptr(x4), ptr(dz), ptr(yraw), ptr(coef), ptr(dw), B, H, W, current_stream()))
+    return dw

@@ -60,6 +60,15 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_softmax_xent": [vp, vp, vp, vp, vp, i, i, f, vp],
         "b200dp_softmax_topk": [vp, vp, vp, vp, i, i, i, vp],
         "b200dp_pw_gemm": [i, i, i, i, i, vp, i, vp, vp, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
+        "b200dp_pw_wgrad": [i, i, i, i, vp, i, vp, vp, i, vp, vp, i, i, vp],
+        "b200dp_dw_fwd": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
+        "b200dp_dw_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, i, i, i, i, i, vp],
+        "b200dp_stem_fwd": [vp, vp, vp, vp, i, i, i, i, vp],
+        "b200dp_stem_wgrad": [vp, vp, vp, vp, vp, i, i, i, vp],
+        "b200dp_bn_fwd_finalize": [vp, i, vp, vp, f, f, f, vp, vp, vp, vp, i, vp],
+        "b200dp_bn_bwd_finalize": [vp, i, vp, vp, f, vp, vp, vp, i, vp],
+        "b200dp_affine": [vp, vp, vp, i, vp, ll, i, vp],
+        "b200dp_grad_join_stats": [vp, vp, vp, vp, vp, i, ll, i, vp],
     }
     for name, args in sigs.items():
         fn = getattr(lib, name)
@@ -87,6 +96,13 @@ def load() -> Optional[C.CDLL]:
 
 
 _EXTRA_DECLS = []   # other binding modules register their own declarations here
+
+
+def register_decls(fn) -> None:
+    """Register extra ctypes declarations; applied now if the library is already loaded."""
+    _EXTRA_DECLS.append(fn)
+    if _lib is not None:
+        fn(_lib)
 
 
 def load_error() -> Optional[str]:
