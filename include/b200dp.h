@@ -130,6 +130,52 @@ int b200dp_softmax_xent(const float* logits, const int64_t* labels, float* loss_
 int b200dp_softmax_topk(const float* logits, float* probs_out, float* topv_out, int32_t* topi_out,
                         int batch, int classes, int k, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Convolution building blocks of the native engine (stand-alone entry points; the executor in
+ * csrc/engine.cu drives the same kernels).  All activations are NHWC bf16, channels % 16 == 0.
+ *   reference: torchvision MobileNetV2 ConvBNReLU / InvertedResidual forward + autograd backward,
+ *   i.e. cuDNN conv + cuDNN batch-norm + ATen hardtanh (cifar10_mpi_mobilenet_224.py:177, :179)
+ * ------------------------------------------------------------------------------------------- */
+/* Pointwise conv as a tcgen05 GEMM, out[M,N] = Aeff[M,K] * w[N,K]^T (csrc/pw_gemm.cu).
+ * amode 0: a_tma is the bf16 A matrix; 1: Aeff = relu6?(acoef[0]*a0 + acoef[1]); 2: Aeff = acoef[0]*a0 + acoef[1]*a1 + acoef[2].
+ * emode 0: store; 1: store + stats[0] += sum(out), stats[1] += sum(out^2); 2: out masked by ReLU6'(ecoef[0]*aux+ecoef[1]),
+ * stats[0] += sum(out), stats[1] += sum(out*aux).  `stats` is [2][stats_stride] fp32 and is ACCUMULATED into. */
+int b200dp_pw_gemm(int amode, int emode, int M, int N, int K, const void* a_tma, int lda, const void* a0,
+                   const void* a1, const float* acoef, int a_relu6, const void* w, void* out, int ldo,
+                   const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas,
+                   void* stream);
+/* Pointwise conv weight gradient dw[N][ldw] += G^T A on tcgen05 with MN-major operands (csrc/pw_wgrad.cu).
+ * mode 0: `pure` = A [M,K]; G = coef[0]*t0 + coef[1]*t1 + coef[2].  mode 1: `pure` = G [M,N]; A = relu6(coef[0]*t0 + coef[1]). */
+int b200dp_pw_wgrad(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
+                    int ld_t, const float* coef, float* dw, int ldw, int max_ctas, void* stream);
+/* Depthwise 3x3 (pad 1, stride 1|2): y = dwconv(relu6(scale*x + shift)), w fp32 [9][C];
+ * stats (may be NULL) [2][stats_stride] += sum(y), sum(y^2): a scratch accumulator that must be zero on entry. */
+int b200dp_dw_fwd(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
+                  int stats_stride, int B, int H, int W, int C, int stride, void* stream);
+/* Depthwise backward: data gradient (masked by ReLU6' of the input activation), weight gradient and the sums the
+ * producer's BatchNorm backward needs, in one pass (csrc/dwconv.cu). */
+int b200dp_dw_bwd(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
+                  const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
+                  int H, int W, int C, int stride, void* stream);
+/* Stem 3x3 stride-2 conv 3->32 on a 4-channel bf16 image, and its weight gradient (csrc/stem.cu). */
+int b200dp_stem_fwd(const void* x, const float* w, void* y, float* stats, int stats_stride, int B, int H, int W,
+                    void* stream);
+int b200dp_stem_wgrad(const void* x, const void* dz, const void* yraw, const float* coef, float* dw, int B, int H,
+                      int W, void* stream);
+/* BatchNorm finalisation: sums -> (scale, shift), (mean, invstd), running statistics (rmean/rvar may be NULL);
+ * and sums of (dz, dz*x) -> (ca, cb, cc) with dx = ca*dz + cb*x + cc, plus dgamma / dbeta (accumulated). */
+int b200dp_bn_fwd_finalize(const float* sums, int stride, const float* gamma, const float* beta, float count,
+                           float eps, float momentum, float* rmean, float* rvar, float* coef, float* saved, int C,
+                           void* stream);
+int b200dp_bn_bwd_finalize(const float* sums, int stride, const float* saved, const float* gamma, float count,
+                           float* coef3, float* dgamma, float* dbeta, int C, void* stream);
+/* Passes over the narrow block outputs: out = c0*a + c1 (+ b), or (three) c0*a + c1*b + c2; and the gradient
+ * join dout = g1 (+ g2) with the two per-channel sums of the projection BatchNorm backward. */
+int b200dp_affine(const void* a, const void* b, const float* coef, int three, void* out, long long rows, int C,
+                  void* stream);
+int b200dp_grad_join_stats(const void* g1, const void* g2, const void* x, void* dout, float* sums, int stride,
+                           long long rows, int C, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
