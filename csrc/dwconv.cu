@@ -392,3 +392,73 @@ extern "C" int b200dp_dw_bwd(const void* e_raw, const float* escale, const float
   return dw_bwd_launch(e_raw, escale, eshift, dzd, d_raw, dcoef, w, dze, stats, stats_stride, dw, B, H, W, C, stride,
                        static_cast<cudaStream_t>(stream));
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free variant: depthwise conv + the BatchNorm coefficients of its output, in one call.
+//
+// b200dp_dw_fwd accumulates the per-channel sums of its output into a buffer the caller owns, and the
+// caller then runs b200dp_bn_fwd_finalize on it.  That buffer is pure scratch: nobody wants the sums, only
+// the scale / shift they turn into.  Some callers cannot provide it, because they are not allowed to
+// allocate device memory where they sit: a plug-in running inside another runtime's enqueue hook, a serving
+// loop whose memory pool is sized up front, a latency-critical path that must never enter the allocator, or
+// a process that has handed all free memory to a framework allocator.  For them
+// the scratch lives in the library image itself: a file-scope __device__ array, 8 KB on every GPU that loads
+// this library, held until the process exits.
+//
+// Rules that follow from the scratch being shared and static:
+//   * at most B200DP_DW_NOALLOC_MAX_C channels; larger C is rejected with B200DP_EINVAL;
+//   * the sums must start at zero, so every call clears the part it uses first (a memset node on `stream`);
+//   * all calls share the one array per GPU: two calls that can overlap on the device (different streams,
+//     no dependency between them) race on it and give wrong coefficients -- serialise them;
+//   * the array's name is only a host-side handle.  Its device address is looked up once per device with
+//     cudaGetSymbolAddress while that device is current.  The first call on a device does this look-up, so
+//     make that first call outside any stream capture.
+// No cudaMalloc / cudaFree / allocating library routine is called here or below.
+namespace b200dp {
+namespace {
+
+constexpr int kMaxDevices = 64;
+static __device__ __align__(256) float g_dw_noalloc_sums[2 * B200DP_DW_NOALLOC_MAX_C];
+float* g_dw_noalloc_ptr[kMaxDevices] = {nullptr};
+
+int dw_noalloc_scratch(float** out) {
+  int dev = -1;
+  B200DP_CUDA(cudaGetDevice(&dev));
+  B200DP_REQUIRE(dev >= 0 && dev < kMaxDevices, "dw_fwd_bn_noalloc: device ordinal %d unsupported", dev);
+  if (g_dw_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    B200DP_CUDA(cudaGetSymbolAddress(&p, g_dw_noalloc_sums));   // device address of the symbol ON THIS DEVICE
+    B200DP_REQUIRE(p != nullptr, "dw_fwd_bn_noalloc: cudaGetSymbolAddress returned a null address");
+    g_dw_noalloc_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_dw_noalloc_ptr[dev];
+  return B200DP_OK;
+}
+
+}  // namespace
+
+int bn_fwd_finalize_launch(const float* sums, int stride, const float* gamma, const float* beta, float count,
+                           float eps, float momentum, float* rmean, float* rvar, float* coef, float* saved, int C,
+                           cudaStream_t s);
+
+}  // namespace b200dp
+
+extern "C" int b200dp_dw_fwd_bn_noalloc(const void* x, const float* in_scale, const float* in_shift, const float* w,
+                                        const float* gamma, const float* beta, float eps, void* y, float* coef_out,
+                                        float* saved_out, int B, int H, int W, int C, int stride, void* stream) {
+  B200DP_REQUIRE(x && in_scale && in_shift && w && gamma && beta && y && coef_out && saved_out,
+                 "dw_fwd_bn_noalloc: null pointer argument");
+  B200DP_REQUIRE(C > 0 && C <= B200DP_DW_NOALLOC_MAX_C,
+                 "dw_fwd_bn_noalloc: C=%d exceeds the static scratch (at most %d channels); use b200dp_dw_fwd with "
+                 "your own sums buffer", C, B200DP_DW_NOALLOC_MAX_C);
+  B200DP_REQUIRE(B > 0 && H > 0 && W > 0, "dw_fwd_bn_noalloc: empty tensor");
+  float* sums = nullptr;
+  if (int rc = dw_noalloc_scratch(&sums)) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the previous call's sums are still in the array: clear the 2*C entries this call accumulates into
+  B200DP_CUDA(cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(float), s));
+  if (int rc = dw_fwd_launch(x, in_scale, in_shift, w, y, sums, C, B, H, W, C, stride, s)) return rc;
+  const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
+  return bn_fwd_finalize_launch(sums, C, gamma, beta, (float)B * Ho * Wo, eps, 0.f, nullptr, nullptr, coef_out,
+                                saved_out, C, s);
+}

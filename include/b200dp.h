@@ -176,6 +176,25 @@ int b200dp_affine(const void* a, const void* b, const float* coef, int three, vo
 int b200dp_grad_join_stats(const void* g1, const void* g2, const void* x, void* dout, float* sums, int stride,
                            long long rows, int C, void* stream);
 
+/* Depthwise conv + the BatchNorm coefficients of its output, with NO device allocation by anyone.
+ * This entry point has no counterpart in the reference.
+ * It is b200dp_dw_fwd followed by b200dp_bn_fwd_finalize, except that the per-channel sums -- scratch that
+ * the two-call form makes the caller allocate and zero -- live in a static 8 KB __device__ array inside this
+ * library (one copy on every GPU that loads it, kept until exit).  It exists for callers that may not
+ * allocate device memory at the point of the call: plug-ins inside another runtime's enqueue hook, serving
+ * loops with a fixed up-front memory budget, latency-critical paths that must never enter the allocator, or
+ * processes whose free memory is all held by a framework allocator.
+ *   - C must be <= B200DP_DW_NOALLOC_MAX_C (else B200DP_EINVAL; use the two-call form);
+ *   - the call clears the part of the scratch it uses, runs the conv, writes coef_out [2][C] = (scale, shift)
+ *     and saved_out [2][C] = (mean, inv-std); running statistics are not touched;
+ *   - all calls on one GPU share the scratch: calls that may overlap on the device race -- serialise them;
+ *   - the FIRST call on each device looks up the scratch's device address (cudaGetSymbolAddress); make that
+ *     first call before any stream capture begins. */
+#define B200DP_DW_NOALLOC_MAX_C 1024
+int b200dp_dw_fwd_bn_noalloc(const void* x, const float* in_scale, const float* in_shift, const float* w,
+                             const float* gamma, const float* beta, float eps, void* y, float* coef_out,
+                             float* saved_out, int B, int H, int W, int C, int stride, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
