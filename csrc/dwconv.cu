@@ -22,7 +22,7 @@ namespace b200dp {
 namespace {
 
 constexpr int TH = 2;
-constexpr int VEC = 4;
+constexpr int VEC = 2;     // channels per thread: one bf16x2 word, a warp covers 64 contiguous channels (128 B)
 
 struct DwFwdParams {
   const __nv_bfloat16* x;
@@ -31,34 +31,31 @@ struct DwFwdParams {
   const float* w;        // [9][C] fp32 (tap-major)
   __nv_bfloat16* y;
   float* stats;          // [2][stats_stride]; may be null (inference)
-  int B, H, W, C, Ho, Wo, nseg, seglen, stats_stride;
+  int B, H, W, C, Ho, Wo, nseg, seglen, stats_stride, cgb;   // cgb: channel pairs handled by one block
 };
 
-__device__ __forceinline__ void unpack4(const uint2& v, float (&f)[4]) {
-  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
-}
-__device__ __forceinline__ uint2 ldg8(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint2*>(p)); }
+__device__ __forceinline__ uint32_t ldg4(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint32_t*>(p)); }
 
+// Forward.  Per output column a thread loads S new input columns of R rows (4-byte words), already issued one
+// iteration ahead (register prefetch), so global latency overlaps the FMAs of the current column.
 template <int S>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 dw_fwd_kernel(const DwFwdParams P) {
   constexpr int R = (TH - 1) * S + 3;
   extern __shared__ float s_red[];                 // [2][C]
-  const int CG = P.C / VEC;
+  const int CG = P.cgb;                            // channel pairs of this block: [blockIdx.y * cgb, +cgb)
   const int ipb = blockDim.x / CG;
-  const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
+  const int cg = blockIdx.y * CG + threadIdx.x % CG, ti = threadIdx.x / CG;
   const int c0 = cg * VEC;
+  const int cb0 = blockIdx.y * CG * VEC, cbn = CG * VEC;   // channel range flushed by this block
   for (int i = threadIdx.x; i < 2 * P.C; i += blockDim.x) s_red[i] = 0.f;
   __syncthreads();
-  float s0[VEC] = {0.f, 0.f, 0.f, 0.f}, s1[VEC] = {0.f, 0.f, 0.f, 0.f};
+  float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
   if (ti < ipb) {
-    float wr[9][VEC], sc[VEC], sh[VEC];
+    float wa[9], wb[9];
 #pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) wr[k][j] = P.w[k * P.C + c0 + j];
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) { sc[j] = P.scale[c0 + j]; sh[j] = P.shift[c0 + j]; }
+    for (int k = 0; k < 9; ++k) { wa[k] = P.w[k * P.C + c0]; wb[k] = P.w[k * P.C + c0 + 1]; }
+    const float sca = P.scale[c0], scb = P.scale[c0 + 1], sha = P.shift[c0], shb = P.shift[c0 + 1];
     const int rblocks = (P.Ho + TH - 1) / TH;
     const long long items = (long long)P.B * rblocks * P.nseg;
     for (long long item = (long long)blockIdx.x * ipb + ti; item < items; item += (long long)gridDim.x * ipb) {
@@ -66,75 +63,82 @@ dw_fwd_kernel(const DwFwdParams P) {
       const int yb = (int)((item / P.nseg) % rblocks);
       const int n = (int)(item / ((long long)P.nseg * rblocks));
       const int y0 = yb * TH, xs = seg * P.seglen, xe = min(xs + P.seglen, P.Wo);
+      if (xs >= xe) continue;
       const int iy0 = y0 * S - 1;
       const __nv_bfloat16* xin = P.x + (size_t)n * P.H * P.W * P.C + c0;
       __nv_bfloat16* yout = P.y + (size_t)n * P.Ho * P.Wo * P.C + c0;
-      auto loadcol = [&](int xi, float (&col)[R][VEC]) {
+      uint32_t rmask = 0;
+#pragma unroll
+      for (int r = 0; r < R; ++r) rmask |= ((iy0 + r) >= 0 && (iy0 + r) < P.H) ? (1u << r) : 0u;
+      auto fetch = [&](int xi, uint32_t (&raw)[R]) {
         const bool xok = xi >= 0 && xi < P.W;
-        uint2 raw[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          raw[r] = (xok && ((rmask >> r) & 1u)) ? ldg4(xin + ((size_t)(iy0 + r) * P.W + xi) * P.C) : 0u;
+      };
+      // zero padding is post-activation: out-of-image taps contribute 0, not relu6(shift)
+      auto xform = [&](int xi, const uint32_t (&raw)[R], float (&a)[R], float (&b)[R]) {
+        const bool xok = xi >= 0 && xi < P.W;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const int iy = iy0 + r;
-          raw[r] = make_uint2(0u, 0u);
-          if (xok && iy >= 0 && iy < P.H) raw[r] = ldg8(xin + ((size_t)iy * P.W + xi) * P.C);
-        }
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-          const bool ok = xok && (iy0 + r) >= 0 && (iy0 + r) < P.H;
-          float f[VEC];
-          unpack4(raw[r], f);
-#pragma unroll
-          for (int j = 0; j < VEC; ++j) col[r][j] = ok ? relu6f(fmaf(f[j], sc[j], sh[j])) : 0.f;   // zero padding is post-activation
+          const bool ok = xok && ((rmask >> r) & 1u);
+          a[r] = ok ? relu6f(fmaf(bf16_lo(raw[r]), sca, sha)) : 0.f;
+          b[r] = ok ? relu6f(fmaf(bf16_hi(raw[r]), scb, shb)) : 0.f;
         }
       };
-      float ca[R][VEC], cb[R][VEC], cc[R][VEC];
-      if (S == 1) { loadcol(xs - 1, ca); loadcol(xs, cb); } else { loadcol(2 * xs - 1, ca); }
+      float pa[R], pb[R], ca[R], cb[R], na[R], nb[R];     // previous / centre / next input column (2 channels)
+      uint32_t n0[R], n1[R];
+      if (S == 1) {
+        fetch(xs - 1, n0); xform(xs - 1, n0, pa, pb);
+        fetch(xs, n0);     xform(xs, n0, ca, cb);
+        fetch(xs + 1, n0);
+      } else {
+        fetch(2 * xs - 1, n0); xform(2 * xs - 1, n0, pa, pb);
+        fetch(2 * xs, n0);
+        fetch(2 * xs + 1, n1);
+      }
       for (int xo = xs; xo < xe; ++xo) {
-        if (S == 1) { loadcol(xo + 1, cc); } else { loadcol(2 * xo, cb); loadcol(2 * xo + 1, cc); }
+        if (S == 1) {
+          xform(xo + 1, n0, na, nb);
+          if (xo + 1 < xe) fetch(xo + 2, n0);
+        } else {
+          xform(2 * xo, n0, ca, cb);
+          xform(2 * xo + 1, n1, na, nb);
+          if (xo + 1 < xe) { fetch(2 * xo + 2, n0); fetch(2 * xo + 3, n1); }
+        }
 #pragma unroll
         for (int t = 0; t < TH; ++t) {
           if (y0 + t < P.Ho) {
-            float acc[VEC] = {0.f, 0.f, 0.f, 0.f};
+            float acca = 0.f, accb = 0.f;
 #pragma unroll
-            for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-              for (int j = 0; j < VEC; ++j) {
-                acc[j] = fmaf(wr[ky * 3 + 0][j], ca[t * S + ky][j], acc[j]);
-                acc[j] = fmaf(wr[ky * 3 + 1][j], cb[t * S + ky][j], acc[j]);
-                acc[j] = fmaf(wr[ky * 3 + 2][j], cc[t * S + ky][j], acc[j]);
-              }
-            const uint2 o = make_uint2(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]));
-            *reinterpret_cast<uint2*>(yout + ((size_t)(y0 + t) * P.Wo + xo) * P.C) = o;
-            float q[VEC];
-            unpack4(o, q);      // statistics of the values the consumer will actually read
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) { s0[j] += q[j]; s1[j] = fmaf(q[j], q[j], s1[j]); }
+            for (int ky = 0; ky < 3; ++ky) {
+              const int r = t * S + ky;
+              acca = fmaf(wa[ky * 3 + 0], pa[r], acca); accb = fmaf(wb[ky * 3 + 0], pb[r], accb);
+              acca = fmaf(wa[ky * 3 + 1], ca[r], acca); accb = fmaf(wb[ky * 3 + 1], cb[r], accb);
+              acca = fmaf(wa[ky * 3 + 2], na[r], acca); accb = fmaf(wb[ky * 3 + 2], nb[r], accb);
+            }
+            const uint32_t o = pack_bf16x2(acca, accb);
+            *reinterpret_cast<uint32_t*>(yout + ((size_t)(y0 + t) * P.Wo + xo) * P.C) = o;
+            const float qa = bf16_lo(o), qb = bf16_hi(o);   // statistics of the values the consumer will read
+            s0a += qa; s0b += qb;
+            s1a = fmaf(qa, qa, s1a); s1b = fmaf(qb, qb, s1b);
           }
         }
-        if (S == 1) {
 #pragma unroll
-          for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) { ca[r][j] = cb[r][j]; cb[r][j] = cc[r][j]; }
-        } else {
-#pragma unroll
-          for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) ca[r][j] = cc[r][j];
+        for (int r = 0; r < R; ++r) {
+          if (S == 1) { pa[r] = ca[r]; pb[r] = cb[r]; ca[r] = na[r]; cb[r] = nb[r]; }
+          else { pa[r] = na[r]; pb[r] = nb[r]; }
         }
       }
     }
     if (P.stats != nullptr) {
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        atomicAdd(&s_red[c0 + j], s0[j]);
-        atomicAdd(&s_red[P.C + c0 + j], s1[j]);
-      }
+      atomicAdd(&s_red[c0], s0a); atomicAdd(&s_red[c0 + 1], s0b);
+      atomicAdd(&s_red[P.C + c0], s1a); atomicAdd(&s_red[P.C + c0 + 1], s1b);
     }
   }
   __syncthreads();
   if (P.stats != nullptr)
-    for (int i = threadIdx.x; i < P.C; i += blockDim.x) {
+    for (int i = cb0 + threadIdx.x; i < cb0 + cbn; i += blockDim.x) {
       atomicAdd(P.stats + i, s_red[i]);
       atomicAdd(P.stats + P.stats_stride + i, s_red[P.C + i]);
     }
@@ -151,31 +155,37 @@ struct DwBwdParams {
   __nv_bfloat16* dze;           // [B,H,W,C] out: gradient w.r.t. the input-side BatchNorm output (masked)
   float* stats;                 // [2][stats_stride]: sum dze, sum dze*e_raw
   float* dw;                    // [9][C] fp32 weight gradient (accumulated)
-  int B, H, W, C, Ho, Wo, nseg, seglen, stats_stride;
+  int B, H, W, C, Ho, Wo, nseg, seglen, stats_stride, cgb;
 };
 
+// Backward.  Stride 1: sliding window over the three output columns wo = w-1, w, w+1 that read input column w.
+// Stride 2: input pixels are handled as 2x2 blocks (rows 2r, 2r+1; columns 2c, 2c+1), which read exactly the
+// output positions (r..r+1, c..c+1) -- nine (tap, position) pairs per block, column c+1 carried to the next block.
+// Either way each dd = ca*dz_d + cb*d_raw + cc is formed once per thread and raw words are prefetched one
+// iteration ahead.
 template <int S>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 dw_bwd_kernel(const DwBwdParams P) {
   extern __shared__ float s_red[];                 // [2][C] stats + [9][C] dW
-  const int CG = P.C / VEC;
+  const int CG = P.cgb;                            // channel pairs of this block: [blockIdx.y * cgb, +cgb)
   const int ipb = blockDim.x / CG;
-  const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
+  const int cg = blockIdx.y * CG + threadIdx.x % CG, ti = threadIdx.x / CG;
   const int c0 = cg * VEC;
+  const int cb0 = blockIdx.y * CG * VEC, cbn = CG * VEC;   // channel range flushed by this block
   for (int i = threadIdx.x; i < 11 * P.C; i += blockDim.x) s_red[i] = 0.f;
   __syncthreads();
   if (ti < ipb) {
-    float wr[9][VEC], gw[9][VEC], sc[VEC], sh[VEC], ka[VEC], kb[VEC], kc[VEC];
-    float s0[VEC] = {0.f, 0.f, 0.f, 0.f}, s1[VEC] = {0.f, 0.f, 0.f, 0.f};
+    float wa[9], wb[9], ga[9], gb[9];
 #pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) { wr[k][j] = P.w[k * P.C + c0 + j]; gw[k][j] = 0.f; }
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) {
-      sc[j] = P.escale[c0 + j]; sh[j] = P.eshift[c0 + j];
-      ka[j] = P.dcoef[c0 + j]; kb[j] = P.dcoef[P.C + c0 + j]; kc[j] = P.dcoef[2 * P.C + c0 + j];
+    for (int k = 0; k < 9; ++k) {
+      wa[k] = P.w[k * P.C + c0]; wb[k] = P.w[k * P.C + c0 + 1];
+      ga[k] = 0.f; gb[k] = 0.f;
     }
+    const float sca = P.escale[c0], scb = P.escale[c0 + 1], sha = P.eshift[c0], shb = P.eshift[c0 + 1];
+    const float kaa = P.dcoef[c0], kab = P.dcoef[c0 + 1];
+    const float kba = P.dcoef[P.C + c0], kbb = P.dcoef[P.C + c0 + 1];
+    const float kca = P.dcoef[2 * P.C + c0], kcb = P.dcoef[2 * P.C + c0 + 1];
+    float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
     const int rblocks = (P.H + TH - 1) / TH;
     const long long items = (long long)P.B * rblocks * P.nseg;
     for (long long item = (long long)blockIdx.x * ipb + ti; item < items; item += (long long)gridDim.x * ipb) {
@@ -183,144 +193,188 @@ dw_bwd_kernel(const DwBwdParams P) {
       const int hb = (int)((item / P.nseg) % rblocks);
       const int n = (int)(item / ((long long)P.nseg * rblocks));
       const int h0 = hb * TH, ws = seg * P.seglen, we = min(ws + P.seglen, P.W);
+      if (ws >= we) continue;
       const __nv_bfloat16* ein = P.e_raw + (size_t)n * P.H * P.W * P.C + c0;
       __nv_bfloat16* dout = P.dze + (size_t)n * P.H * P.W * P.C + c0;
       const __nv_bfloat16* gz = P.dzd + (size_t)n * P.Ho * P.Wo * P.C + c0;
       const __nv_bfloat16* gr = P.d_raw + (size_t)n * P.Ho * P.Wo * P.C + c0;
-      // dd(ho, wo) = ca*dz_d + cb*d_raw + cc inside the output grid, 0 outside
-      auto dd_at = [&](int ho, int wo, float (&d)[VEC]) {
-        const bool ok = ho >= 0 && ho < P.Ho && wo >= 0 && wo < P.Wo;
-        uint2 a = make_uint2(0u, 0u), b = make_uint2(0u, 0u);
-        if (ok) {
-          const size_t off = ((size_t)ho * P.Wo + wo) * P.C;
-          a = ldg8(gz + off);
-          b = ldg8(gr + off);
-        }
-        float fa[VEC], fb[VEC];
-        unpack4(a, fa);
-        unpack4(b, fb);
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) d[j] = ok ? fmaf(ka[j], fa[j], fmaf(kb[j], fb[j], kc[j])) : 0.f;
-      };
-      // finish one input pixel: mask, store, statistics, weight-gradient contribution is done by the caller
-      auto finish = [&](int h, int w, const float (&da)[VEC], const float (&e)[VEC], const bool (&keep)[VEC]) {
-        float o[VEC];
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) o[j] = keep[j] ? da[j] : 0.f;
-        const uint2 pk = make_uint2(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]));
-        *reinterpret_cast<uint2*>(dout + ((size_t)h * P.W + w) * P.C) = pk;
-        float q[VEC];
-        unpack4(pk, q);
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) { s0[j] += q[j]; s1[j] = fmaf(q[j], e[j], s1[j]); }
+      // one input pixel: mask, store, statistics (the tap sums da and the weight-gradient terms come from the caller)
+      auto finish = [&](int h, int w, uint32_t eraw, float daa, float dab) {
+        const float ea = bf16_lo(eraw), eb = bf16_hi(eraw);
+        const float za = fmaf(ea, sca, sha), zb = fmaf(eb, scb, shb);
+        const float oa = (za > 0.f && za < 6.f) ? daa : 0.f;
+        const float ob = (zb > 0.f && zb < 6.f) ? dab : 0.f;
+        const uint32_t pk = pack_bf16x2(oa, ob);
+        *reinterpret_cast<uint32_t*>(dout + ((size_t)h * P.W + w) * P.C) = pk;
+        const float qa = bf16_lo(pk), qb = bf16_hi(pk);
+        s0a += qa; s0b += qb;
+        s1a = fmaf(qa, ea, s1a); s1b = fmaf(qb, eb, s1b);
       };
       if (S == 1) {
-        // sliding window over output columns wo = w-1, w, w+1; rows ho = h0-1 .. h0+TH
-        constexpr int R = TH + 2;
-        float dp[R][VEC], dc[R][VEC], dn[R][VEC];
+        constexpr int R = TH + 2;                   // output rows ho = h0-1 .. h0+TH
+        uint32_t rmask = 0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) { dd_at(h0 - 1 + r, ws - 1, dp[r]); dd_at(h0 - 1 + r, ws, dc[r]); }
+        for (int r = 0; r < R; ++r) rmask |= ((h0 - 1 + r) >= 0 && (h0 - 1 + r) < P.Ho) ? (1u << r) : 0u;
+        auto fetch = [&](int wo, uint32_t (&z)[R], uint32_t (&g)[R]) {
+          const bool ok = wo >= 0 && wo < P.Wo;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const bool v = ok && ((rmask >> r) & 1u);
+            const size_t off = ((size_t)(h0 - 1 + r) * P.Wo + wo) * P.C;
+            z[r] = v ? ldg4(gz + off) : 0u;
+            g[r] = v ? ldg4(gr + off) : 0u;
+          }
+        };
+        auto xform = [&](int wo, const uint32_t (&z)[R], const uint32_t (&g)[R], float (&a)[R], float (&b)[R]) {
+          const bool ok = wo >= 0 && wo < P.Wo;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const bool v = ok && ((rmask >> r) & 1u);
+            a[r] = v ? fmaf(kaa, bf16_lo(z[r]), fmaf(kba, bf16_lo(g[r]), kca)) : 0.f;
+            b[r] = v ? fmaf(kab, bf16_hi(z[r]), fmaf(kbb, bf16_hi(g[r]), kcb)) : 0.f;
+          }
+        };
+        auto fetch_e = [&](int w, uint32_t (&e)[TH]) {
+#pragma unroll
+          for (int t = 0; t < TH; ++t)
+            e[t] = (w < P.W && h0 + t < P.H) ? ldg4(ein + ((size_t)(h0 + t) * P.W + w) * P.C) : 0u;
+        };
+        float pa[R], pb[R], ca[R], cb[R], na[R], nb[R];
+        uint32_t nz[R], ng[R], ne[TH], ec[TH];
+        fetch(ws - 1, nz, ng); xform(ws - 1, nz, ng, pa, pb);
+        fetch(ws, nz, ng);     xform(ws, nz, ng, ca, cb);
+        fetch(ws + 1, nz, ng);
+        fetch_e(ws, ne);
         for (int w = ws; w < we; ++w) {
+          xform(w + 1, nz, ng, na, nb);
 #pragma unroll
-          for (int r = 0; r < R; ++r) dd_at(h0 - 1 + r, w + 1, dn[r]);
+          for (int t = 0; t < TH; ++t) ec[t] = ne[t];
+          if (w + 1 < we) { fetch(w + 2, nz, ng); fetch_e(w + 1, ne); }
 #pragma unroll
           for (int t = 0; t < TH; ++t) {
             const int h = h0 + t;
             if (h < P.H) {
-              float e[VEC], a[VEC], da[VEC] = {0.f, 0.f, 0.f, 0.f};
-              bool keep[VEC];
-              unpack4(ldg8(ein + ((size_t)h * P.W + w) * P.C), e);
-#pragma unroll
-              for (int j = 0; j < VEC; ++j) {
-                const float z = fmaf(e[j], sc[j], sh[j]);
-                keep[j] = z > 0.f && z < 6.f;
-                a[j] = relu6f(z);
-              }
+              const float aa = relu6f(fmaf(bf16_lo(ec[t]), sca, sha));
+              const float ab = relu6f(fmaf(bf16_hi(ec[t]), scb, shb));
+              float daa = 0.f, dab = 0.f;
 #pragma unroll
               for (int ky = 0; ky < 3; ++ky) {
-                const int r = t + 2 - ky;        // ho = h + 1 - ky  ->  row index ho - (h0 - 1)
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) {
-                  da[j] = fmaf(dn[r][j], wr[ky * 3 + 0][j], da[j]);   // kx = 0 -> wo = w + 1
-                  da[j] = fmaf(dc[r][j], wr[ky * 3 + 1][j], da[j]);   // kx = 1 -> wo = w
-                  da[j] = fmaf(dp[r][j], wr[ky * 3 + 2][j], da[j]);   // kx = 2 -> wo = w - 1
-                  gw[ky * 3 + 0][j] = fmaf(a[j], dn[r][j], gw[ky * 3 + 0][j]);
-                  gw[ky * 3 + 1][j] = fmaf(a[j], dc[r][j], gw[ky * 3 + 1][j]);
-                  gw[ky * 3 + 2][j] = fmaf(a[j], dp[r][j], gw[ky * 3 + 2][j]);
-                }
+                const int r = t + 2 - ky;              // ho = h + 1 - ky  ->  row index ho - (h0 - 1)
+                daa = fmaf(na[r], wa[ky * 3 + 0], daa); dab = fmaf(nb[r], wb[ky * 3 + 0], dab);   // kx = 0 -> wo = w + 1
+                daa = fmaf(ca[r], wa[ky * 3 + 1], daa); dab = fmaf(cb[r], wb[ky * 3 + 1], dab);   // kx = 1 -> wo = w
+                daa = fmaf(pa[r], wa[ky * 3 + 2], daa); dab = fmaf(pb[r], wb[ky * 3 + 2], dab);   // kx = 2 -> wo = w - 1
+                ga[ky * 3 + 0] = fmaf(aa, na[r], ga[ky * 3 + 0]); gb[ky * 3 + 0] = fmaf(ab, nb[r], gb[ky * 3 + 0]);
+                ga[ky * 3 + 1] = fmaf(aa, ca[r], ga[ky * 3 + 1]); gb[ky * 3 + 1] = fmaf(ab, cb[r], gb[ky * 3 + 1]);
+                ga[ky * 3 + 2] = fmaf(aa, pa[r], ga[ky * 3 + 2]); gb[ky * 3 + 2] = fmaf(ab, pb[r], gb[ky * 3 + 2]);
               }
-              finish(h, w, da, e, keep);
+              finish(h, w, ec[t], daa, dab);
             }
           }
 #pragma unroll
-          for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) { dp[r][j] = dc[r][j]; dc[r][j] = dn[r][j]; }
+          for (int r = 0; r < R; ++r) { pa[r] = ca[r]; pb[r] = cb[r]; ca[r] = na[r]; cb[r] = nb[r]; }
         }
       } else {
-        // stride 2: gather the (at most 4) output positions that read this input pixel
-        for (int w = ws; w < we; ++w) {
+        // h0 is even (TH == 2): rows h0 = 2r, h0+1; output rows r, r+1.  Column pairs (2c, 2c+1), output cols c, c+1.
+        const int r0 = h0 >> 1;
+        const int cs = ws >> 1, ce = (we + 1) >> 1;     // segments start at even columns (seglen is even)
+        auto fetch = [&](int wo, uint32_t (&z)[2], uint32_t (&g)[2]) {
 #pragma unroll
-          for (int t = 0; t < TH; ++t) {
-            const int h = h0 + t;
-            if (h < P.H) {
-              float e[VEC], a[VEC], da[VEC] = {0.f, 0.f, 0.f, 0.f};
-              bool keep[VEC];
-              unpack4(ldg8(ein + ((size_t)h * P.W + w) * P.C), e);
-#pragma unroll
-              for (int j = 0; j < VEC; ++j) {
-                const float z = fmaf(e[j], sc[j], sh[j]);
-                keep[j] = z > 0.f && z < 6.f;
-                a[j] = relu6f(z);
-              }
-#pragma unroll
-              for (int ky = 0; ky < 3; ++ky) {
-                const int hy = h + 1 - ky;
-                if (hy < 0 || (hy & 1)) continue;
-#pragma unroll
-                for (int kx = 0; kx < 3; ++kx) {
-                  const int wx = w + 1 - kx;
-                  if (wx < 0 || (wx & 1)) continue;
-                  float d[VEC];
-                  dd_at(hy >> 1, wx >> 1, d);
-#pragma unroll
-                  for (int j = 0; j < VEC; ++j) {
-                    da[j] = fmaf(d[j], wr[ky * 3 + kx][j], da[j]);
-                    gw[ky * 3 + kx][j] = fmaf(a[j], d[j], gw[ky * 3 + kx][j]);
-                  }
-                }
-              }
-              finish(h, w, da, e, keep);
-            }
+          for (int r = 0; r < 2; ++r) {
+            const bool v = wo >= 0 && wo < P.Wo && (r0 + r) < P.Ho;
+            const size_t off = ((size_t)(r0 + r) * P.Wo + wo) * P.C;
+            z[r] = v ? ldg4(gz + off) : 0u;
+            g[r] = v ? ldg4(gr + off) : 0u;
           }
+        };
+        auto xform = [&](int wo, const uint32_t (&z)[2], const uint32_t (&g)[2], float (&a)[2], float (&b)[2]) {
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
+            const bool v = wo >= 0 && wo < P.Wo && (r0 + r) < P.Ho;
+            a[r] = v ? fmaf(kaa, bf16_lo(z[r]), fmaf(kba, bf16_lo(g[r]), kca)) : 0.f;
+            b[r] = v ? fmaf(kab, bf16_hi(z[r]), fmaf(kbb, bf16_hi(g[r]), kcb)) : 0.f;
+          }
+        };
+        auto fetch_e = [&](int c, uint32_t (&e)[4]) {    // e[2*dy + dx]
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int h = h0 + (q >> 1), w = 2 * c + (q & 1);
+            e[q] = (h < P.H && w < P.W) ? ldg4(ein + ((size_t)h * P.W + w) * P.C) : 0u;
+          }
+        };
+        float d0a[2], d0b[2], d1a[2], d1b[2];
+        uint32_t nz[2], ng[2], ne[4], ec[4];
+        fetch(cs, nz, ng); xform(cs, nz, ng, d0a, d0b);
+        fetch(cs + 1, nz, ng);
+        fetch_e(cs, ne);
+        for (int c = cs; c < ce; ++c) {
+          xform(c + 1, nz, ng, d1a, d1b);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) ec[q] = ne[q];
+          if (c + 1 < ce) { fetch(c + 2, nz, ng); fetch_e(c + 1, ne); }
+          float aa[4], ab[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int hq = h0 + (q >> 1), wq = 2 * c + (q & 1);
+            const bool v = hq < P.H && wq >= ws && wq < we;       // outside the image / segment: no contribution
+            aa[q] = v ? relu6f(fmaf(bf16_lo(ec[q]), sca, sha)) : 0.f;
+            ab[q] = v ? relu6f(fmaf(bf16_hi(ec[q]), scb, shb)) : 0.f;
+          }
+          // (even h, even w): tap (1,1) <- (r, c)
+          float da0a = d0a[0] * wa[4], da0b = d0b[0] * wb[4];
+          ga[4] = fmaf(aa[0], d0a[0], ga[4]); gb[4] = fmaf(ab[0], d0b[0], gb[4]);
+          // (even h, odd w): (1,0) <- (r, c+1), (1,2) <- (r, c)
+          float da1a = fmaf(d1a[0], wa[3], d0a[0] * wa[5]), da1b = fmaf(d1b[0], wb[3], d0b[0] * wb[5]);
+          ga[3] = fmaf(aa[1], d1a[0], ga[3]); gb[3] = fmaf(ab[1], d1b[0], gb[3]);
+          ga[5] = fmaf(aa[1], d0a[0], ga[5]); gb[5] = fmaf(ab[1], d0b[0], gb[5]);
+          // (odd h, even w): (0,1) <- (r+1, c), (2,1) <- (r, c)
+          float da2a = fmaf(d0a[1], wa[1], d0a[0] * wa[7]), da2b = fmaf(d0b[1], wb[1], d0b[0] * wb[7]);
+          ga[1] = fmaf(aa[2], d0a[1], ga[1]); gb[1] = fmaf(ab[2], d0b[1], gb[1]);
+          ga[7] = fmaf(aa[2], d0a[0], ga[7]); gb[7] = fmaf(ab[2], d0b[0], gb[7]);
+          // (odd h, odd w): (0,0) <- (r+1, c+1), (0,2) <- (r+1, c), (2,0) <- (r, c+1), (2,2) <- (r, c)
+          float da3a = fmaf(d1a[1], wa[0], fmaf(d0a[1], wa[2], fmaf(d1a[0], wa[6], d0a[0] * wa[8])));
+          float da3b = fmaf(d1b[1], wb[0], fmaf(d0b[1], wb[2], fmaf(d1b[0], wb[6], d0b[0] * wb[8])));
+          ga[0] = fmaf(aa[3], d1a[1], ga[0]); gb[0] = fmaf(ab[3], d1b[1], gb[0]);
+          ga[2] = fmaf(aa[3], d0a[1], ga[2]); gb[2] = fmaf(ab[3], d0b[1], gb[2]);
+          ga[6] = fmaf(aa[3], d1a[0], ga[6]); gb[6] = fmaf(ab[3], d1b[0], gb[6]);
+          ga[8] = fmaf(aa[3], d0a[0], ga[8]); gb[8] = fmaf(ab[3], d0b[0], gb[8]);
+          const int w0 = 2 * c;
+          if (w0 >= ws && w0 < we) {
+            if (h0 < P.H) finish(h0, w0, ec[0], da0a, da0b);
+            if (h0 + 1 < P.H) finish(h0 + 1, w0, ec[2], da2a, da2b);
+          }
+          if (w0 + 1 >= ws && w0 + 1 < we) {
+            if (h0 < P.H) finish(h0, w0 + 1, ec[1], da1a, da1b);
+            if (h0 + 1 < P.H) finish(h0 + 1, w0 + 1, ec[3], da3a, da3b);
+          }
+#pragma unroll
+          for (int r = 0; r < 2; ++r) { d0a[r] = d1a[r]; d0b[r] = d1b[r]; }
         }
       }
     }
+    atomicAdd(&s_red[c0], s0a); atomicAdd(&s_red[c0 + 1], s0b);
+    atomicAdd(&s_red[P.C + c0], s1a); atomicAdd(&s_red[P.C + c0 + 1], s1b);
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) {
-      atomicAdd(&s_red[c0 + j], s0[j]);
-      atomicAdd(&s_red[P.C + c0 + j], s1[j]);
+    for (int k = 0; k < 9; ++k) {
+      atomicAdd(&s_red[(2 + k) * P.C + c0], ga[k]);
+      atomicAdd(&s_red[(2 + k) * P.C + c0 + 1], gb[k]);
     }
-#pragma unroll
-    for (int k = 0; k < 9; ++k)
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) atomicAdd(&s_red[(2 + k) * P.C + c0 + j], gw[k][j]);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < P.C; i += blockDim.x) {
+  for (int i = cb0 + threadIdx.x; i < cb0 + cbn; i += blockDim.x) {
     atomicAdd(P.stats + i, s_red[i]);
     atomicAdd(P.stats + P.stats_stride + i, s_red[P.C + i]);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) atomicAdd(P.dw + k * P.C + i, s_red[(2 + k) * P.C + i]);
   }
-  for (int i = threadIdx.x; i < 9 * P.C; i += blockDim.x) atomicAdd(P.dw + i, s_red[2 * P.C + i]);
 }
 
 void pick_segments(int rows, int width, int B, int C, int* nseg, int* seglen) {
   // enough independent strips to fill the machine (~300k threads), segments no shorter than 7 pixels
   const long long base = (long long)B * ((rows + TH - 1) / TH) * (C / VEC);
   int n = 1;
-  while (base * n < 300000 && width / (n * 2) >= 7) n *= 2;
+  while (base * n < 600000 && width / (n * 2) >= 7) n *= 2;
   *nseg = n;
-  *seglen = (width + n - 1) / n;
+  *seglen = ((width + n - 1) / n + 1) & ~1;      // even: the stride-2 backward walks columns in pairs
 }
 
 }  // namespace
@@ -336,16 +390,19 @@ int dw_fwd_launch(const void* x, const float* scale, const float* shift, const f
   P.Ho = (H - 1) / stride + 1; P.Wo = (W - 1) / stride + 1;
   pick_segments(P.Ho, P.Wo, B, C, &P.nseg, &P.seglen);
   const int CG = C / VEC;
-  const int threads = CG >= 256 ? 256 : (256 / CG) * CG;
-  B200DP_REQUIRE(CG <= 256, "dw_fwd: C too large");
-  const int ipb = threads / CG;
+  const int csplit = (CG + 255) / 256;
+  B200DP_REQUIRE(CG % csplit == 0, "dw_fwd: C=%d cannot be split evenly over blocks", C);
+  P.cgb = CG / csplit;
+  const int threads = (256 / P.cgb) * P.cgb;
+  const int ipb = threads / P.cgb;
   const long long items = (long long)B * ((P.Ho + TH - 1) / TH) * P.nseg;
   long long blocks = (items + ipb - 1) / ipb;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   const size_t smem = 2 * (size_t)C * sizeof(float);
-  if (stride == 1) dw_fwd_kernel<1><<<(int)blocks, threads, smem, s>>>(P);
-  else dw_fwd_kernel<2><<<(int)blocks, threads, smem, s>>>(P);
+  const dim3 grid((unsigned)blocks, (unsigned)csplit);
+  if (stride == 1) dw_fwd_kernel<1><<<grid, threads, smem, s>>>(P);
+  else dw_fwd_kernel<2><<<grid, threads, smem, s>>>(P);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -363,16 +420,19 @@ int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, c
   P.Ho = (H - 1) / stride + 1; P.Wo = (W - 1) / stride + 1;
   pick_segments(H, W, B, C, &P.nseg, &P.seglen);
   const int CG = C / VEC;
-  B200DP_REQUIRE(CG <= 256, "dw_bwd: C too large");
-  const int threads = (256 / CG) * CG;
-  const int ipb = threads / CG;
+  const int csplit = (CG + 255) / 256;
+  B200DP_REQUIRE(CG % csplit == 0, "dw_bwd: C=%d cannot be split evenly over blocks", C);
+  P.cgb = CG / csplit;
+  const int threads = (256 / P.cgb) * P.cgb;
+  const int ipb = threads / P.cgb;
   const long long items = (long long)B * ((H + TH - 1) / TH) * P.nseg;
   long long blocks = (items + ipb - 1) / ipb;
   const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
   const size_t smem = 11 * (size_t)C * sizeof(float);
-  if (stride == 1) dw_bwd_kernel<1><<<(int)blocks, threads, smem, s>>>(P);
-  else dw_bwd_kernel<2><<<(int)blocks, threads, smem, s>>>(P);
+  const dim3 grid((unsigned)blocks, (unsigned)csplit);
+  if (stride == 1) dw_bwd_kernel<1><<<grid, threads, smem, s>>>(P);
+  else dw_bwd_kernel<2><<<grid, threads, smem, s>>>(P);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
