@@ -255,7 +255,7 @@ int build_plans(Engine& e, Plans& pl, int n) {
 // A dgrad plan writes to a fixed output buffer chosen at plan time; the executor alternates gx[0]/gx[1], so the
 // output tensor map is re-encoded when the target changes (cheap; host only).
 int retarget_out(PwGemmPlan& pl, void* out) {
-  return make_tmap_2d_bf16(&pl.tmO, out, (uint64_t)pl.p.M, (uint64_t)pl.p.N, (uint64_t)pl.p.ldo, 64, 128);
+  return make_tmap_2d_bf16(&pl.tmO, out, (uint64_t)pl.p.M, (uint64_t)pl.p.N, (uint64_t)pl.p.ldo, 64, 32);
 }
 
 int bn_fin_f(Engine& e, Conv& c, float count, cudaStream_t s) {

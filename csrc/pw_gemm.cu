@@ -72,10 +72,23 @@ __device__ __forceinline__ uint4 lds16(uint32_t addr) {
   return v;
 }
 
+// Thread layout.  A_TMA kernels: 4 control warps + 2 epilogue groups of 4 warps (384 threads); each group owns one
+// TMEM accumulator stage, one staging buffer and (E_MASKSTATS) one aux buffer, so two tiles drain concurrently.
+// Register-path kernels: 4 control + 4 epilogue + 8 producer warps (512 threads).
+template <int AMODE>
+struct Layout {
+  static constexpr int kEpiGroups = AMODE == A_TMA ? 2 : 1;
+  static constexpr int kProdWarp0 = 4 + 4 * kEpiGroups;
+  static constexpr int kThreads = AMODE == A_TMA ? 384 : 512;
+};
+
 template <int AMODE, int EMODE>
-__global__ void __launch_bounds__(AMODE == A_TMA ? 256 : 512, 1)
+__global__ void __launch_bounds__(Layout<AMODE>::kThreads, 1)
 pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ PwGemmParams P) {
+               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmX,
+               const __grid_constant__ PwGemmParams P) {
+  using L = Layout<AMODE>;
+  constexpr int NG = L::kEpiGroups;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // ---- carve shared memory (tile buffers 1024-byte aligned for the 128-byte swizzle) ------------
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -84,18 +97,22 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int nch = (P.block_n + 63) >> 6;
   uint8_t* stage_a = base;
   uint8_t* stage_b = stage_a + (size_t)stages * A_STAGE;
-  uint8_t* out_buf = stage_b + (size_t)stages * b_stage;          // 2 x nch x 16 KB
-  float* s_acoef = reinterpret_cast<float*>(out_buf + 2 * (size_t)nch * OUT_CHUNK);
+  uint8_t* out_buf = stage_b + (size_t)stages * b_stage;                       // 2 x nch x 16 KB
+  uint8_t* aux_buf = out_buf + 2 * (size_t)nch * OUT_CHUNK;                    // 2 x nch x 16 KB (E_MASKSTATS)
+  float* s_acoef = reinterpret_cast<float*>(aux_buf + (EMODE == E_MASKSTATS ? 2 * (size_t)nch * OUT_CHUNK : 0));
   const int n_acoef = (AMODE == A_BNRELU ? 2 : (AMODE == A_BNGRAD ? 3 : 0)) * P.K;
   float* s_ecoef = s_acoef + n_acoef;
   const int n_ecoef = (EMODE == E_MASKSTATS ? 2 : 0) * P.N;
-  float* s_stats = s_ecoef + n_ecoef;                              // [2][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stats + 2 * 128);
+  float* s_stats = s_ecoef + n_ecoef;                                          // [2][N] (absolute columns)
+  const int n_stats = (EMODE != E_PLAIN ? 2 : 0) * P.N;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stats + ((n_stats + 1) & ~1));
   uint64_t* full = bars;
   uint64_t* empty = bars + MAX_STAGES;
   uint64_t* tmem_full = bars + 2 * MAX_STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* aux_full = tmem_empty + 2;
+  uint64_t* aux_empty = aux_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -106,6 +123,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmO);
     if (AMODE == A_TMA) prefetch_tmap(&tmA);
+    if (EMODE == E_MASKSTATS) prefetch_tmap(&tmX);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -115,13 +133,15 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
       mbar_init(&tmem_empty[a], EPI_THREADS);
+      mbar_init(&aux_full[a], 1);
+      mbar_init(&aux_empty[a], EPI_THREADS);
     }
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
   for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) s_acoef[i] = P.acoef[i];
   for (int i = threadIdx.x; i < n_ecoef; i += blockDim.x) s_ecoef[i] = P.ecoef[i];
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) s_stats[i] = 0.f;
+  for (int i = threadIdx.x; i < n_stats; i += blockDim.x) s_stats[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -133,8 +153,16 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t tx = (AMODE == A_TMA ? A_STAGE : 0) + b_stage;
       int s = 0;
       uint32_t ph = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
         const int m0 = (t / P.n_tiles) * BM, n0 = (t % P.n_tiles) * P.block_n;
+        if (EMODE == E_MASKSTATS) {     // raw forward activation tile for the ReLU6 mask, read by the epilogue
+          const int ab = it & 1;
+          mbar_wait(&aux_empty[ab], ((it >> 1) & 1) ^ 1);
+          mbar_arrive_expect_tx(&aux_full[ab], (uint32_t)nch * OUT_CHUNK);
+          for (int c = 0; c < nch; ++c)
+            tma_load_2d(aux_buf + ((size_t)ab * nch + c) * OUT_CHUNK, &tmX, &aux_full[ab], n0 + 64 * c, m0);
+        }
         for (int kc = 0; kc < P.kc; ++kc) {
           mbar_wait(&empty[s], ph ^ 1);
           mbar_arrive_expect_tx(&full[s], tx);
@@ -171,12 +199,15 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         umma_commit(&tmem_full[as]);  // accumulator complete
       }
     }
-  } else if (warp >= 4 && warp < 8) {
-    // =========================== epilogue ===========================
-    const int et = threadIdx.x - 128;          // 0..127
+  } else if (warp >= 4 && warp < L::kProdWarp0) {
+    // =========================== epilogue (warp-local: no block-level barrier per tile) ===========================
+    // Warp q of a group owns TMEM lanes / tile rows 32q..32q+31 end to end: TMEM -> bf16 -> swizzled staging rows
+    // -> coalesced sweep over the same rows (statistics / mask) -> its own TMA store of a {64, 32} box.
+    const int eg = (warp - 4) >> 2;            // epilogue group
     const int q = warp & 3;                    // TMEM lane quadrant this warp may read
-    const int row = q * 32 + lane;
-    const int p = et & 7, rbase = et >> 3;     // pass-2 mapping: 16-byte piece p of rows rbase + 16 i
+    const int row0 = q * 32;
+    const int row = row0 + lane;               // pass 1: one row per thread
+    const int p = lane & 7, rr = lane >> 3;    // pass 2: 16-byte piece p of rows row0 + rr + 4 i
     float s0[2][8], s1[2][8];
 #pragma unroll
     for (int c = 0; c < 2; ++c)
@@ -184,9 +215,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int j = 0; j < 8; ++j) s0[c][j] = s1[c][j] = 0.f;
     float esc[2][8], esh[2][8];
     int prev_n = -1;
-    int it = 0;
 
-    auto flush = [&](int n0) {
+    auto flush = [&](int n0) {     // registers -> shared [2][N] (absolute columns); global flush after the main loop
       if (EMODE == E_PLAIN) return;
 #pragma unroll
       for (int c = 0; c < 2; ++c)
@@ -197,23 +227,16 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           a += __shfl_xor_sync(0xffffffffu, a, 16);
           b += __shfl_xor_sync(0xffffffffu, b, 8);
           b += __shfl_xor_sync(0xffffffffu, b, 16);
-          if (lane < 8) {
-            atomicAdd(&s_stats[c * 64 + lane * 8 + j], a);
-            atomicAdd(&s_stats[128 + c * 64 + lane * 8 + j], b);
+          const int col = n0 + c * 64 + lane * 8 + j;
+          if (lane < 8 && (c * 64 + lane * 8) < P.block_n && col < P.N) {
+            atomicAdd(&s_stats[col], a);
+            atomicAdd(&s_stats[P.N + col], b);
           }
           s0[c][j] = s1[c][j] = 0.f;
         }
-      named_bar_sync(1, EPI_THREADS);
-      if (et < P.block_n && n0 + et < P.N) {
-        atomicAdd(P.stats + n0 + et, s_stats[et]);
-        atomicAdd(P.stats + P.stats_stride + n0 + et, s_stats[128 + et]);
-      }
-      s_stats[et] = 0.f;
-      s_stats[128 + et] = 0.f;
-      named_bar_sync(1, EPI_THREADS);
     };
 
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    for (int it = eg, t = blockIdx.x + eg * gridDim.x; t < total_tiles; it += NG, t += NG * gridDim.x) {
       const int m0 = (t / P.n_tiles) * BM, n0 = (t % P.n_tiles) * P.block_n;
       if (n0 != prev_n) {
         if (prev_n >= 0) flush(prev_n);
@@ -230,15 +253,17 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       const int as = it & 1;
-      uint8_t* ob = out_buf + (size_t)(it & 1) * nch * OUT_CHUNK;
+      uint8_t* ob = out_buf + (size_t)as * nch * OUT_CHUNK;
       const uint32_t ob_u32 = smem_u32(ob);
       mbar_wait(&tmem_full[as], (it >> 1) & 1);
       tc_fence_after();
-      // the TMA store issued from this staging buffer two tiles ago must have finished reading it
-      if (et == 0) tma_store_wait_read<1>();
-      named_bar_sync(1, EPI_THREADS);
+      // this warp's previous TMA store out of the same staging rows must have finished reading them
+      if (lane == 0) {
+        if (NG == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>();
+      }
+      __syncwarp();
       // ---- pass 1: TMEM -> registers -> bf16 -> swizzled staging tile (one row per thread)
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * ACC_COLS;
+      const uint32_t taddr = tmem_base + ((uint32_t)row0 << 16) + as * ACC_COLS;
       for (int c16 = 0; c16 < (P.block_n >> 4); ++c16) {
         uint32_t r[16];
         tmem_ld_x16(taddr + c16 * 16, r);
@@ -258,9 +283,14 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);   // accumulator stage free for the MMA warp
-      named_bar_sync(1, EPI_THREADS);
-      // ---- pass 2: coalesced sweep over the staged tile: statistics (and ReLU6 mask)
+      __syncwarp();
+      // ---- pass 2: coalesced sweep over this warp's 32 staged rows: statistics (and ReLU6 mask)
       if (EMODE != E_PLAIN) {
+        uint32_t ax_u32 = 0;
+        if (EMODE == E_MASKSTATS) {
+          mbar_wait(&aux_full[as], (it >> 1) & 1);
+          ax_u32 = smem_u32(aux_buf + (size_t)as * nch * OUT_CHUNK);
+        }
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           if (c < nch) {
@@ -269,10 +299,10 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (!colok) continue;   // staging columns past the tile hold no data
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-              const int r = rbase + 16 * i;
-              const uint32_t addr = ob_u32 + c * OUT_CHUNK + r * 128 + ((p ^ (r & 7)) << 4);
+              const int r = row0 + rr + 4 * i;
+              const uint32_t off = c * OUT_CHUNK + r * 128 + ((p ^ (r & 7)) << 4);
               float x[8];
-              unpack8(lds16(addr), x);
+              unpack8(lds16(ob_u32 + off), x);
               if (EMODE == E_STATS) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
@@ -280,11 +310,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   s1[c][j] = fmaf(x[j], x[j], s1[c][j]);
                 }
               } else {
-                const int gm = m0 + r;
                 float a[8];
-                uint4 av = make_uint4(0u, 0u, 0u, 0u);
-                if (gm < P.M) av = ldg_stream(P.aux + (size_t)gm * P.ldo + col0);
-                unpack8(av, a);
+                unpack8(lds16(ax_u32 + off), a);     // rows past M were zero-filled by TMA -> masked to 0
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                   const float z = fmaf(a[j], esc[c][j], esh[c][j]);
@@ -293,86 +320,107 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   s0[c][j] += o;
                   s1[c][j] = fmaf(o, a[j], s1[c][j]);
                 }
-                sts16(addr, pack8(x));
+                sts16(ob_u32 + off, pack8(x));
               }
             }
           }
         }
-        fence_proxy_async_smem();
-        named_bar_sync(1, EPI_THREADS);
-      } else {
-        fence_proxy_async_smem();
-        named_bar_sync(1, EPI_THREADS);
+        if (EMODE == E_MASKSTATS) mbar_arrive(&aux_empty[as]);
       }
-      if (et == 0) {
-        for (int c = 0; c < nch; ++c) tma_store_2d(&tmO, ob + (size_t)c * OUT_CHUNK, n0 + c * 64, m0);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        for (int c = 0; c < nch; ++c)
+          tma_store_2d(&tmO, ob + (size_t)c * OUT_CHUNK + row0 * 128, n0 + c * 64, m0 + row0);
         tma_store_commit();
       }
     }
     if (prev_n >= 0) flush(prev_n);
-    if (et == 0) tma_store_wait_all<0>();
-  } else if (AMODE != A_TMA && warp >= 8) {
+    if (lane == 0) tma_store_wait_all<0>();
+  } else if (AMODE != A_TMA && warp >= L::kProdWarp0) {
     // =========================== A producers (register path) ===========================
-    const int pt = threadIdx.x - 256;          // 0..255
-    const int p = pt & 7, rb = pt >> 3;        // 16-byte piece p of rows rb + 32 i
+    const int pt = threadIdx.x - L::kProdWarp0 * 32;   // 0..255
+    const int p = pt & 7, rb = pt >> 3;                // 16-byte piece p of rows rb + 32 i
     int s = 0;
     uint32_t ph = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int n_iter = my_tiles * P.kc;
+    auto issue = [&](int j, uint4 (&v0)[4], uint4 (&v1)[4]) {     // global loads of iteration j = (tile, k chunk)
+      const int t = blockIdx.x + (j / P.kc) * gridDim.x;
       const int m0 = (t / P.n_tiles) * BM;
-      for (int kc = 0; kc < P.kc; ++kc) {
-        const int col = kc * KCH + p * 8;
-        const bool colok = col < P.K;
-        uint4 v0[4], v1[4];
+      const int col = (j % P.kc) * KCH + p * 8;
+      const bool colok = col < P.K;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int gm = m0 + rb + 32 * i;
-          v0[i] = make_uint4(0u, 0u, 0u, 0u);
-          v1[i] = make_uint4(0u, 0u, 0u, 0u);
-          if (colok && gm < P.M) {
-            v0[i] = ldg_stream(P.a0 + (size_t)gm * P.lda + col);
-            if (AMODE == A_BNGRAD) v1[i] = ldg_stream(P.a1 + (size_t)gm * P.lda + col);
-          }
+      for (int i = 0; i < 4; ++i) {
+        const int gm = m0 + rb + 32 * i;
+        v0[i] = make_uint4(0u, 0u, 0u, 0u);
+        v1[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (colok && gm < P.M) {
+          v0[i] = ldg_stream(P.a0 + (size_t)gm * P.lda + col);
+          if (AMODE == A_BNGRAD) v1[i] = ldg_stream(P.a1 + (size_t)gm * P.lda + col);
         }
-        float c0[8], c1[8], c2[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          c0[j] = colok ? s_acoef[col + j] : 0.f;
-          c1[j] = colok ? s_acoef[P.K + col + j] : 0.f;
-          c2[j] = (AMODE == A_BNGRAD && colok) ? s_acoef[2 * P.K + col + j] : 0.f;
-        }
-        mbar_wait(&empty[s], ph ^ 1);
-        const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int r = rb + 32 * i;
-          const bool ok = colok && (m0 + r) < P.M;
-          float x[8], y[8];
-          unpack8(v0[i], x);
-          if (AMODE == A_BNRELU) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float z = fmaf(x[j], c0[j], c1[j]);
-              if (P.a_relu6) z = relu6f(z);
-              y[j] = ok ? z : 0.f;
-            }
-          } else {
-            float g[8];
-            unpack8(v1[i], g);   // v0 = dz, v1 = raw activation
-#pragma unroll
-            for (int j = 0; j < 8; ++j) y[j] = ok ? fmaf(c0[j], x[j], fmaf(c1[j], g[j], c2[j])) : 0.f;
-          }
-          sts16(sa + r * 128 + ((p ^ (r & 7)) << 4), pack8(y));
-        }
-        fence_proxy_async_smem();
-        mbar_arrive(&full[s]);
-        if (++s == stages) { s = 0; ph ^= 1; }
       }
+    };
+    uint4 n0v[4], n1v[4];
+    if (AMODE == A_BNRELU && n_iter > 0) issue(0, n0v, n1v);     // software prefetch, one iteration ahead
+    for (int j = 0; j < n_iter; ++j) {
+      const int t = blockIdx.x + (j / P.kc) * gridDim.x;
+      const int m0 = (t / P.n_tiles) * BM;
+      const int col = (j % P.kc) * KCH + p * 8;
+      const bool colok = col < P.K;
+      uint4 v0[4], v1[4];
+      if (AMODE == A_BNRELU) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v0[i] = n0v[i];
+        if (j + 1 < n_iter) issue(j + 1, n0v, n1v);
+      } else {
+        issue(j, v0, v1);
+      }
+      float c0[8], c1[8], c2[8];
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) {
+        c0[jj] = colok ? s_acoef[col + jj] : 0.f;
+        c1[jj] = colok ? s_acoef[P.K + col + jj] : 0.f;
+        c2[jj] = (AMODE == A_BNGRAD && colok) ? s_acoef[2 * P.K + col + jj] : 0.f;
+      }
+      mbar_wait(&empty[s], ph ^ 1);
+      const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = rb + 32 * i;
+        const bool ok = colok && (m0 + r) < P.M;
+        float x[8], y[8];
+        unpack8(v0[i], x);
+        if (AMODE == A_BNRELU) {
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) {
+            float z = fmaf(x[jj], c0[jj], c1[jj]);
+            if (P.a_relu6) z = relu6f(z);
+            y[jj] = ok ? z : 0.f;
+          }
+        } else {
+          float g[8];
+          unpack8(v1[i], g);   // v0 = dz, v1 = raw activation
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) y[jj] = ok ? fmaf(c0[jj], x[jj], fmaf(c1[jj], g[jj], c2[jj])) : 0.f;
+        }
+        sts16(sa + r * 128 + ((p ^ (r & 7)) << 4), pack8(y));
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&full[s]);
+      if (++s == stages) { s = 0; ph ^= 1; }
     }
   }
 
-  // ---- teardown -------------------------------------------------------------------------------------
+  // ---- teardown: per-channel sums shared -> global, TMEM release ------------------------------------
   tc_fence_before();
   __syncthreads();
+  if (EMODE != E_PLAIN) {
+    for (int i = threadIdx.x; i < P.N; i += blockDim.x) {
+      atomicAdd(P.stats + i, s_stats[i]);
+      atomicAdd(P.stats + P.stats_stride + i, s_stats[P.N + i]);
+    }
+  }
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
@@ -385,7 +433,7 @@ int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
   // always the architectural maximum: the attribute is function-global state, and CUDA-graph replays must not
   // depend on which layer set it last
   B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  kern<<<pl.grid, AMODE == A_TMA ? 256 : 512, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmO, pl.p);
+  kern<<<pl.grid, Layout<AMODE>::kThreads, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmO, pl.tmX, pl.p);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -447,8 +495,10 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   if (emode != E_PLAIN) B200DP_REQUIRE(stats != nullptr, "pw_gemm: stats pointer missing");
   if (emode == E_MASKSTATS) B200DP_REQUIRE(aux != nullptr && ecoef != nullptr, "pw_gemm: E_MASKSTATS needs aux + ecoef");
   const int nch = (p.block_n + 63) / 64;
-  const size_t fixed = 2 * (size_t)nch * OUT_CHUNK + ((amode == A_BNRELU ? 2 : amode == A_BNGRAD ? 3 : 0) * (size_t)K +
-                       (emode == E_MASKSTATS ? 2 : 0) * (size_t)N + 256) * 4 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024;
+  const size_t fixed = (emode == E_MASKSTATS ? 4 : 2) * (size_t)nch * OUT_CHUNK +
+                       ((amode == A_BNRELU ? 2 : amode == A_BNGRAD ? 3 : 0) * (size_t)K +
+                        (emode == E_MASKSTATS ? 4 : emode == E_STATS ? 2 : 0) * (size_t)N + 8) * 4 +
+                       (2 * MAX_STAGES + 8) * 8 + 16 + 1024;
   const size_t per_stage = A_STAGE + (size_t)p.block_n * 128;
   const size_t budget = 220 * 1024;
   B200DP_REQUIRE(fixed + 2 * per_stage <= budget, "pw_gemm: shared memory budget exceeded (K=%d N=%d)", K, N);
@@ -466,7 +516,13 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
     pl->tmA = CUtensorMap{};
   }
   if (int rc = make_tmap_2d_bf16(&pl->tmB, w, N, K, K, KCH, p.block_n)) return rc;
-  if (int rc = make_tmap_2d_bf16(&pl->tmO, out, M, N, ldo, 64, BM)) return rc;
+  if (int rc = make_tmap_2d_bf16(&pl->tmO, out, M, N, ldo, 64, 32)) return rc;     // each epilogue warp stores its 32 rows
+  if (emode == E_MASKSTATS) {
+    B200DP_REQUIRE(amode == A_TMA, "pw_gemm: E_MASKSTATS is implemented for the TMA A path only");
+    if (int rc = make_tmap_2d_bf16(&pl->tmX, aux, M, N, ldo, 64, BM)) return rc;
+  } else {
+    pl->tmX = CUtensorMap{};
+  }
   return B200DP_OK;
 }
 

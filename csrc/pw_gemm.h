@@ -26,7 +26,7 @@ struct PwGemmParams {
 };
 
 struct PwGemmPlan {
-  CUtensorMap tmA, tmB, tmO;
+  CUtensorMap tmA, tmB, tmO, tmX;
   PwGemmParams p;
   int amode, emode, grid;
   size_t smem_bytes;
