@@ -45,7 +45,7 @@ constexpr int OUT_CHUNK = BM * 128;     // one 64-column block of the output til
 constexpr int ACC_COLS = 128;           // TMEM columns per accumulator stage
 constexpr int TMEM_COLS = 256;
 constexpr int EPI_THREADS = 128;
-constexpr int PROD_THREADS = 256;
+constexpr int PROD_THREADS = 128;
 constexpr int MAX_STAGES = 8;
 
 struct Smem {
@@ -72,12 +72,13 @@ __device__ __forceinline__ uint4 lds16(uint32_t addr) {
   return v;
 }
 
-// Thread layout.  A_TMA kernels: 4 control warps + 2 epilogue groups of 4 warps (384 threads); each group owns one
-// TMEM accumulator stage, one staging buffer and (E_MASKSTATS) one aux buffer, so two tiles drain concurrently.
-// Register-path kernels: 4 control + 4 epilogue + 8 producer warps (512 threads).
+// Thread layout: 4 control warps + 2 epilogue groups of 4 warps; each group owns one TMEM accumulator stage, one
+// staging buffer and (E_MASKSTATS) one aux buffer, so two tiles drain concurrently.  A_BNRELU / A_BNGRAD add 4
+// transform warps: ALL global->shared traffic is TMA (deeply pipelined, no registers held across the latency); the
+// transform warps rewrite the landed raw tile in place (shared -> registers -> BatchNorm math -> shared).
 template <int AMODE>
 struct Layout {
-  static constexpr int kEpiGroups = AMODE == A_TMA ? 2 : 1;
+  static constexpr int kEpiGroups = 2;
   static constexpr int kProdWarp0 = 4 + 4 * kEpiGroups;
   static constexpr int kThreads = AMODE == A_TMA ? 384 : 512;
 };
@@ -85,6 +86,8 @@ struct Layout {
 template <int AMODE, int EMODE>
 __global__ void __launch_bounds__(Layout<AMODE>::kThreads, 1)
 pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmAt, const __grid_constant__ CUtensorMap tmBt,
+               const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA2t,
                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmX,
                const __grid_constant__ PwGemmParams P) {
   using L = Layout<AMODE>;
@@ -96,7 +99,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int b_stage = P.block_n * 128;
   const int nch = (P.block_n + 63) >> 6;
   uint8_t* stage_a = base;
-  uint8_t* stage_b = stage_a + (size_t)stages * A_STAGE;
+  uint8_t* stage_a2 = stage_a + (size_t)stages * A_STAGE;                      // A_BNGRAD: raw x tile next to raw dz
+  uint8_t* stage_b = stage_a2 + (AMODE == A_BNGRAD ? (size_t)stages * A_STAGE : 0);
   uint8_t* out_buf = stage_b + (size_t)stages * b_stage;                       // 2 x nch x 16 KB
   uint8_t* aux_buf = out_buf + 2 * (size_t)nch * OUT_CHUNK;                    // 2 x nch x 16 KB (E_MASKSTATS)
   float* s_acoef = reinterpret_cast<float*>(aux_buf + (EMODE == E_MASKSTATS ? 2 * (size_t)nch * OUT_CHUNK : 0));
@@ -112,7 +116,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tmem_empty = tmem_full + 2;
   uint64_t* aux_full = tmem_empty + 2;
   uint64_t* aux_empty = aux_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_empty + 2);
+  uint64_t* raw_full = aux_empty + 2;                                          // [MAX_STAGES] raw A tile(s) landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(raw_full + MAX_STAGES);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -121,14 +126,18 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // ---- one-time set-up ---------------------------------------------------------------------------
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmBt);
     prefetch_tmap(&tmO);
-    if (AMODE == A_TMA) prefetch_tmap(&tmA);
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmAt);
+    if (AMODE == A_BNGRAD) { prefetch_tmap(&tmA2); prefetch_tmap(&tmA2t); }
     if (EMODE == E_MASKSTATS) prefetch_tmap(&tmX);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full[s], AMODE == A_TMA ? 1 : 1 + PROD_THREADS);
       mbar_init(&empty[s], 1);
+      mbar_init(&raw_full[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
@@ -150,7 +159,6 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0) {
     // =========================== TMA producer ===========================
     if (lane == 0) {
-      const uint32_t tx = (AMODE == A_TMA ? A_STAGE : 0) + b_stage;
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
@@ -164,10 +172,23 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tma_load_2d(aux_buf + ((size_t)ab * nch + c) * OUT_CHUNK, &tmX, &aux_full[ab], n0 + 64 * c, m0);
         }
         for (int kc = 0; kc < P.kc; ++kc) {
+          // the last K chunk may be narrower than 64: its box is exactly that wide (a box that hangs over the
+          // tensor edge makes TMA crawl), and lands in the matching 32B / 64B swizzle layout
+          const bool last = kc == P.kc - 1;
+          const int w = last ? P.tail_w : KCH;
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full[s], tx);
-          if (AMODE == A_TMA) tma_load_2d(stage_a + (size_t)s * A_STAGE, &tmA, &full[s], kc * KCH, m0);
-          tma_load_2d(stage_b + (size_t)s * b_stage, &tmB, &full[s], kc * KCH, n0);
+          if (AMODE == A_TMA) {
+            mbar_arrive_expect_tx(&full[s], (uint32_t)(BM + P.block_n) * w * 2);
+            tma_load_2d(stage_a + (size_t)s * A_STAGE, last ? &tmAt : &tmA, &full[s], kc * KCH, m0);
+          } else {
+            // raw tile(s) -> raw_full (consumed by the transform warps); weights -> full (consumed by the MMA)
+            mbar_arrive_expect_tx(&raw_full[s], (uint32_t)BM * w * 2 * (AMODE == A_BNGRAD ? 2 : 1));
+            tma_load_2d(stage_a + (size_t)s * A_STAGE, last ? &tmAt : &tmA, &raw_full[s], kc * KCH, m0);
+            if (AMODE == A_BNGRAD)
+              tma_load_2d(stage_a2 + (size_t)s * A_STAGE, last ? &tmA2t : &tmA2, &raw_full[s], kc * KCH, m0);
+            mbar_arrive_expect_tx(&full[s], (uint32_t)P.block_n * w * 2);
+          }
+          tma_load_2d(stage_b + (size_t)s * b_stage, last ? &tmBt : &tmB, &full[s], kc * KCH, n0);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
@@ -187,10 +208,10 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kc = 0; kc < P.kc; ++kc) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
-          const uint64_t da = umma_desc_kmajor_sw128(smem_u32(stage_a + (size_t)s * A_STAGE));
-          const uint64_t db = umma_desc_kmajor_sw128(smem_u32(stage_b + (size_t)s * b_stage));
-          const int rem = P.K - kc * KCH;
-          const int ksteps = rem >= KCH ? 4 : (rem >> 4);
+          const int w = kc == P.kc - 1 ? P.tail_w : KCH;
+          const uint64_t da = umma_desc_kmajor(smem_u32(stage_a + (size_t)s * A_STAGE), w);
+          const uint64_t db = umma_desc_kmajor(smem_u32(stage_b + (size_t)s * b_stage), w);
+          const int ksteps = w >> 4;
           for (int k = 0; k < ksteps; ++k)
             umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kc | k) != 0);
           umma_commit(&empty[s]);   // smem slot reusable once these MMAs have read it
@@ -338,77 +359,56 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (prev_n >= 0) flush(prev_n);
     if (lane == 0) tma_store_wait_all<0>();
   } else if (AMODE != A_TMA && warp >= L::kProdWarp0) {
-    // =========================== A producers (register path) ===========================
-    const int pt = threadIdx.x - L::kProdWarp0 * 32;   // 0..255
-    const int p = pt & 7, rb = pt >> 3;                // 16-byte piece p of rows rb + 32 i
+    // =========================== transform warps: raw tile -> operand tile, in place ===========================
+    const int pt = threadIdx.x - L::kProdWarp0 * 32;   // 0..127
+    const int p = pt & 7, rb = pt >> 3;                // 16-byte piece p of rows rb + 16 i
     int s = 0;
     uint32_t ph = 0;
-    const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-    const int n_iter = my_tiles * P.kc;
-    auto issue = [&](int j, uint4 (&v0)[4], uint4 (&v1)[4]) {     // global loads of iteration j = (tile, k chunk)
-      const int t = blockIdx.x + (j / P.kc) * gridDim.x;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int m0 = (t / P.n_tiles) * BM;
-      const int col = (j % P.kc) * KCH + p * 8;
-      const bool colok = col < P.K;
+      for (int kc = 0; kc < P.kc; ++kc) {
+        const int w = kc == P.kc - 1 ? P.tail_w : KCH;   // chunk width: row pitch 2w bytes, w/8 pieces per row
+        const int wsh = w == 64 ? 0 : (w == 32 ? 1 : 2);
+        const int col = kc * KCH + p * 8;
+        const bool colok = p * 8 < w;
+        float c0[8], c1[8], c2[8];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int gm = m0 + rb + 32 * i;
-        v0[i] = make_uint4(0u, 0u, 0u, 0u);
-        v1[i] = make_uint4(0u, 0u, 0u, 0u);
-        if (colok && gm < P.M) {
-          v0[i] = ldg_stream(P.a0 + (size_t)gm * P.lda + col);
-          if (AMODE == A_BNGRAD) v1[i] = ldg_stream(P.a1 + (size_t)gm * P.lda + col);
+        for (int jj = 0; jj < 8; ++jj) {
+          c0[jj] = colok ? s_acoef[col + jj] : 0.f;
+          c1[jj] = colok ? s_acoef[P.K + col + jj] : 0.f;
+          c2[jj] = (AMODE == A_BNGRAD && colok) ? s_acoef[2 * P.K + col + jj] : 0.f;
         }
-      }
-    };
-    uint4 n0v[4], n1v[4];
-    if (AMODE == A_BNRELU && n_iter > 0) issue(0, n0v, n1v);     // software prefetch, one iteration ahead
-    for (int j = 0; j < n_iter; ++j) {
-      const int t = blockIdx.x + (j / P.kc) * gridDim.x;
-      const int m0 = (t / P.n_tiles) * BM;
-      const int col = (j % P.kc) * KCH + p * 8;
-      const bool colok = col < P.K;
-      uint4 v0[4], v1[4];
-      if (AMODE == A_BNRELU) {
+        mbar_wait(&raw_full[s], ph);
+        const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
+        const uint32_t sx = smem_u32(stage_a2 + (size_t)s * A_STAGE);
+        if (colok) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v0[i] = n0v[i];
-        if (j + 1 < n_iter) issue(j + 1, n0v, n1v);
-      } else {
-        issue(j, v0, v1);
-      }
-      float c0[8], c1[8], c2[8];
+          for (int i = 0; i < 8; ++i) {
+            const int r = rb + 16 * i;
+            const uint32_t off = r * 2 * w + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
+            const bool ok = (m0 + r) < P.M;            // rows past M were zero-filled by TMA and must stay zero
+            float x[8], y[8];
+            unpack8(lds16(sa + off), x);
+            if (AMODE == A_BNRELU) {
 #pragma unroll
-      for (int jj = 0; jj < 8; ++jj) {
-        c0[jj] = colok ? s_acoef[col + jj] : 0.f;
-        c1[jj] = colok ? s_acoef[P.K + col + jj] : 0.f;
-        c2[jj] = (AMODE == A_BNGRAD && colok) ? s_acoef[2 * P.K + col + jj] : 0.f;
-      }
-      mbar_wait(&empty[s], ph ^ 1);
-      const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
+              for (int jj = 0; jj < 8; ++jj) {
+                float z = fmaf(x[jj], c0[jj], c1[jj]);
+                if (P.a_relu6) z = relu6f(z);
+                y[jj] = ok ? z : 0.f;
+              }
+            } else {
+              float g[8];
+              unpack8(lds16(sx + off), g);             // sa = dz, sx = raw activation
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int r = rb + 32 * i;
-        const bool ok = colok && (m0 + r) < P.M;
-        float x[8], y[8];
-        unpack8(v0[i], x);
-        if (AMODE == A_BNRELU) {
-#pragma unroll
-          for (int jj = 0; jj < 8; ++jj) {
-            float z = fmaf(x[jj], c0[jj], c1[jj]);
-            if (P.a_relu6) z = relu6f(z);
-            y[jj] = ok ? z : 0.f;
+              for (int jj = 0; jj < 8; ++jj) y[jj] = ok ? fmaf(c0[jj], x[jj], fmaf(c1[jj], g[jj], c2[jj])) : 0.f;
+            }
+            sts16(sa + off, pack8(y));
           }
-        } else {
-          float g[8];
-          unpack8(v1[i], g);   // v0 = dz, v1 = raw activation
-#pragma unroll
-          for (int jj = 0; jj < 8; ++jj) y[jj] = ok ? fmaf(c0[jj], x[jj], fmaf(c1[jj], g[jj], c2[jj])) : 0.f;
         }
-        sts16(sa + r * 128 + ((p ^ (r & 7)) << 4), pack8(y));
+        fence_proxy_async_smem();
+        mbar_arrive(&full[s]);
+        if (++s == stages) { s = 0; ph ^= 1; }
       }
-      fence_proxy_async_smem();
-      mbar_arrive(&full[s]);
-      if (++s == stages) { s = 0; ph ^= 1; }
     }
   }
 
@@ -433,7 +433,7 @@ int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
   // always the architectural maximum: the attribute is function-global state, and CUDA-graph replays must not
   // depend on which layer set it last
   B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  kern<<<pl.grid, Layout<AMODE>::kThreads, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmO, pl.tmX, pl.p);
+  kern<<<pl.grid, Layout<AMODE>::kThreads, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmAt, pl.tmBt, pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -441,7 +441,7 @@ int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
 }  // namespace
 
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                      uint32_t box_cols, uint32_t box_rows) {
+                      uint32_t box_cols, uint32_t box_rows, int swizzle_bytes) {
   typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -461,7 +461,9 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) for rows=%llu cols=%llu ld=%llu box=%ux%u base=%p", (int)r,
@@ -498,8 +500,8 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   const size_t fixed = (emode == E_MASKSTATS ? 4 : 2) * (size_t)nch * OUT_CHUNK +
                        ((amode == A_BNRELU ? 2 : amode == A_BNGRAD ? 3 : 0) * (size_t)K +
                         (emode == E_MASKSTATS ? 4 : emode == E_STATS ? 2 : 0) * (size_t)N + 8) * 4 +
-                       (2 * MAX_STAGES + 8) * 8 + 16 + 1024;
-  const size_t per_stage = A_STAGE + (size_t)p.block_n * 128;
+                       (3 * MAX_STAGES + 8) * 8 + 16 + 1024;
+  const size_t per_stage = (amode == A_BNGRAD ? 2 : 1) * (size_t)A_STAGE + (size_t)p.block_n * 128;
   const size_t budget = 220 * 1024;
   B200DP_REQUIRE(fixed + 2 * per_stage <= budget, "pw_gemm: shared memory budget exceeded (K=%d N=%d)", K, N);
   int stages = (int)((budget - fixed) / per_stage);
@@ -510,16 +512,26 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   const int tiles = p.m_tiles * p.n_tiles;
   const int cap = max_ctas > 0 ? max_ctas : num_sms();
   pl->grid = tiles < cap ? tiles : cap;
-  if (amode == A_TMA) {
-    if (int rc = make_tmap_2d_bf16(&pl->tmA, a_tma, M, K, lda, KCH, BM)) return rc;
+  const int tail = K % KCH;
+  B200DP_REQUIRE(tail == 0 || tail == 16 || tail == 32, "pw_gemm: K %% 64 must be 0, 16 or 32 (K=%d)", K);
+  p.tail_w = tail == 0 ? KCH : tail;
+  const uint32_t wfull = K >= KCH ? KCH : p.tail_w;          // box width of the full-chunk maps (unused when K < 64)
+  const void* a_first = amode == A_TMA ? a_tma : a0;       // register modes: raw tiles also arrive by TMA
+  if (int rc = make_tmap_2d_bf16(&pl->tmA, a_first, M, K, lda, wfull, BM, wfull * 2)) return rc;
+  if (int rc = make_tmap_2d_bf16(&pl->tmAt, a_first, M, K, lda, p.tail_w, BM, p.tail_w * 2)) return rc;
+  if (amode == A_BNGRAD) {
+    if (int rc = make_tmap_2d_bf16(&pl->tmA2, a1, M, K, lda, wfull, BM, wfull * 2)) return rc;
+    if (int rc = make_tmap_2d_bf16(&pl->tmA2t, a1, M, K, lda, p.tail_w, BM, p.tail_w * 2)) return rc;
   } else {
-    pl->tmA = CUtensorMap{};
+    pl->tmA2 = CUtensorMap{};
+    pl->tmA2t = CUtensorMap{};
   }
-  if (int rc = make_tmap_2d_bf16(&pl->tmB, w, N, K, K, KCH, p.block_n)) return rc;
-  if (int rc = make_tmap_2d_bf16(&pl->tmO, out, M, N, ldo, 64, 32)) return rc;     // each epilogue warp stores its 32 rows
+  if (int rc = make_tmap_2d_bf16(&pl->tmB, w, N, K, K, wfull, p.block_n, wfull * 2)) return rc;
+  if (int rc = make_tmap_2d_bf16(&pl->tmBt, w, N, K, K, p.tail_w, p.block_n, p.tail_w * 2)) return rc;
+  if (int rc = make_tmap_2d_bf16(&pl->tmO, out, M, N, ldo, 64, 32, 128)) return rc;     // each epilogue warp stores its 32 rows
   if (emode == E_MASKSTATS) {
     B200DP_REQUIRE(amode == A_TMA, "pw_gemm: E_MASKSTATS is implemented for the TMA A path only");
-    if (int rc = make_tmap_2d_bf16(&pl->tmX, aux, M, N, ldo, 64, BM)) return rc;
+    if (int rc = make_tmap_2d_bf16(&pl->tmX, aux, M, N, ldo, 64, BM, 128)) return rc;
   } else {
     pl->tmX = CUtensorMap{};
   }

@@ -15,6 +15,7 @@ struct PwGemmParams {
   int M, N, K;                  // rows, output channels, input channels (channels are multiples of 16)
   int lda, ldo;                 // row pitches (elements) of the register-path A sources / of out and aux
   int block_n, n_tiles, m_tiles, kc, stages;
+  int tail_w;                   // width of the last K chunk: 16, 32 or 64 elements
   const __nv_bfloat16* a0;      // A_BNRELU: raw activation          A_BNGRAD: dz
   const __nv_bfloat16* a1;      //                                    A_BNGRAD: raw activation x
   const float* acoef;           // A_BNRELU: [2][K] scale, shift      A_BNGRAD: [3][K] ca, cb, cc
@@ -26,7 +27,7 @@ struct PwGemmParams {
 };
 
 struct PwGemmPlan {
-  CUtensorMap tmA, tmB, tmO, tmX;
+  CUtensorMap tmA, tmB, tmAt, tmBt, tmA2, tmA2t, tmO, tmX;   // At/Bt: maps for the (possibly narrower) last K chunk
   PwGemmParams p;
   int amode, emode, grid;
   size_t smem_bytes;
@@ -39,6 +40,6 @@ int pw_gemm_launch(const PwGemmPlan& pl, cudaStream_t s);
 
 // 2-D bf16 row-major tensor map [rows][cols] (row pitch `ld` elements), box {box_cols, box_rows}, 128-byte swizzle.
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                      uint32_t box_cols, uint32_t box_rows);
+                      uint32_t box_cols, uint32_t box_rows, int swizzle_bytes = 128);
 
 }  // namespace b200dp

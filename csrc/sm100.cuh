@@ -150,6 +150,17 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;
   return d;
 }
+// Same, for a chunk of w = 16 / 32 / 64 elements per row: rows of 2w bytes with the 32 / 64 / 128-byte swizzle
+// (layout type 6 / 4 / 2), 8-row groups 16w bytes apart.
+__device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t smem_addr, int w) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)((16 * w) >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)(w == 64 ? 2 : (w == 32 ? 4 : 6)) << 61;
+  return d;
+}
 // MN-major bf16 operand (the contiguous direction is M or N): 64-element (128 B) lines along MN, one
 // line per K index, 128-byte swizzle in groups of 8 K-lines.  `lbo_bytes` = distance between
 // consecutive 64-wide MN blocks, stride byte offset = 1024 B between groups of 8 K-lines.
@@ -172,11 +183,5 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_ma
 }
 
 }  // namespace sm100
-
-// ---- host: tensor maps ----------------------------------------------------------------------------------
-// 2-D bf16 row-major tensor [rows][cols] (cols contiguous, row pitch `ld` elements), box {box_cols, box_rows},
-// 128-byte swizzle, out-of-bounds reads give zeros and out-of-bounds writes are dropped.
-int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                      uint32_t box_cols, uint32_t box_rows);
 
 }  // namespace b200dp
