@@ -2,20 +2,25 @@
 //
 //   dW[n][k] += sum_m G[m][n] * A[m][k]          (fp32, accumulated into the flat gradient arena)
 //
-// Both operands are [rows m][channels] NHWC tensors, i.e. the reduction index m is the *slow* index in
-// memory: they are MN-major UMMA operands.  A tile of 64 rows x 64 channels lands in shared memory as
-// 64 lines of 128 bytes with the 128-byte swizzle (exactly what a TMA box {64 ch, 64 rows} writes), and
-// tcgen05.mma consumes it with the "MN-major" descriptor bits set -- no transpose pass, no im2col.
+// Both operands are [rows m][channels] NHWC tensors, i.e. the reduction index m is the *slow* index in memory:
+// they are MN-major UMMA operands.  A TMA box {64 channels, MK rows} lands in shared memory as MK lines of 128
+// bytes with the 128-byte swizzle, which IS the canonical MN-major tile -- no transpose pass exists anywhere.
 //
-//   D[k (128 TMEM lanes)][n (<= 256 columns)] += P[m x 128 k-channels]^T * Q[m x n-channels]
-//   P = A side (conv input),  Q = G side (gradient of the conv output)
-//
-// One side of every wgrad needs a BatchNorm transform that cannot be materialised cheaply:
-//   MODE 0 (expand / last conv):  P = finished activation, pure, via TMA;   Q = ca*dz + cb*y_raw + cc on load
-//   MODE 1 (project conv):        P = relu6(scale*d_raw + shift) on load;   Q = materialised gradient, via TMA
-// The transformed side is produced by 8 warps (global -> registers -> swizzled smem), the other by TMA.
-// Work items = (128-wide k chunk) x (n chunk) x (split of the m range); each item's 128 x n fp32 tile is
-// added to dW with coalesced red.global.add.f32 (lane = k is the contiguous index of dW).
+// Every 1x1 conv in MobileNetV2 has one wide side ("hidden": 32..1280 channels) and one narrow side (16..320):
+//   MODE 0 (expand / last conv):  hidden = G side, formed as ca*dz + cb*y_raw + cc;  narrow = A side (block input)
+//   MODE 1 (project conv):        hidden = A side, formed as relu6(scale*d_raw + shift);  narrow = G side (dp)
+// The hidden side is the UMMA M operand (128 TMEM lanes), the narrow side the N operand:
+//   D[hidden chunk (128 lanes)][narrow chunk (<= 256 columns)] += H[m x 128]^T * Q[m x nq]
+// Global->shared traffic is cp.async (LDGSTS, 16 bytes per thread) issued by 4 loader warps straight into the
+// swizzled operand layout and tracked by mbarriers (cp.async.mbarrier.arrive.noinc): measured here, TMA costs
+// ~4.5-8 cycles per box ROW whatever its width, which caps narrow NHWC rows (32-256 B) far below the HBM roofline,
+// while LDGSTS has no per-row cost and holds no registers across the latency.  The raw hidden tile(s) are then
+// rewritten in place by 4 transform warps (shared -> registers -> BatchNorm math -> shared, fence.proxy.async);
+// the narrow side is consumed as loaded.  A tail of 16 / 32 channels uses lines of 32 / 64 bytes with the matching
+// swizzle and, for the N operand, its own MMA into the next TMEM columns; missing lanes of a tail M chunk are zero
+// blocks in shared memory.
+// Work items = (hidden chunk) x (narrow chunk) x (split of the m range); each item's fp32 tile is added to dW with
+// red.global.add (vectorised v4 when the narrow index is the contiguous one).
 // Reference behaviour replaced: cuDNN convolution-backward-filter for the 34 1x1 convs.
 #include "common.cuh"
 #include "pw_gemm.h"
@@ -26,23 +31,24 @@ namespace {
 
 using namespace sm100;
 
-constexpr int MK = 64;                 // m rows per pipeline stage
-constexpr int BLK = MK * 128;          // one 64-channel block of a stage: 64 lines x 128 B
-constexpr int P_BLKS = 2;              // 128 k-channels
-constexpr int MAXQ_BLKS = 4;           // up to 256 n-channels
 constexpr int MAX_STAGES = 6;
-constexpr int PROD_THREADS = 256;
+constexpr int XF_THREADS = 128;        // transform warps 8..11
+constexpr int LD_THREADS = 128;        // loader warps 12..15
 constexpr int TMEM_COLS = 512;         // 2 accumulator stages x 256 columns
 
 struct WgradParams {
-  int M, N, K;                 // rows, G channels (cout), A channels (cin)
-  int lda, ldg, ldw;           // row pitches (elements) of A-side, G-side tensors and of dW
-  int nq, qblks;               // n-chunk width (multiple of 16, <= 256) and its number of 64-wide blocks
-  int kchunks, nchunks, msplit, chunks_per_split, stages;
-  const __nv_bfloat16* t0;     // transformed side, first source  (MODE 0: dz      MODE 1: d_raw)
-  const __nv_bfloat16* t1;     // transformed side, second source (MODE 0: y_raw)
-  const float* coef;           // MODE 0: [3][N] ca, cb, cc     MODE 1: [2][K] scale, shift
-  float* dw;                   // [N][ldw] fp32
+  int M;                       // rows
+  int hidden, narrow;          // channel counts of the wide / narrow side
+  int ldh, ldq, ldw;           // row pitches (elements): hidden tensors, narrow tensor, dW
+  int mk;                      // m rows per pipeline stage (64 / 128 / 256)
+  int nq, nqf, nqp, qchunks;   // narrow chunk width = nqf (full 64-blocks) + nqp (16/32 tail), number of chunks
+  int n128, tail;              // hidden = 128 * n128 + tail
+  int hchunks, msplit, chunks_per_split, stages;
+  const float* coef;           // MODE 0: [3][hidden] ca, cb, cc     MODE 1: [2][hidden] scale, shift
+  float* dw;
+  const __nv_bfloat16* t0;     // hidden raw tensor 0 (MODE 0: dz, MODE 1: d_raw)
+  const __nv_bfloat16* t1;     // hidden raw tensor 1 (MODE 0: y_raw)
+  const __nv_bfloat16* qsrc;   // narrow tensor
 };
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
@@ -53,32 +59,63 @@ __device__ __forceinline__ void sts16(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
+__device__ __forceinline__ uint4 lds16(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// MN-major operand: lines of (16 * w / 8) bytes holding w consecutive channels, one line per m row, swizzle by line
+// width; blocks of w channels are `lbo` bytes apart, groups of 8 lines are 8 lines apart.
+__device__ __forceinline__ uint64_t desc_mn(uint32_t addr, int w, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((16 * w) >> 4) << 32;                 // 8 lines x 2w bytes
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)(w == 64 ? 2 : (w == 32 ? 4 : 6)) << 61;
+  return d;
+}
+// 16-byte asynchronous global->shared copy (zero-fills when src_bytes == 0) and its mbarrier completion hook
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(512, 1)
-pw_wgrad_kernel(const __grid_constant__ CUtensorMap tmPure, const __grid_constant__ WgradParams P) {
+pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int MK = P.mk;
+  const int h_bytes = MK * 256;                                     // hidden tile: always 128 channels wide
+  const int q_bytes = MK * P.nq * 2;
+  const int stage_bytes = h_bytes * (MODE == 0 ? 2 : 1) + ((q_bytes + 1023) & ~1023);
   const int stages = P.stages;
-  const int stage_bytes = (P_BLKS + P.qblks) * BLK;
   float* s_coef = reinterpret_cast<float*>(base + (size_t)stages * stage_bytes);
-  const int ncoef = MODE == 0 ? 3 * P.N : 2 * P.K;
+  const int ncoef = (MODE == 0 ? 3 : 2) * P.hidden;
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_coef + ((ncoef + 3) & ~3));
   uint64_t* full = bars;
   uint64_t* empty = bars + MAX_STAGES;
-  uint64_t* tmem_full = bars + 2 * MAX_STAGES;
+  uint64_t* raw_full = bars + 2 * MAX_STAGES;
+  uint64_t* tmem_full = bars + 3 * MAX_STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int items = P.kchunks * P.nchunks * P.msplit;
+  const int items = P.hchunks * P.qchunks * P.msplit;
   const int total_chunks = (P.M + MK - 1) / MK;
 
-  if (warp == 0 && lane == 0) prefetch_tmap(&tmPure);
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full[s], 1 + PROD_THREADS);
+      mbar_init(&full[s], XF_THREADS);
       mbar_init(&empty[s], 1);
+      mbar_init(&raw_full[s], LD_THREADS);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
@@ -93,63 +130,55 @@ pw_wgrad_kernel(const __grid_constant__ CUtensorMap tmPure, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // item -> (k chunk, n chunk, m split); k fastest so concurrently running CTAs share the Q-side rows in L2
-  auto decode = [&](int item, int& k0, int& n0, int& c_lo, int& c_hi) {
-    const int kc = item % P.kchunks;
-    const int nc = (item / P.kchunks) % P.nchunks;
-    const int ms = item / (P.kchunks * P.nchunks);
-    k0 = kc * 128;
-    n0 = nc * P.nq;
+  // item -> hidden chunk (h0, hw), narrow chunk q0, m-chunk range.  Hidden chunk fastest: CTAs running side by
+  // side read the same narrow rows, which stay in L2.
+  auto decode = [&](int item, int& h0, int& hw, int& q0, int& c_lo, int& c_hi) {
+    const int hc = item % P.hchunks;
+    const int qc = (item / P.hchunks) % P.qchunks;
+    const int ms = item / (P.hchunks * P.qchunks);
+    if (hc < P.n128) { h0 = hc * 128; hw = 128; }
+    else {
+      const int j = hc - P.n128;
+      h0 = P.n128 * 128;
+      if (P.tail >= 64) { if (j == 0) hw = 64; else { h0 += 64; hw = P.tail - 64; } }
+      else hw = P.tail;
+    }
+    q0 = qc * P.nq;
     c_lo = ms * P.chunks_per_split;
     c_hi = min(c_lo + P.chunks_per_split, total_chunks);
   };
 
   if (warp == 0) {
-    // =========================== TMA producer (pure side) ===========================
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      const uint32_t tx = (MODE == 0 ? P_BLKS : P.qblks) * BLK;
-      for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        int k0, n0, c_lo, c_hi;
-        decode(item, k0, n0, c_lo, c_hi);
-        for (int c = c_lo; c < c_hi; ++c) {
-          mbar_wait(&empty[s], ph ^ 1);
-          mbar_arrive_expect_tx(&full[s], tx);
-          uint8_t* st = base + (size_t)s * stage_bytes;
-          if (MODE == 0) {
-            for (int b = 0; b < P_BLKS; ++b) tma_load_2d(st + b * BLK, &tmPure, &full[s], k0 + 64 * b, c * MK);
-          } else {
-            for (int b = 0; b < P.qblks; ++b)
-              tma_load_2d(st + (P_BLKS + b) * BLK, &tmPure, &full[s], n0 + 64 * b, c * MK);
-          }
-          if (++s == stages) { s = 0; ph ^= 1; }
-        }
-      }
-    }
+    // (idle: loads are issued by the loader warps below)
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
     if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(128, P.nq, 1, 1);
+      const uint32_t idesc_f = umma_idesc_bf16(128, P.nqf ? P.nqf : 16, 1, 1);
+      const uint32_t idesc_p = umma_idesc_bf16(128, P.nqp ? P.nqp : 16, 1, 1);
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
       for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
-        int k0, n0, c_lo, c_hi;
-        decode(item, k0, n0, c_lo, c_hi);
+        int h0, hw, q0, c_lo, c_hi;
+        decode(item, h0, hw, q0, c_lo, c_hi);
         const int as = it & 1;
         mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * 256;
+        const int wh = hw >= 64 ? 64 : hw;                     // channels per hidden block
         for (int c = c_lo; c < c_hi; ++c) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
           const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
-          const uint64_t dp = umma_desc_mnmajor_sw128(st, BLK);
-          const uint64_t dq = umma_desc_mnmajor_sw128(st + P_BLKS * BLK, BLK);
-#pragma unroll
-          for (int k = 0; k < MK / 16; ++k)   // 16 m-rows per MMA = 2 swizzle groups = 2048 B
-            umma_bf16(d_tmem, dp + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, (c > c_lo) | (k > 0));
+          const uint32_t sq = st + h_bytes * (MODE == 0 ? 2 : 1);
+          const uint64_t dh = desc_mn(st, wh, (uint32_t)MK * 2 * wh);
+          const uint64_t dqf = desc_mn(sq, 64, (uint32_t)MK * 128);
+          const uint64_t dqp = desc_mn(sq + (P.nqf >> 6) * MK * 128, P.nqp ? P.nqp : 16, (uint32_t)MK * 128);
+          for (int k = 0; k < (MK >> 4); ++k) {                // 16 m-rows per MMA
+            const uint32_t acc = (c > c_lo) | (k > 0);
+            if (P.nqf) umma_bf16(d_tmem, dh + (uint64_t)(2 * wh * k), dqf + (uint64_t)(128 * k), idesc_f, acc);
+            if (P.nqp) umma_bf16(d_tmem + P.nqf, dh + (uint64_t)(2 * wh * k), dqp + (uint64_t)(2 * P.nqp * k), idesc_p, acc);
+          }
           umma_commit(&empty[s]);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
@@ -161,86 +190,140 @@ pw_wgrad_kernel(const __grid_constant__ CUtensorMap tmPure, const __grid_constan
     const int q = warp & 3;
     int it = 0;
     for (int item = blockIdx.x; item < items; item += gridDim.x, ++it) {
-      int k0, n0, c_lo, c_hi;
-      decode(item, k0, n0, c_lo, c_hi);
+      int h0, hw, q0, c_lo, c_hi;
+      decode(item, h0, hw, q0, c_lo, c_hi);
       const int as = it & 1;
       mbar_wait(&tmem_full[as], (it >> 1) & 1);
       tc_fence_after();
-      const int k = k0 + q * 32 + lane;
+      const int hl = q * 32 + lane;                    // lane within the hidden chunk
+      const bool ok = hl < hw && c_hi > c_lo;
+      const int h = h0 + hl;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * 256;
       for (int c16 = 0; c16 < (P.nq >> 4); ++c16) {
         uint32_t r[16];
         tmem_ld_x16(taddr + c16 * 16, r);
         tmem_ld_wait();
-        if (k < P.K && c_hi > c_lo) {
+        if (ok) {
+          const int qq = q0 + c16 * 16;
+          if (MODE == 0) {           // dW[n = hidden][k = narrow]: this lane's row, 16 consecutive k
+            float* dst = P.dw + (size_t)h * P.ldw + qq;
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int n = n0 + c16 * 16 + j;
-            if (n < P.N) atomicAdd(P.dw + (size_t)n * P.ldw + k, __uint_as_float(r[j]));
+            for (int j = 0; j < 16; j += 4)
+              red_add_v4(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                         __uint_as_float(r[j + 3]));
+          } else {                   // dW[n = narrow][k = hidden]: consecutive lanes -> consecutive k
+#pragma unroll
+            for (int j = 0; j < 16; ++j) atomicAdd(P.dw + (size_t)(qq + j) * P.ldw + h, __uint_as_float(r[j]));
           }
         }
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
     }
-  } else if (warp >= 8) {
-    // =========================== producers (transformed side) ===========================
-    const int pt = threadIdx.x - 256;
-    const int p = pt & 7, rb = pt >> 3;          // 16-byte piece p of rows rb, rb + 32
-    const int nblk = MODE == 0 ? P.qblks : P_BLKS;
-    const int ld = MODE == 0 ? P.ldg : P.lda;
-    const int cdim = MODE == 0 ? P.N : P.K;
+  } else if (warp >= 8 && warp < 12) {
+    // =========================== transform warps: raw hidden tile -> operand tile, in place ===========================
+    const int tt = threadIdx.x - 256;            // 0..127
+    int s = 0;
+    uint32_t ph = 0;
+    int last_hw[MAX_STAGES];
+#pragma unroll
+    for (int i = 0; i < MAX_STAGES; ++i) last_hw[i] = 128;   // buffers start zeroed by nobody: treat as "full" so tails zero them
+    for (int item = blockIdx.x; item < items; item += gridDim.x) {
+      int h0, hw, q0, c_lo, c_hi;
+      decode(item, h0, hw, q0, c_lo, c_hi);
+      const int wh = hw >= 64 ? 64 : hw;           // channels per block; line = 2*wh bytes; wh/8 pieces per line
+      const int wsh = wh == 64 ? 0 : (wh == 32 ? 1 : 2);
+      const int ppl = wh >> 3;                     // pieces per line
+      const int nblk = hw >= 64 ? (hw >> 6) : 1;
+      const int pieces = nblk * MK * ppl;
+      for (int c = c_lo; c < c_hi; ++c) {
+        const int row0 = c * MK;
+        mbar_wait(&raw_full[s], ph);
+        const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
+        for (int idx = tt; idx < pieces; idx += XF_THREADS) {
+          const int p = idx % ppl;
+          const int r = (idx / ppl) % MK;
+          const int b = idx / (ppl * MK);
+          const uint32_t off = b * MK * 2 * wh + r * 2 * wh + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
+          const int ch = h0 + b * 64 + p * 8;
+          const bool ok = (row0 + r) < P.M;        // rows past M were zero-filled by TMA and must stay zero
+          float x[8], y[8];
+          unpack8(lds16(st + off), x);
+          if (MODE == 0) {
+            float g[8];
+            unpack8(lds16(st + h_bytes + off), g);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              y[j] = ok ? fmaf(s_coef[ch + j], x[j], fmaf(s_coef[P.hidden + ch + j], g[j], s_coef[2 * P.hidden + ch + j])) : 0.f;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y[j] = ok ? relu6f(fmaf(x[j], s_coef[ch + j], s_coef[P.hidden + ch + j])) : 0.f;
+          }
+          sts16(st + off, make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
+                                     pack_bf16x2(y[6], y[7])));
+        }
+        // lanes of the 128-wide M operand that this chunk does not cover must read as zero
+        if (hw < 128 && last_hw[s] != hw) {
+          const int used = MK * 2 * hw;            // bytes written above (hw >= 64: one block; hw < 64: one narrow block)
+          for (int o = used + tt * 16; o < h_bytes; o += XF_THREADS * 16) sts16(st + o, make_uint4(0u, 0u, 0u, 0u));
+        }
+        last_hw[s] = hw;
+        fence_proxy_async_smem();
+        mbar_arrive(&full[s]);
+        if (++s == stages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp >= 12) {
+    // =========================== loader warps: cp.async straight into the swizzled operand layout ===========================
+    const int lt = threadIdx.x - 384;            // 0..127
     int s = 0;
     uint32_t ph = 0;
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
-      int k0, n0, c_lo, c_hi;
-      decode(item, k0, n0, c_lo, c_hi);
-      const int ch0 = MODE == 0 ? n0 : k0;
-      const int chw = MODE == 0 ? P.nq : 128;
+      int h0, hw, q0, c_lo, c_hi;
+      decode(item, h0, hw, q0, c_lo, c_hi);
+      const int wh = hw >= 64 ? 64 : hw;
+      const int wsh = wh == 64 ? 0 : (wh == 32 ? 1 : 2);
+      const int ppl = wh >> 3;
+      const int nblk = hw >= 64 ? (hw >> 6) : 1;
+      const int hpieces = nblk * MK * ppl;
+      const int qfp = (P.nqf >> 6) * MK * 8;                     // pieces of the full 64-wide narrow blocks
+      const int qsh = P.nqp == 32 ? 1 : 2;                        // tail line: 64 B (4 pieces) or 32 B (2 pieces)
+      const int qpp = P.nqp >> 3;
+      const int qpieces = qfp + MK * qpp;
       for (int c = c_lo; c < c_hi; ++c) {
+        const int row0 = c * MK;
         mbar_wait(&empty[s], ph ^ 1);
-        const uint32_t st = smem_u32(base + (size_t)s * stage_bytes) + (MODE == 0 ? P_BLKS * BLK : 0);
-        for (int b = 0; b < nblk; ++b) {
-          const int lc = b * 64 + p * 8;                 // channel offset inside the chunk
-          const int col = ch0 + lc;
-          const bool colok = lc < chw && col < cdim;
-          float c0[8], c1[8], c2[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            c0[j] = colok ? s_coef[col + j] : 0.f;
-            c1[j] = colok ? s_coef[cdim + col + j] : 0.f;
-            c2[j] = (MODE == 0 && colok) ? s_coef[2 * cdim + col + j] : 0.f;
-          }
-          uint4 v0[2], v1[2];
-#pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const int gm = c * MK + rb + 32 * i;
-            v0[i] = make_uint4(0u, 0u, 0u, 0u);
-            v1[i] = make_uint4(0u, 0u, 0u, 0u);
-            if (colok && gm < P.M) {
-              v0[i] = ldg_stream(P.t0 + (size_t)gm * ld + col);
-              if (MODE == 0) v1[i] = ldg_stream(P.t1 + (size_t)gm * ld + col);
-            }
-          }
-#pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            const int r = rb + 32 * i;
-            const bool ok = colok && (c * MK + r) < P.M;
-            float x[8], g[8], y[8];
-            unpack8(v0[i], x);
-            unpack8(v1[i], g);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              if (MODE == 0) y[j] = ok ? fmaf(c0[j], x[j], fmaf(c1[j], g[j], c2[j])) : 0.f;
-              else y[j] = ok ? relu6f(fmaf(x[j], c0[j], c1[j])) : 0.f;
-            }
-            sts16(st + b * BLK + r * 128 + ((p ^ (r & 7)) << 4),
-                  make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
-                             pack_bf16x2(y[6], y[7])));
-          }
+        const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
+        const uint32_t sq = st + h_bytes * (MODE == 0 ? 2 : 1);
+        for (int idx = lt; idx < hpieces; idx += LD_THREADS) {
+          const int p = idx % ppl;
+          const int r = (idx / ppl) % MK;
+          const int b = idx / (ppl * MK);
+          const uint32_t off = b * MK * 2 * wh + r * 2 * wh + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
+          const int gr = row0 + r;
+          const uint32_t nb = gr < P.M ? 16u : 0u;
+          const size_t goff = (size_t)(gr < P.M ? gr : 0) * P.ldh + h0 + b * 64 + p * 8;
+          cp_async16(st + off, P.t0 + goff, nb);
+          if (MODE == 0) cp_async16(st + h_bytes + off, P.t1 + goff, nb);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(&full[s]);
+        for (int idx = lt; idx < qpieces; idx += LD_THREADS) {
+          int p, r, ch;
+          uint32_t off;
+          if (idx < qfp) {
+            p = idx & 7; r = (idx >> 3) % MK;
+            const int b = idx / (8 * MK);
+            off = b * MK * 128 + r * 128 + ((p ^ (r & 7)) << 4);
+            ch = q0 + b * 64 + p * 8;
+          } else {
+            const int k = idx - qfp;
+            p = k % qpp; r = k / qpp;
+            off = (P.nqf >> 6) * MK * 128 + r * 2 * P.nqp + ((p ^ ((r >> qsh) & ((8 >> qsh) - 1))) << 4);
+            ch = q0 + P.nqf + p * 8;
+          }
+          const int gr = row0 + r;
+          cp_async16(sq + off, P.qsrc + (size_t)(gr < P.M ? gr : 0) * P.ldq + ch, gr < P.M ? 16u : 0u);
+        }
+        cp_async_arrive(&raw_full[s]);            // arrives when this thread's copies above have landed
         if (++s == stages) { s = 0; ph ^= 1; }
       }
     }
@@ -256,55 +339,59 @@ pw_wgrad_kernel(const __grid_constant__ CUtensorMap tmPure, const __grid_constan
 
 }  // namespace
 
-// mode 0: a_pure = finished input activation [M][K] (TMA); g0 = dz, g1 = y_raw [M][N]; coef = [3][N]
-// mode 1: g_pure = materialised output gradient [M][N] (TMA); a0 = d_raw [M][K]; coef = [2][K]
+// mode 0: hidden side = G = ca*t0 + cb*t1 + cc with t0 = dz, t1 = y_raw [M][N];  narrow side = `pure` = A [M][K]
+// mode 1: hidden side = A = relu6(scale*t0 + shift) with t0 = d_raw [M][K];      narrow side = `pure` = G [M][N]
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
                     int ld_t, const float* coef, float* dw, int ldw, int max_ctas, cudaStream_t s) {
   B200DP_REQUIRE(mode == 0 || mode == 1, "pw_wgrad: bad mode");
   B200DP_REQUIRE(M > 0 && N % 16 == 0 && K % 16 == 0, "pw_wgrad: M=%d N=%d K=%d invalid", M, N, K);
   B200DP_REQUIRE(pure && t0 && coef && dw && (mode == 1 || t1), "pw_wgrad: missing pointers");
   WgradParams p{};
-  p.M = M; p.N = N; p.K = K;
-  p.lda = mode == 0 ? ld_pure : ld_t;
-  p.ldg = mode == 0 ? ld_t : ld_pure;
-  p.ldw = ldw;
-  p.nchunks = (N + 255) / 256;
-  p.nq = ((N + p.nchunks - 1) / p.nchunks + 15) / 16 * 16;
-  p.qblks = (p.nq + 63) / 64;
-  p.kchunks = (K + 127) / 128;
-  const int total_chunks = (M + MK - 1) / MK;
-  const int cap = max_ctas > 0 ? max_ctas : num_sms();
-  int msplit = (2 * cap + p.kchunks * p.nchunks - 1) / (p.kchunks * p.nchunks);
-  const int max_split = (total_chunks + 3) / 4;        // at least 4 stages of work per item
-  if (msplit > max_split) msplit = max_split;
-  if (msplit < 1) msplit = 1;
-  p.chunks_per_split = (total_chunks + msplit - 1) / msplit;
-  p.msplit = (total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
-  p.t0 = static_cast<const __nv_bfloat16*>(t0);
-  p.t1 = static_cast<const __nv_bfloat16*>(t1);
+  p.M = M;
+  p.hidden = mode == 0 ? N : K;
+  p.narrow = mode == 0 ? K : N;
+  p.ldh = ld_t; p.ldq = ld_pure; p.ldw = ldw;
   p.coef = coef; p.dw = dw;
-  const size_t stage_bytes = (size_t)(P_BLKS + p.qblks) * BLK;
-  const size_t fixed = ((mode == 0 ? 3 * (size_t)N : 2 * (size_t)K) + 4) * 4 + (2 * MAX_STAGES + 4) * 8 + 16 + 1024;
+  p.n128 = p.hidden / 128;
+  p.tail = p.hidden % 128;
+  B200DP_REQUIRE(p.tail % 64 == 0 || p.tail % 64 == 16 || p.tail % 64 == 32, "pw_wgrad: hidden=%d unsupported", p.hidden);
+  p.hchunks = p.n128 + (p.tail >= 64 ? 1 : 0) + (p.tail % 64 ? 1 : 0);
+  p.qchunks = (p.narrow + 255) / 256;
+  B200DP_REQUIRE(p.narrow % p.qchunks == 0 && (p.narrow / p.qchunks) % 16 == 0, "pw_wgrad: narrow=%d unsupported", p.narrow);
+  p.nq = p.narrow / p.qchunks;
+  p.nqp = p.nq % 64;
+  p.nqf = p.nq - p.nqp;
+  B200DP_REQUIRE(p.nqp == 0 || p.nqp == 16 || p.nqp == 32, "pw_wgrad: narrow chunk %d unsupported", p.nq);
+  const int row_bytes = 256 * (mode == 0 ? 2 : 1) + p.nq * 2;
+  p.mk = row_bytes <= 160 ? 256 : (row_bytes <= 352 ? 128 : 64);
+  const size_t stage_bytes = (size_t)p.mk * 256 * (mode == 0 ? 2 : 1) + (((size_t)p.mk * p.nq * 2 + 1023) & ~(size_t)1023);
+  const size_t fixed = ((size_t)(mode == 0 ? 3 : 2) * p.hidden + 4) * 4 + (3 * MAX_STAGES + 4) * 8 + 16 + 1024;
   const size_t budget = 220 * 1024;
   int stages = (int)((budget - fixed) / stage_bytes);
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   B200DP_REQUIRE(stages >= 2, "pw_wgrad: shared memory budget exceeded");
   p.stages = stages;
   const size_t smem = fixed + stages * stage_bytes;
-  CUtensorMap tm;
-  if (mode == 0) {
-    if (int rc = make_tmap_2d_bf16(&tm, pure, M, K, ld_pure, 64, MK)) return rc;
-  } else {
-    if (int rc = make_tmap_2d_bf16(&tm, pure, M, N, ld_pure, 64, MK)) return rc;
-  }
-  const int items = p.kchunks * p.nchunks * p.msplit;
+  const int total_chunks = (M + p.mk - 1) / p.mk;
+  const int cap = max_ctas > 0 ? max_ctas : num_sms();
+  const int hq = p.hchunks * p.qchunks;
+  int msplit = (2 * cap + hq - 1) / hq;
+  const int max_split = (total_chunks + 3) / 4;        // at least ~4 stages of work per item
+  if (msplit > max_split) msplit = max_split;
+  if (msplit < 1) msplit = 1;
+  p.chunks_per_split = (total_chunks + msplit - 1) / msplit;
+  p.msplit = (total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
+  p.t0 = static_cast<const __nv_bfloat16*>(t0);
+  p.t1 = static_cast<const __nv_bfloat16*>(t1);
+  p.qsrc = static_cast<const __nv_bfloat16*>(pure);
+  const int items = hq * p.msplit;
   const int grid = items < cap ? items : cap;
   if (mode == 0) {
     B200DP_CUDA(cudaFuncSetAttribute(pw_wgrad_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    pw_wgrad_kernel<0><<<grid, 512, smem, s>>>(tm, p);
+    pw_wgrad_kernel<0><<<grid, 512, smem, s>>>(p);
   } else {
     B200DP_CUDA(cudaFuncSetAttribute(pw_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    pw_wgrad_kernel<1><<<grid, 512, smem, s>>>(tm, p);
+    pw_wgrad_kernel<1><<<grid, 512, smem, s>>>(p);
   }
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
