@@ -147,6 +147,49 @@ grad_join_stats_kernel(const __nv_bfloat16* __restrict__ g1, const __nv_bfloat16
   }
 }
 
+
+// Block output: out = scale*raw + shift (+ res), and the per-channel column sums of the ROUNDED result.  The next
+// expand conv's weight gradient factors its BatchNorm-backward affine out of the reduction and needs sum_m x[m][k].
+// Each thread keeps one 8-channel group for its whole life (like grad_join_stats_kernel).
+__global__ void __launch_bounds__(256)
+block_out_kernel(const __nv_bfloat16* __restrict__ raw, const __nv_bfloat16* __restrict__ res,
+                 const float* __restrict__ coef, __nv_bfloat16* __restrict__ out, float* __restrict__ colsum,
+                 long long rows, int C) {
+  extern __shared__ float s_red[];   // [C]
+  const int CG = C >> 3;
+  const int ipb = blockDim.x / CG;
+  const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+  if (ti < ipb) {
+    float k0[8], k1[8], acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { k0[j] = coef[cg * 8 + j]; k1[j] = coef[C + cg * 8 + j]; acc[j] = 0.f; }
+    for (long long r = (long long)blockIdx.x * ipb + ti; r < rows; r += (long long)gridDim.x * ipb) {
+      const long long off = r * C + cg * 8;
+      float x[8], y[8], o[8];
+      unpack8(ldg_stream(raw + off), x);
+      if (res != nullptr) unpack8(ldg_stream(res + off), y);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fmaf(k0[j], x[j], k1[j]) + (res != nullptr ? y[j] : 0.f);
+      const uint4 pk = pack8(o);
+      stg_stream(out + off, pk);
+      if (colsum != nullptr) {
+        unpack8(pk, o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += o[j];
+      }
+    }
+    if (colsum != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(&s_red[cg * 8 + j], acc[j]);
+    }
+  }
+  __syncthreads();
+  if (colsum != nullptr)
+    for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(colsum + i, s_red[i]);
+}
+
 // Weight preparation: fp32 master [N][K] -> bf16 [N][K] and bf16 transposed [K][N] for every pointwise conv.
 struct WPrepEntry { long long off; int n, k; };
 
@@ -197,6 +240,23 @@ int affine_launch(const void* a, const void* b, const float* coef, int three, vo
   if (blocks > cap) blocks = cap;
   affine_kernel<<<(int)blocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b),
                                             coef, three, static_cast<__nv_bfloat16*>(out), rows, C);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+
+int block_out_launch(const void* raw, const void* res, const float* coef, void* out, float* colsum, long long rows,
+                     int C, cudaStream_t s) {
+  B200DP_REQUIRE(C % 8 == 0 && C / 8 <= 256, "block_out: C=%d unsupported", C);
+  const int CG = C / 8;
+  const int threads = (256 / CG) * CG;
+  const int ipb = threads / CG;
+  long long blocks = (rows + ipb - 1) / ipb;
+  const long long cap = (long long)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  block_out_kernel<<<(int)blocks, threads, C * sizeof(float), s>>>(
+      static_cast<const __nv_bfloat16*>(raw), static_cast<const __nv_bfloat16*>(res), coef,
+      static_cast<__nv_bfloat16*>(out), colsum, rows, C);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

@@ -43,6 +43,7 @@ struct Block {
   bool use_res;
   int ce, cd, cp;      // conv indices (ce = -1 when expand == 1)
   __nv_bfloat16* xout = nullptr;   // finished block output [B, hout, hout, coutp]
+  float* xsum = nullptr;           // per-channel column sums of xout (for the consumer's factored weight gradient)
 };
 
 struct WPrepEntry { long long off; int n, k; };
@@ -159,6 +160,7 @@ size_t layout_workspace(Engine& e, char* base) {
     c.sums_f = carve<float>(p, 2 * c.coutp);
     c.sums_b = carve<float>(p, 2 * c.coutp);
   }
+  for (auto& b : e.blocks) b.xsum = carve<float>(p, b.coutp);
   e.sums_all = reinterpret_cast<float*>(sums0);
   e.sums_bytes = (size_t)(p - sums0);
   for (auto& c : e.convs) {
@@ -303,7 +305,8 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
     mark(e, s, "pw_fwd_project", b.cp);
     if (train) ENG_TRY(bn_fin_f(e, cp, (float)n * cp.hout * cp.hout, s));
     const void* res = b.use_res ? e.blocks[b.index - 2].xout : nullptr;
-    ENG_TRY(affine_launch(cp.raw, res, cp.coef_f, 0, b.xout, (long long)n * b.hout * b.hout, cp.coutp, s));
+    ENG_TRY(block_out_launch(cp.raw, res, cp.coef_f, b.xout, train ? b.xsum : nullptr, (long long)n * b.hout * b.hout,
+                             cp.coutp, s));
     mark(e, s, "block_out", b.cp);
   }
   const int li = (int)e.convs.size() - 1;
@@ -334,7 +337,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
   ENG_TRY(bn_fin_b(e, cl, (float)n * HW, s));
   Block& lb = e.blocks.back();
   const int Ml = n * HW;
-  ENG_TRY(pw_wgrad_launch(0, Ml, cl.coutp, cl.cinp, lb.xout, cl.cinp, e.dze, cl.raw, cl.coutp, cl.coef_b,
+  ENG_TRY(pw_wgrad_launch(0, Ml, cl.coutp, cl.cinp, lb.xout, cl.cinp, e.dze, cl.raw, cl.coutp, cl.coef_b, lb.xsum,
                           e.grads + cl.off_w, cl.cinp, 0, s));
   mark(e, s, "pw_wgrad_last", li);
   int gxi = 0, doi = 0;
@@ -364,7 +367,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     mark(e, s, "bn_bwd_apply", b.cp);
     // ---- projection conv: weight gradient, then data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
     ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, e.dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
-                            e.grads + cp.off_w, cp.cinp, 0, s));
+                            nullptr, e.grads + cp.off_w, cp.cinp, 0, s));
     mark(e, s, "pw_wgrad_project", b.cp);
     ENG_TRY(pw_gemm_launch(pl.dgrad[b.cp], s));
     mark(e, s, "pw_dgrad_project", b.cp);
@@ -381,7 +384,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       Conv& ce = e.convs[b.ce];
       const __nv_bfloat16* xin = e.blocks[bi - 1].xout;
       ENG_TRY(pw_wgrad_launch(0, (int)rows_in, ce.coutp, ce.cinp, xin, ce.cinp, e.dze, ce.raw, ce.coutp, ce.coef_b,
-                              e.grads + ce.off_w, ce.cinp, 0, s));
+                              e.blocks[bi - 1].xsum, e.grads + ce.off_w, ce.cinp, 0, s));
       mark(e, s, "pw_wgrad_expand", b.ce);
       gxi ^= 1;
       ENG_TRY(retarget_out(pl.dgrad[b.ce], e.gx[gxi]));

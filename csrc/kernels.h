@@ -21,7 +21,7 @@ int stem_wgrad_launch(const void* x, const void* dz, const void* yraw, const flo
                       int W, cudaStream_t s);
 // pw_wgrad.cu
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
-                    int ld_t, const float* coef, float* dw, int ldw, int max_ctas, cudaStream_t s);
+                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s);
 // bn_ops.cu
 int bn_fwd_finalize_launch(const float* sums, int stride, const float* gamma, const float* beta, float count,
                            float eps, float momentum, float* rmean, float* rvar, float* coef, float* saved, int C,
@@ -32,6 +32,8 @@ int bn_bwd_finalize_launch(const float* sums, int stride, const float* saved, co
                            float* coef3, float* dgamma, float* dbeta, int C, cudaStream_t s);
 int affine_launch(const void* a, const void* b, const float* coef, int three, void* out, long long rows, int C,
                   cudaStream_t s);
+int block_out_launch(const void* raw, const void* res, const float* coef, void* out, float* colsum, long long rows,
+                     int C, cudaStream_t s);
 int grad_join_stats_launch(const void* g1, const void* g2, const void* x, void* dout, float* sums, int stride,
                            long long rows, int C, cudaStream_t s);
 int weight_prep_launch(const float* master, void* w, void* wt, const void* table_dev, int nlayers, cudaStream_t s);

@@ -7,7 +7,11 @@
 // bytes with the 128-byte swizzle, which IS the canonical MN-major tile -- no transpose pass exists anywhere.
 //
 // Every 1x1 conv in MobileNetV2 has one wide side ("hidden": 32..1280 channels) and one narrow side (16..320):
-//   MODE 0 (expand / last conv):  hidden = G side, formed as ca*dz + cb*y_raw + cc;  narrow = A side (block input)
+//   MODE 0 (expand / last conv):  hidden = G side = ca*dz + cb*y_raw + cc;  narrow = A side (block input).  The
+//                                 affine map is per hidden channel, so it FACTORS out of the reduction over m:
+//                                   dW[n][k] = ca[n] (dz^T A)[n][k] + cb[n] (y^T A)[n][k] + cc[n] sum_m A[m][k]
+//                                 -> two MMAs on the raw bf16 tensors, no per-element transform at all; the
+//                                 combination happens once per output element in the epilogue (fp32).
 //   MODE 1 (project conv):        hidden = A side, formed as relu6(scale*d_raw + shift);  narrow = G side (dp)
 // The hidden side is the UMMA M operand (128 TMEM lanes), the narrow side the N operand:
 //   D[hidden chunk (128 lanes)][narrow chunk (<= 256 columns)] += H[m x 128]^T * Q[m x nq]
@@ -41,14 +45,14 @@ struct WgradParams {
   int hidden, narrow;          // channel counts of the wide / narrow side
   int ldh, ldq, ldw;           // row pitches (elements): hidden tensors, narrow tensor, dW
   int mk;                      // m rows per pipeline stage (64 / 128 / 256)
-  int nq, nqf, nqp, qchunks;   // narrow chunk width = nqf (full 64-blocks) + nqp (16/32 tail), number of chunks
-  int n128, tail;              // hidden = 128 * n128 + tail
+  int nq, qblks, qchunks;      // narrow chunk width (multiple of 16), its 64-wide blocks, number of chunks
   int hchunks, msplit, chunks_per_split, stages;
   const float* coef;           // MODE 0: [3][hidden] ca, cb, cc     MODE 1: [2][hidden] scale, shift
   float* dw;
   const __nv_bfloat16* t0;     // hidden raw tensor 0 (MODE 0: dz, MODE 1: d_raw)
   const __nv_bfloat16* t1;     // hidden raw tensor 1 (MODE 0: y_raw)
   const __nv_bfloat16* qsrc;   // narrow tensor
+  const float* asum;           // MODE 0: [narrow] column sums of the narrow tensor over all M rows
 };
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
@@ -68,17 +72,6 @@ __device__ __forceinline__ uint4 lds16(uint32_t addr) {
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-// MN-major operand: lines of (16 * w / 8) bytes holding w consecutive channels, one line per m row, swizzle by line
-// width; blocks of w channels are `lbo` bytes apart, groups of 8 lines are 8 lines apart.
-__device__ __forceinline__ uint64_t desc_mn(uint32_t addr, int w, uint32_t lbo) {
-  uint64_t d = 0;
-  d |= (uint64_t)((addr & 0x3FFFF) >> 4);
-  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((16 * w) >> 4) << 32;                 // 8 lines x 2w bytes
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)(w == 64 ? 2 : (w == 32 ? 4 : 6)) << 61;
-  return d;
-}
 // 16-byte asynchronous global->shared copy (zero-fills when src_bytes == 0) and its mbarrier completion hook
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
@@ -87,15 +80,17 @@ __device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// Roles (512 threads): warp 0 = MMA issuer + TMEM allocator | warps 4-7 = epilogue | warps 8-11 = transform (MODE 1)
+// or publish-only (MODE 0) | warps 12-15 = cp.async loaders | warps 1-3 idle.
 template <int MODE>
 __global__ void __launch_bounds__(512, 1)
 pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int MK = P.mk;
-  const int h_bytes = MK * 256;                                     // hidden tile: always 128 channels wide
-  const int q_bytes = MK * P.nq * 2;
-  const int stage_bytes = h_bytes * (MODE == 0 ? 2 : 1) + ((q_bytes + 1023) & ~1023);
+  const int h_bytes = MK * 256;                                     // hidden tile: 2 blocks of 64 channels, 128-byte lines
+  const int q_bytes = P.qblks * MK * 128;
+  const int stage_bytes = h_bytes * (MODE == 0 ? 2 : 1) + q_bytes;
   const int stages = P.stages;
   float* s_coef = reinterpret_cast<float*>(base + (size_t)stages * stage_bytes);
   const int ncoef = (MODE == 0 ? 3 : 2) * P.hidden;
@@ -111,7 +106,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   const int items = P.hchunks * P.qchunks * P.msplit;
   const int total_chunks = (P.M + MK - 1) / MK;
 
-  if (warp == 1 && lane == 0) {
+  if (warp == 0 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full[s], XF_THREADS);
       mbar_init(&empty[s], 1);
@@ -123,38 +118,33 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
   for (int i = threadIdx.x; i < ncoef; i += blockDim.x) s_coef[i] = P.coef[i];
+  // operand tiles are zero-padded past the channels a chunk covers: start from all-zero stages
+  for (int o = threadIdx.x * 16; o < stages * stage_bytes; o += blockDim.x * 16) sts16(smem_u32(base) + o, make_uint4(0u, 0u, 0u, 0u));
+  fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // item -> hidden chunk (h0, hw), narrow chunk q0, m-chunk range.  Hidden chunk fastest: CTAs running side by
-  // side read the same narrow rows, which stay in L2.
+  // item -> hidden chunk (h0, hw <= 128), narrow chunk q0, m-chunk range.  Hidden chunk fastest: CTAs running side
+  // by side read the same narrow rows, which stay in L2.
   auto decode = [&](int item, int& h0, int& hw, int& q0, int& c_lo, int& c_hi) {
     const int hc = item % P.hchunks;
     const int qc = (item / P.hchunks) % P.qchunks;
     const int ms = item / (P.hchunks * P.qchunks);
-    if (hc < P.n128) { h0 = hc * 128; hw = 128; }
-    else {
-      const int j = hc - P.n128;
-      h0 = P.n128 * 128;
-      if (P.tail >= 64) { if (j == 0) hw = 64; else { h0 += 64; hw = P.tail - 64; } }
-      else hw = P.tail;
-    }
+    h0 = hc * 128;
+    hw = min(128, P.hidden - h0);
     q0 = qc * P.nq;
     c_lo = ms * P.chunks_per_split;
     c_hi = min(c_lo + P.chunks_per_split, total_chunks);
   };
 
   if (warp == 0) {
-    // (idle: loads are issued by the loader warps below)
-  } else if (warp == 1) {
     // =========================== MMA issuer ===========================
     if (lane == 0) {
-      const uint32_t idesc_f = umma_idesc_bf16(128, P.nqf ? P.nqf : 16, 1, 1);
-      const uint32_t idesc_p = umma_idesc_bf16(128, P.nqp ? P.nqp : 16, 1, 1);
+      const uint32_t idesc = umma_idesc_bf16(128, P.nq, 1, 1);
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
@@ -165,19 +155,18 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
         mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * 256;
-        const int wh = hw >= 64 ? 64 : hw;                     // channels per hidden block
         for (int c = c_lo; c < c_hi; ++c) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
           const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
           const uint32_t sq = st + h_bytes * (MODE == 0 ? 2 : 1);
-          const uint64_t dh = desc_mn(st, wh, (uint32_t)MK * 2 * wh);
-          const uint64_t dqf = desc_mn(sq, 64, (uint32_t)MK * 128);
-          const uint64_t dqp = desc_mn(sq + (P.nqf >> 6) * MK * 128, P.nqp ? P.nqp : 16, (uint32_t)MK * 128);
-          for (int k = 0; k < (MK >> 4); ++k) {                // 16 m-rows per MMA
+          const uint64_t dh = umma_desc_mnmajor_sw128(st, (uint32_t)MK * 128);
+          const uint64_t dh2 = umma_desc_mnmajor_sw128(st + h_bytes, (uint32_t)MK * 128);   // MODE 0: y_raw tile
+          const uint64_t dq = umma_desc_mnmajor_sw128(sq, (uint32_t)MK * 128);
+          for (int k = 0; k < (MK >> 4); ++k) {                // 16 m-rows per MMA = 2048 B of 128-byte lines
             const uint32_t acc = (c > c_lo) | (k > 0);
-            if (P.nqf) umma_bf16(d_tmem, dh + (uint64_t)(2 * wh * k), dqf + (uint64_t)(128 * k), idesc_f, acc);
-            if (P.nqp) umma_bf16(d_tmem + P.nqf, dh + (uint64_t)(2 * wh * k), dqp + (uint64_t)(2 * P.nqp * k), idesc_p, acc);
+            umma_bf16(d_tmem, dh + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, acc);
+            if (MODE == 0) umma_bf16(d_tmem + 128, dh2 + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, acc);
           }
           umma_commit(&empty[s]);
           if (++s == stages) { s = 0; ph ^= 1; }
@@ -199,18 +188,30 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
       const bool ok = hl < hw && c_hi > c_lo;
       const int h = h0 + hl;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * 256;
+      float ka = 0.f, kb = 0.f, kc = 0.f;
+      if (MODE == 0 && ok) {
+        ka = s_coef[h]; kb = s_coef[P.hidden + h];
+        kc = c_lo == 0 ? s_coef[2 * P.hidden + h] : 0.f;     // the cc * sum_m A term is added by the first m-split only
+      }
       for (int c16 = 0; c16 < (P.nq >> 4); ++c16) {
         uint32_t r[16];
         tmem_ld_x16(taddr + c16 * 16, r);
         tmem_ld_wait();
+        uint32_t r2[16];
+        if (MODE == 0) {
+          tmem_ld_x16(taddr + 128 + c16 * 16, r2);
+          tmem_ld_wait();
+        }
         if (ok) {
           const int qq = q0 + c16 * 16;
           if (MODE == 0) {           // dW[n = hidden][k = narrow]: this lane's row, 16 consecutive k
             float* dst = P.dw + (size_t)h * P.ldw + qq;
+            float v[16];
 #pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              red_add_v4(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                         __uint_as_float(r[j + 3]));
+            for (int j = 0; j < 16; ++j)
+              v[j] = fmaf(ka, __uint_as_float(r[j]), fmaf(kb, __uint_as_float(r2[j]), kc * __ldg(P.asum + qq + j)));
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
           } else {                   // dW[n = narrow][k = hidden]: consecutive lanes -> consecutive k
 #pragma unroll
             for (int j = 0; j < 16; ++j) atomicAdd(P.dw + (size_t)(qq + j) * P.ldw + h, __uint_as_float(r[j]));
@@ -221,51 +222,54 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
       mbar_arrive(&tmem_empty[as]);
     }
   } else if (warp >= 8 && warp < 12) {
-    // =========================== transform warps: raw hidden tile -> operand tile, in place ===========================
+    // =========================== transform warps ===========================
+    // MODE 1: rewrite the raw hidden tile in place with relu6(scale*x + shift).  MODE 0: nothing to compute (the
+    // BatchNorm-backward affine is applied in the epilogue); the warps only publish the tile to the async proxy.
+    // Pieces past the chunk's channels are zero (never written by the loaders) unless an earlier, wider item used
+    // the stage: then they are re-zeroed once.
     const int tt = threadIdx.x - 256;            // 0..127
+    const int pp = tt & 15, rb = tt >> 4;        // 16-byte piece pp (0..15 over the two 64-channel blocks) of rows rb + 8 i
+    const int blk = pp >> 3, p = pp & 7;         // rows rb + 8 i all have (r & 7) == rb: the swizzle term is constant
     int s = 0;
     uint32_t ph = 0;
     int last_hw[MAX_STAGES];
 #pragma unroll
-    for (int i = 0; i < MAX_STAGES; ++i) last_hw[i] = 128;   // buffers start zeroed by nobody: treat as "full" so tails zero them
+    for (int i = 0; i < MAX_STAGES; ++i) last_hw[i] = 0;
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
       int h0, hw, q0, c_lo, c_hi;
       decode(item, h0, hw, q0, c_lo, c_hi);
-      const int wh = hw >= 64 ? 64 : hw;           // channels per block; line = 2*wh bytes; wh/8 pieces per line
-      const int wsh = wh == 64 ? 0 : (wh == 32 ? 1 : 2);
-      const int ppl = wh >> 3;                     // pieces per line
-      const int nblk = hw >= 64 ? (hw >> 6) : 1;
-      const int pieces = nblk * MK * ppl;
+      const bool mine = pp * 8 < hw;
+      float sc[8], sh[8];
+      if (MODE == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          sc[j] = mine ? s_coef[h0 + pp * 8 + j] : 0.f;
+          sh[j] = mine ? s_coef[P.hidden + h0 + pp * 8 + j] : 0.f;
+        }
+      }
       for (int c = c_lo; c < c_hi; ++c) {
         const int row0 = c * MK;
         mbar_wait(&raw_full[s], ph);
         const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
-        for (int idx = tt; idx < pieces; idx += XF_THREADS) {
-          const int p = idx % ppl;
-          const int r = (idx / ppl) % MK;
-          const int b = idx / (ppl * MK);
-          const uint32_t off = b * MK * 2 * wh + r * 2 * wh + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
-          const int ch = h0 + b * 64 + p * 8;
-          const bool ok = (row0 + r) < P.M;        // rows past M were zero-filled by TMA and must stay zero
-          float x[8], y[8];
-          unpack8(lds16(st + off), x);
-          if (MODE == 0) {
-            float g[8];
-            unpack8(lds16(st + h_bytes + off), g);
+        const bool rezero = last_hw[s] > hw;
+        if (MODE == 1 && mine) {
+          for (int r = rb; r < MK; r += 8) {
+            const uint32_t off = blk * MK * 128 + r * 128 + ((p ^ rb) << 4);
+            const bool ok = (row0 + r) < P.M;      // rows past M were zero-filled and must stay zero
+            float x[8], y[8];
+            unpack8(lds16(st + off), x);
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              y[j] = ok ? fmaf(s_coef[ch + j], x[j], fmaf(s_coef[P.hidden + ch + j], g[j], s_coef[2 * P.hidden + ch + j])) : 0.f;
-          } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) y[j] = ok ? relu6f(fmaf(x[j], s_coef[ch + j], s_coef[P.hidden + ch + j])) : 0.f;
+            for (int j = 0; j < 8; ++j) y[j] = ok ? relu6f(fmaf(x[j], sc[j], sh[j])) : 0.f;
+            sts16(st + off, make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
+                                       pack_bf16x2(y[6], y[7])));
           }
-          sts16(st + off, make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
-                                     pack_bf16x2(y[6], y[7])));
         }
-        // lanes of the 128-wide M operand that this chunk does not cover must read as zero
-        if (hw < 128 && last_hw[s] != hw) {
-          const int used = MK * 2 * hw;            // bytes written above (hw >= 64: one block; hw < 64: one narrow block)
-          for (int o = used + tt * 16; o < h_bytes; o += XF_THREADS * 16) sts16(st + o, make_uint4(0u, 0u, 0u, 0u));
+        if (rezero && !mine) {
+          for (int r = rb; r < MK; r += 8) {
+            const uint32_t off = blk * MK * 128 + r * 128 + ((p ^ rb) << 4);
+            sts16(st + off, make_uint4(0u, 0u, 0u, 0u));
+            if (MODE == 0) sts16(st + h_bytes + off, make_uint4(0u, 0u, 0u, 0u));
+          }
         }
         last_hw[s] = hw;
         fence_proxy_async_smem();
@@ -276,52 +280,43 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   } else if (warp >= 12) {
     // =========================== loader warps: cp.async straight into the swizzled operand layout ===========================
     const int lt = threadIdx.x - 384;            // 0..127
+    const int pp = lt & 15, rb = lt >> 4;        // hidden tile: piece pp of rows rb + 8 i   ((r & 7) == rb)
+    const int blk = pp >> 3, p = pp & 7;
+    const int pq = lt & 31, rq = lt >> 5;        // narrow tile: piece pq of rows rq + 4 i
+    const bool qmine = pq * 8 < P.nq;
     int s = 0;
     uint32_t ph = 0;
     for (int item = blockIdx.x; item < items; item += gridDim.x) {
       int h0, hw, q0, c_lo, c_hi;
       decode(item, h0, hw, q0, c_lo, c_hi);
-      const int wh = hw >= 64 ? 64 : hw;
-      const int wsh = wh == 64 ? 0 : (wh == 32 ? 1 : 2);
-      const int ppl = wh >> 3;
-      const int nblk = hw >= 64 ? (hw >> 6) : 1;
-      const int hpieces = nblk * MK * ppl;
-      const int qfp = (P.nqf >> 6) * MK * 8;                     // pieces of the full 64-wide narrow blocks
-      const int qsh = P.nqp == 32 ? 1 : 2;                        // tail line: 64 B (4 pieces) or 32 B (2 pieces)
-      const int qpp = P.nqp >> 3;
-      const int qpieces = qfp + MK * qpp;
+      const bool mine = pp * 8 < hw;
+      const uint32_t hoff = blk * MK * 128 + rb * 128 + ((p ^ rb) << 4);
       for (int c = c_lo; c < c_hi; ++c) {
         const int row0 = c * MK;
         mbar_wait(&empty[s], ph ^ 1);
         const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
         const uint32_t sq = st + h_bytes * (MODE == 0 ? 2 : 1);
-        for (int idx = lt; idx < hpieces; idx += LD_THREADS) {
-          const int p = idx % ppl;
-          const int r = (idx / ppl) % MK;
-          const int b = idx / (ppl * MK);
-          const uint32_t off = b * MK * 2 * wh + r * 2 * wh + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
-          const int gr = row0 + r;
-          const uint32_t nb = gr < P.M ? 16u : 0u;
-          const size_t goff = (size_t)(gr < P.M ? gr : 0) * P.ldh + h0 + b * 64 + p * 8;
-          cp_async16(st + off, P.t0 + goff, nb);
-          if (MODE == 0) cp_async16(st + h_bytes + off, P.t1 + goff, nb);
-        }
-        for (int idx = lt; idx < qpieces; idx += LD_THREADS) {
-          int p, r, ch;
-          uint32_t off;
-          if (idx < qfp) {
-            p = idx & 7; r = (idx >> 3) % MK;
-            const int b = idx / (8 * MK);
-            off = b * MK * 128 + r * 128 + ((p ^ (r & 7)) << 4);
-            ch = q0 + b * 64 + p * 8;
-          } else {
-            const int k = idx - qfp;
-            p = k % qpp; r = k / qpp;
-            off = (P.nqf >> 6) * MK * 128 + r * 2 * P.nqp + ((p ^ ((r >> qsh) & ((8 >> qsh) - 1))) << 4);
-            ch = q0 + P.nqf + p * 8;
+        if (mine) {
+          const __nv_bfloat16* g0 = P.t0 + (size_t)(row0 + rb) * P.ldh + h0 + pp * 8;
+          const __nv_bfloat16* g1 = MODE == 0 ? P.t1 + (size_t)(row0 + rb) * P.ldh + h0 + pp * 8 : nullptr;
+          uint32_t d = st + hoff;
+          for (int r = rb; r < MK; r += 8) {
+            const bool ok = (row0 + r) < P.M;
+            cp_async16(d, ok ? g0 : P.t0, ok ? 16u : 0u);
+            if (MODE == 0) cp_async16(d + h_bytes, ok ? g1 : P.t1, ok ? 16u : 0u);
+            d += 8 * 128;
+            g0 += (size_t)8 * P.ldh;
+            if (MODE == 0) g1 += (size_t)8 * P.ldh;
           }
-          const int gr = row0 + r;
-          cp_async16(sq + off, P.qsrc + (size_t)(gr < P.M ? gr : 0) * P.ldq + ch, gr < P.M ? 16u : 0u);
+        }
+        if (qmine) {
+          const __nv_bfloat16* g = P.qsrc + (size_t)(row0 + rq) * P.ldq + q0 + pq * 8;
+          const uint32_t qb = sq + (pq >> 3) * MK * 128;
+          for (int r = rq; r < MK; r += 4) {
+            const bool ok = (row0 + r) < P.M;
+            cp_async16(qb + r * 128 + (((pq & 7) ^ (r & 7)) << 4), ok ? g : P.qsrc, ok ? 16u : 0u);
+            g += (size_t)4 * P.ldq;
+          }
         }
         cp_async_arrive(&raw_full[s]);            // arrives when this thread's copies above have landed
         if (++s == stages) { s = 0; ph ^= 1; }
@@ -331,7 +326,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
@@ -342,29 +337,25 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
 // mode 0: hidden side = G = ca*t0 + cb*t1 + cc with t0 = dz, t1 = y_raw [M][N];  narrow side = `pure` = A [M][K]
 // mode 1: hidden side = A = relu6(scale*t0 + shift) with t0 = d_raw [M][K];      narrow side = `pure` = G [M][N]
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
-                    int ld_t, const float* coef, float* dw, int ldw, int max_ctas, cudaStream_t s) {
+                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s) {
   B200DP_REQUIRE(mode == 0 || mode == 1, "pw_wgrad: bad mode");
   B200DP_REQUIRE(M > 0 && N % 16 == 0 && K % 16 == 0, "pw_wgrad: M=%d N=%d K=%d invalid", M, N, K);
-  B200DP_REQUIRE(pure && t0 && coef && dw && (mode == 1 || t1), "pw_wgrad: missing pointers");
+  B200DP_REQUIRE(pure && t0 && coef && dw && (mode == 1 || (t1 && asum)), "pw_wgrad: missing pointers");
   WgradParams p{};
   p.M = M;
   p.hidden = mode == 0 ? N : K;
   p.narrow = mode == 0 ? K : N;
   p.ldh = ld_t; p.ldq = ld_pure; p.ldw = ldw;
   p.coef = coef; p.dw = dw;
-  p.n128 = p.hidden / 128;
-  p.tail = p.hidden % 128;
-  B200DP_REQUIRE(p.tail % 64 == 0 || p.tail % 64 == 16 || p.tail % 64 == 32, "pw_wgrad: hidden=%d unsupported", p.hidden);
-  p.hchunks = p.n128 + (p.tail >= 64 ? 1 : 0) + (p.tail % 64 ? 1 : 0);
-  p.qchunks = (p.narrow + 255) / 256;
-  B200DP_REQUIRE(p.narrow % p.qchunks == 0 && (p.narrow / p.qchunks) % 16 == 0, "pw_wgrad: narrow=%d unsupported", p.narrow);
+  p.hchunks = (p.hidden + 127) / 128;
+  const int qmax = mode == 0 ? 128 : 256;                // MODE 0 keeps two accumulators per stage
+  p.qchunks = (p.narrow + qmax - 1) / qmax;
+  while (p.narrow % p.qchunks != 0 || (p.narrow / p.qchunks) % 16 != 0) ++p.qchunks;
   p.nq = p.narrow / p.qchunks;
-  p.nqp = p.nq % 64;
-  p.nqf = p.nq - p.nqp;
-  B200DP_REQUIRE(p.nqp == 0 || p.nqp == 16 || p.nqp == 32, "pw_wgrad: narrow chunk %d unsupported", p.nq);
-  const int row_bytes = 256 * (mode == 0 ? 2 : 1) + p.nq * 2;
-  p.mk = row_bytes <= 160 ? 256 : (row_bytes <= 352 ? 128 : 64);
-  const size_t stage_bytes = (size_t)p.mk * 256 * (mode == 0 ? 2 : 1) + (((size_t)p.mk * p.nq * 2 + 1023) & ~(size_t)1023);
+  p.qblks = (p.nq + 63) / 64;
+  const int row_bytes = 256 * (mode == 0 ? 2 : 1) + p.qblks * 128;
+  p.mk = row_bytes <= 384 ? 128 : 64;
+  const size_t stage_bytes = (size_t)p.mk * row_bytes;
   const size_t fixed = ((size_t)(mode == 0 ? 3 : 2) * p.hidden + 4) * 4 + (3 * MAX_STAGES + 4) * 8 + 16 + 1024;
   const size_t budget = 220 * 1024;
   int stages = (int)((budget - fixed) / stage_bytes);
@@ -384,6 +375,7 @@ int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure
   p.t0 = static_cast<const __nv_bfloat16*>(t0);
   p.t1 = static_cast<const __nv_bfloat16*>(t1);
   p.qsrc = static_cast<const __nv_bfloat16*>(pure);
+  p.asum = asum;
   const int items = hq * p.msplit;
   const int grid = items < cap ? items : cap;
   if (mode == 0) {
@@ -402,8 +394,8 @@ int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure
 using namespace b200dp;
 
 extern "C" int b200dp_pw_wgrad(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0,
-                               const void* t1, int ld_t, const float* coef, float* dw, int ldw, int max_ctas,
-                               void* stream) {
-  return pw_wgrad_launch(mode, M, N, K, pure, ld_pure, t0, t1, ld_t, coef, dw, ldw, max_ctas,
+                               const void* t1, int ld_t, const float* coef, const float* asum, float* dw, int ldw,
+                               int max_ctas, void* stream) {
+  return pw_wgrad_launch(mode, M, N, K, pure, ld_pure, t0, t1, ld_t, coef, asum, dw, ldw, max_ctas,
                          static_cast<cudaStream_t>(stream));
 }

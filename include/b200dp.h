@@ -145,9 +145,10 @@ int b200dp_pw_gemm(int amode, int emode, int M, int N, int K, const void* a_tma,
                    const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas,
                    void* stream);
 /* Pointwise conv weight gradient dw[N][ldw] += G^T A on tcgen05 with MN-major operands (csrc/pw_wgrad.cu).
- * mode 0: `pure` = A [M,K]; G = coef[0]*t0 + coef[1]*t1 + coef[2].  mode 1: `pure` = G [M,N]; A = relu6(coef[0]*t0 + coef[1]). */
+ * mode 0: `pure` = A [M,K]; G = coef[0]*t0 + coef[1]*t1 + coef[2]; `asum` = [K] column sums of A over all rows (the
+ * affine map is factored out of the reduction).  mode 1: `pure` = G [M,N]; A = relu6(coef[0]*t0 + coef[1]); asum unused. */
 int b200dp_pw_wgrad(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
-                    int ld_t, const float* coef, float* dw, int ldw, int max_ctas, void* stream);
+                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, void* stream);
 /* Depthwise 3x3 (pad 1, stride 1|2): y = dwconv(relu6(scale*x + shift)), w fp32 [9][C];
  * stats (may be NULL) [2][stats_stride] += sum(y), sum(y^2): a scratch accumulator that must be zero on entry. */
 int b200dp_dw_fwd(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,

@@ -158,8 +158,9 @@ def pw_wgrad(dw: torch.Tensor, *, a: Optional[torch.Tensor] = None, dz: Optional
         mode, pure, t0, t1, ldp, ldt = 1, _chk(g, torch.bfloat16, "g"), _chk(a_raw, torch.bfloat16, "a_raw"), None, N, K
     M = pure.shape[0]
     _chk(coef, torch.float32, "coef")
-    check(lib.b200dp_pw_wgrad(mode, M, N, K, ptr(pure), ldp, ptr(t0), ptr(t1), ldt, ptr(coef), ptr(dw), K, max_ctas,
-                              current_stream()))
+    asum = a.float().sum(0).contiguous() if mode == 0 else None     # the BN-backward affine is factored out of the reduction
+    check(lib.b200dp_pw_wgrad(mode, M, N, K, ptr(pure), ldp, ptr(t0), ptr(t1), ldt, ptr(coef), ptr(asum), ptr(dw), K,
+                              max_ctas, current_stream()))
     return dw
 
 
