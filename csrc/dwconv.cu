@@ -67,25 +67,36 @@ dw_fwd_kernel(const DwFwdParams P) {
       const int iy0 = y0 * S - 1;
       const __nv_bfloat16* xin = P.x + (size_t)n * P.H * P.W * P.C + c0;
       __nv_bfloat16* yout = P.y + (size_t)n * P.Ho * P.Wo * P.C + c0;
-      uint32_t rmask = 0;
+      // row pointers and 0/1 row masks are loop invariants of the sweep (out-of-image rows read row 0 and are
+      // multiplied by 0): the column loop is left with one IMAD per load and no per-element predicates
+      const __nv_bfloat16* rp[R];
+      float rm[R];
 #pragma unroll
-      for (int r = 0; r < R; ++r) rmask |= ((iy0 + r) >= 0 && (iy0 + r) < P.H) ? (1u << r) : 0u;
+      for (int r = 0; r < R; ++r) {
+        const int iy = iy0 + r;
+        const bool ok = iy >= 0 && iy < P.H;
+        rp[r] = xin + (size_t)(ok ? iy : 0) * P.W * P.C;
+        rm[r] = ok ? 1.f : 0.f;
+      }
       auto fetch = [&](int xi, uint32_t (&raw)[R]) {
-        const bool xok = xi >= 0 && xi < P.W;
+        const int xc = min(max(xi, 0), P.W - 1);
+        const size_t co = (size_t)xc * P.C;
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-          raw[r] = (xok && ((rmask >> r) & 1u)) ? ldg4(xin + ((size_t)(iy0 + r) * P.W + xi) * P.C) : 0u;
+        for (int r = 0; r < R; ++r) raw[r] = ldg4(rp[r] + co);
       };
       // zero padding is post-activation: out-of-image taps contribute 0, not relu6(shift)
       auto xform = [&](int xi, const uint32_t (&raw)[R], float (&a)[R], float (&b)[R]) {
-        const bool xok = xi >= 0 && xi < P.W;
+        const float cm = (xi >= 0 && xi < P.W) ? 1.f : 0.f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          const bool ok = xok && ((rmask >> r) & 1u);
-          a[r] = ok ? relu6f(fmaf(bf16_lo(raw[r]), sca, sha)) : 0.f;
-          b[r] = ok ? relu6f(fmaf(bf16_hi(raw[r]), scb, shb)) : 0.f;
+          const float m = rm[r] * cm;
+          a[r] = relu6f(fmaf(bf16_lo(raw[r]), sca, sha)) * m;
+          b[r] = relu6f(fmaf(bf16_hi(raw[r]), scb, shb)) * m;
         }
       };
+      __nv_bfloat16* yrow[TH];
+#pragma unroll
+      for (int t = 0; t < TH; ++t) yrow[t] = yout + (size_t)min(y0 + t, P.Ho - 1) * P.Wo * P.C;
       float pa[R], pb[R], ca[R], cb[R], na[R], nb[R];     // previous / centre / next input column (2 channels)
       uint32_t n0[R], n1[R];
       if (S == 1) {
@@ -118,7 +129,7 @@ dw_fwd_kernel(const DwFwdParams P) {
               acca = fmaf(wa[ky * 3 + 2], na[r], acca); accb = fmaf(wb[ky * 3 + 2], nb[r], accb);
             }
             const uint32_t o = pack_bf16x2(acca, accb);
-            *reinterpret_cast<uint32_t*>(yout + ((size_t)(y0 + t) * P.Wo + xo) * P.C) = o;
+            *reinterpret_cast<uint32_t*>(yrow[t] + (size_t)xo * P.C) = o;
             const float qa = bf16_lo(o), qb = bf16_hi(o);   // statistics of the values the consumer will read
             s0a += qa; s0b += qb;
             s1a = fmaf(qa, qa, s1a); s1b = fmaf(qb, qb, s1b);
@@ -212,32 +223,37 @@ dw_bwd_kernel(const DwBwdParams P) {
       };
       if (S == 1) {
         constexpr int R = TH + 2;                   // output rows ho = h0-1 .. h0+TH
-        uint32_t rmask = 0;
+        const __nv_bfloat16 *zp[R], *gp[R], *ep[TH];
+        float rm[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) rmask |= ((h0 - 1 + r) >= 0 && (h0 - 1 + r) < P.Ho) ? (1u << r) : 0u;
+        for (int r = 0; r < R; ++r) {
+          const int ho = h0 - 1 + r;
+          const bool ok = ho >= 0 && ho < P.Ho;
+          const size_t ro = (size_t)(ok ? ho : 0) * P.Wo * P.C;
+          zp[r] = gz + ro;
+          gp[r] = gr + ro;
+          rm[r] = ok ? 1.f : 0.f;
+        }
+#pragma unroll
+        for (int t = 0; t < TH; ++t) ep[t] = ein + (size_t)min(h0 + t, P.H - 1) * P.W * P.C;
         auto fetch = [&](int wo, uint32_t (&z)[R], uint32_t (&g)[R]) {
-          const bool ok = wo >= 0 && wo < P.Wo;
+          const size_t co = (size_t)min(max(wo, 0), P.Wo - 1) * P.C;
 #pragma unroll
-          for (int r = 0; r < R; ++r) {
-            const bool v = ok && ((rmask >> r) & 1u);
-            const size_t off = ((size_t)(h0 - 1 + r) * P.Wo + wo) * P.C;
-            z[r] = v ? ldg4(gz + off) : 0u;
-            g[r] = v ? ldg4(gr + off) : 0u;
-          }
+          for (int r = 0; r < R; ++r) { z[r] = ldg4(zp[r] + co); g[r] = ldg4(gp[r] + co); }
         };
         auto xform = [&](int wo, const uint32_t (&z)[R], const uint32_t (&g)[R], float (&a)[R], float (&b)[R]) {
-          const bool ok = wo >= 0 && wo < P.Wo;
+          const float cm = (wo >= 0 && wo < P.Wo) ? 1.f : 0.f;
 #pragma unroll
           for (int r = 0; r < R; ++r) {
-            const bool v = ok && ((rmask >> r) & 1u);
-            a[r] = v ? fmaf(kaa, bf16_lo(z[r]), fmaf(kba, bf16_lo(g[r]), kca)) : 0.f;
-            b[r] = v ? fmaf(kab, bf16_hi(z[r]), fmaf(kbb, bf16_hi(g[r]), kcb)) : 0.f;
+            const float m = rm[r] * cm;
+            a[r] = fmaf(kaa, bf16_lo(z[r]), fmaf(kba, bf16_lo(g[r]), kca)) * m;
+            b[r] = fmaf(kab, bf16_hi(z[r]), fmaf(kbb, bf16_hi(g[r]), kcb)) * m;
           }
         };
         auto fetch_e = [&](int w, uint32_t (&e)[TH]) {
+          const size_t co = (size_t)min(w, P.W - 1) * P.C;
 #pragma unroll
-          for (int t = 0; t < TH; ++t)
-            e[t] = (w < P.W && h0 + t < P.H) ? ldg4(ein + ((size_t)(h0 + t) * P.W + w) * P.C) : 0u;
+          for (int t = 0; t < TH; ++t) e[t] = ldg4(ep[t] + co);
         };
         float pa[R], pb[R], ca[R], cb[R], na[R], nb[R];
         uint32_t nz[R], ng[R], ne[TH], ec[TH];
@@ -277,28 +293,36 @@ dw_bwd_kernel(const DwBwdParams P) {
         // h0 is even (TH == 2): rows h0 = 2r, h0+1; output rows r, r+1.  Column pairs (2c, 2c+1), output cols c, c+1.
         const int r0 = h0 >> 1;
         const int cs = ws >> 1, ce = (we + 1) >> 1;     // segments start at even columns (seglen is even)
-        auto fetch = [&](int wo, uint32_t (&z)[2], uint32_t (&g)[2]) {
+        const __nv_bfloat16 *zp[2], *gp[2], *ep[2];
+        float rm[2];
 #pragma unroll
-          for (int r = 0; r < 2; ++r) {
-            const bool v = wo >= 0 && wo < P.Wo && (r0 + r) < P.Ho;
-            const size_t off = ((size_t)(r0 + r) * P.Wo + wo) * P.C;
-            z[r] = v ? ldg4(gz + off) : 0u;
-            g[r] = v ? ldg4(gr + off) : 0u;
-          }
+        for (int r = 0; r < 2; ++r) {
+          const bool ok = (r0 + r) < P.Ho;
+          const size_t ro = (size_t)(ok ? r0 + r : 0) * P.Wo * P.C;
+          zp[r] = gz + ro;
+          gp[r] = gr + ro;
+          rm[r] = ok ? 1.f : 0.f;
+          ep[r] = ein + (size_t)min(h0 + r, P.H - 1) * P.W * P.C;
+        }
+        auto fetch = [&](int wo, uint32_t (&z)[2], uint32_t (&g)[2]) {
+          const size_t co = (size_t)min(max(wo, 0), P.Wo - 1) * P.C;
+#pragma unroll
+          for (int r = 0; r < 2; ++r) { z[r] = ldg4(zp[r] + co); g[r] = ldg4(gp[r] + co); }
         };
         auto xform = [&](int wo, const uint32_t (&z)[2], const uint32_t (&g)[2], float (&a)[2], float (&b)[2]) {
+          const float cm = (wo >= 0 && wo < P.Wo) ? 1.f : 0.f;
 #pragma unroll
           for (int r = 0; r < 2; ++r) {
-            const bool v = wo >= 0 && wo < P.Wo && (r0 + r) < P.Ho;
-            a[r] = v ? fmaf(kaa, bf16_lo(z[r]), fmaf(kba, bf16_lo(g[r]), kca)) : 0.f;
-            b[r] = v ? fmaf(kab, bf16_hi(z[r]), fmaf(kbb, bf16_hi(g[r]), kcb)) : 0.f;
+            const float m = rm[r] * cm;
+            a[r] = fmaf(kaa, bf16_lo(z[r]), fmaf(kba, bf16_lo(g[r]), kca)) * m;
+            b[r] = fmaf(kab, bf16_hi(z[r]), fmaf(kbb, bf16_hi(g[r]), kcb)) * m;
           }
         };
-        auto fetch_e = [&](int c, uint32_t (&e)[4]) {    // e[2*dy + dx]
+        auto fetch_e = [&](int c, uint32_t (&e)[4]) {    // e[2*dy + dx]; out-of-image pixels are masked where used
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            const int h = h0 + (q >> 1), w = 2 * c + (q & 1);
-            e[q] = (h < P.H && w < P.W) ? ldg4(ein + ((size_t)h * P.W + w) * P.C) : 0u;
+            const int w = min(2 * c + (q & 1), P.W - 1);
+            e[q] = ldg4(ep[q >> 1] + (size_t)w * P.C);
           }
         };
         float d0a[2], d0b[2], d1a[2], d1b[2];
