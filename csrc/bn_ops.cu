@@ -20,6 +20,8 @@ __global__ void bn_fwd_finalize_kernel(const float* __restrict__ sums, int strid
                                        float* __restrict__ rmean, float* __restrict__ rvar,
                                        float* __restrict__ coef /*[2][C] scale, shift*/,
                                        float* __restrict__ saved /*[2][C] mean, invstd*/, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float mean = sums[c] / count;
@@ -40,6 +42,8 @@ __global__ void bn_fwd_finalize_kernel(const float* __restrict__ sums, int strid
 __global__ void bn_eval_coef_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
                                     const float* __restrict__ rmean, const float* __restrict__ rvar, float eps,
                                     float* __restrict__ coef, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float sc = gamma[c] * rsqrtf(rvar[c] + eps);
@@ -52,6 +56,8 @@ __global__ void bn_eval_coef_kernel(const float* __restrict__ gamma, const float
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ sums, int stride, const float* __restrict__ saved,
                                        const float* __restrict__ gamma, float count, float* __restrict__ coef3,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float mean = saved[c], r = saved[C + c], g = gamma[c];
@@ -81,6 +87,8 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
 __global__ void __launch_bounds__(256)
 affine_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
               const float* __restrict__ coef, int three, __nv_bfloat16* __restrict__ out, long long rows, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int CG = C >> 3;
   const long long total = rows * CG;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -108,6 +116,8 @@ grad_join_stats_kernel(const __nv_bfloat16* __restrict__ g1, const __nv_bfloat16
                        const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dout,
                        float* __restrict__ sums, int stride, long long rows, int C) {
   extern __shared__ float s_red[];   // [2][C]
+  pdl_trigger();
+  pdl_wait();
   const int CG = C >> 3;
   const int ipb = blockDim.x / CG;
   const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
@@ -156,6 +166,8 @@ block_out_kernel(const __nv_bfloat16* __restrict__ raw, const __nv_bfloat16* __r
                  const float* __restrict__ coef, __nv_bfloat16* __restrict__ out, float* __restrict__ colsum,
                  long long rows, int C) {
   extern __shared__ float s_red[];   // [C]
+  pdl_trigger();
+  pdl_wait();
   const int CG = C >> 3;
   const int ipb = blockDim.x / CG;
   const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
@@ -196,6 +208,8 @@ struct WPrepEntry { long long off; int n, k; };
 __global__ void __launch_bounds__(256)
 weight_prep_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt,
                    const WPrepEntry* __restrict__ table) {
+  pdl_trigger();
+  pdl_wait();
   const WPrepEntry e = table[blockIdx.y];
   const int total = e.n * e.k;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -211,22 +225,22 @@ weight_prep_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__
 int bn_fwd_finalize_launch(const float* sums, int stride, const float* gamma, const float* beta, float count,
                            float eps, float momentum, float* rmean, float* rvar, float* coef, float* saved, int C,
                            cudaStream_t s) {
-  bn_fwd_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(sums, stride, gamma, beta, count, eps, momentum, rmean, rvar,
-                                                         coef, saved, C);
+  B200DP_CUDA(launch_k(bn_fwd_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, s, sums, stride, gamma, beta, count, eps, momentum, rmean, rvar,
+                                                         coef, saved, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int bn_eval_coef_launch(const float* gamma, const float* beta, const float* rmean, const float* rvar, float eps,
                         float* coef, int C, cudaStream_t s) {
-  bn_eval_coef_kernel<<<(C + 127) / 128, 128, 0, s>>>(gamma, beta, rmean, rvar, eps, coef, C);
+  B200DP_CUDA(launch_k(bn_eval_coef_kernel, dim3((C + 127) / 128), dim3(128), 0, s, gamma, beta, rmean, rvar, eps, coef, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int bn_bwd_finalize_launch(const float* sums, int stride, const float* saved, const float* gamma, float count,
                            float* coef3, float* dgamma, float* dbeta, int C, cudaStream_t s) {
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, s>>>(sums, stride, saved, gamma, count, coef3, dgamma, dbeta, C);
+  B200DP_CUDA(launch_k(bn_bwd_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, s, sums, stride, saved, gamma, count, coef3, dgamma, dbeta, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -238,8 +252,8 @@ int affine_launch(const void* a, const void* b, const float* coef, int three, vo
   long long blocks = (total + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  affine_kernel<<<(int)blocks, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b),
-                                            coef, three, static_cast<__nv_bfloat16*>(out), rows, C);
+  B200DP_CUDA(launch_k(affine_kernel, dim3((unsigned)blocks), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(a),
+                       static_cast<const __nv_bfloat16*>(b), coef, three, static_cast<__nv_bfloat16*>(out), rows, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -254,9 +268,9 @@ int block_out_launch(const void* raw, const void* res, const float* coef, void* 
   long long blocks = (rows + ipb - 1) / ipb;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  block_out_kernel<<<(int)blocks, threads, C * sizeof(float), s>>>(
-      static_cast<const __nv_bfloat16*>(raw), static_cast<const __nv_bfloat16*>(res), coef,
-      static_cast<__nv_bfloat16*>(out), colsum, rows, C);
+  B200DP_CUDA(launch_k(block_out_kernel, dim3((unsigned)blocks), dim3(threads), C * sizeof(float), s,
+                       static_cast<const __nv_bfloat16*>(raw), static_cast<const __nv_bfloat16*>(res), coef,
+                       static_cast<__nv_bfloat16*>(out), colsum, rows, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -270,17 +284,17 @@ int grad_join_stats_launch(const void* g1, const void* g2, const void* x, void* 
   long long blocks = (rows + ipb - 1) / ipb;
   const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
-  grad_join_stats_kernel<<<(int)blocks, threads, 2 * C * sizeof(float), s>>>(
-      static_cast<const __nv_bfloat16*>(g1), static_cast<const __nv_bfloat16*>(g2),
-      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(dout), sums, stride, rows, C);
+  B200DP_CUDA(launch_k(grad_join_stats_kernel, dim3((unsigned)blocks), dim3(threads), 2 * C * sizeof(float), s,
+                       static_cast<const __nv_bfloat16*>(g1), static_cast<const __nv_bfloat16*>(g2),
+                       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(dout), sums, stride, rows, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int weight_prep_launch(const float* master, void* w, void* wt, const void* table_dev, int nlayers, cudaStream_t s) {
   dim3 grid(32, nlayers);
-  weight_prep_kernel<<<grid, 256, 0, s>>>(master, static_cast<__nv_bfloat16*>(w), static_cast<__nv_bfloat16*>(wt),
-                                          static_cast<const WPrepEntry*>(table_dev));
+  B200DP_CUDA(launch_k(weight_prep_kernel, grid, dim3(256), 0, s, master, static_cast<__nv_bfloat16*>(w),
+                       static_cast<__nv_bfloat16*>(wt), static_cast<const WPrepEntry*>(table_dev)));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

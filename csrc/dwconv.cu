@@ -41,6 +41,8 @@ __device__ __forceinline__ uint32_t ldg4(const __nv_bfloat16* p) { return __ldg(
 template <int S>
 __global__ void __launch_bounds__(256, 2)
 dw_fwd_kernel(const DwFwdParams P) {
+  pdl_trigger();
+  pdl_wait();
   constexpr int R = (TH - 1) * S + 3;
   extern __shared__ float s_red[];                 // [2][C]
   const int CG = P.cgb;                            // channel pairs of this block: [blockIdx.y * cgb, +cgb)
@@ -177,6 +179,8 @@ struct DwBwdParams {
 template <int S>
 __global__ void __launch_bounds__(256, 2)
 dw_bwd_kernel(const DwBwdParams P) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float s_red[];                 // [2][C] stats + [9][C] dW
   const int CG = P.cgb;                            // channel pairs of this block: [blockIdx.y * cgb, +cgb)
   const int ipb = blockDim.x / CG;
@@ -425,8 +429,8 @@ int dw_fwd_launch(const void* x, const float* scale, const float* shift, const f
   if (blocks > cap) blocks = cap;
   const size_t smem = 2 * (size_t)C * sizeof(float);
   const dim3 grid((unsigned)blocks, (unsigned)csplit);
-  if (stride == 1) dw_fwd_kernel<1><<<grid, threads, smem, s>>>(P);
-  else dw_fwd_kernel<2><<<grid, threads, smem, s>>>(P);
+  if (stride == 1) B200DP_CUDA(launch_k(dw_fwd_kernel<1>, grid, dim3(threads), smem, s, P));
+  else B200DP_CUDA(launch_k(dw_fwd_kernel<2>, grid, dim3(threads), smem, s, P));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -455,8 +459,8 @@ int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, c
   if (blocks > cap) blocks = cap;
   const size_t smem = 11 * (size_t)C * sizeof(float);
   const dim3 grid((unsigned)blocks, (unsigned)csplit);
-  if (stride == 1) dw_bwd_kernel<1><<<grid, threads, smem, s>>>(P);
-  else dw_bwd_kernel<2><<<grid, threads, smem, s>>>(P);
+  if (stride == 1) B200DP_CUDA(launch_k(dw_bwd_kernel<1>, grid, dim3(threads), smem, s, P));
+  else B200DP_CUDA(launch_k(dw_bwd_kernel<2>, grid, dim3(threads), smem, s, P));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

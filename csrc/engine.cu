@@ -324,7 +324,11 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
   return B200DP_OK;
 }
 
-__global__ void bump_step_kernel(int* step) { *step += 1; }
+__global__ void bump_step_kernel(int* step) {
+  pdl_trigger();
+  pdl_wait();
+  *step += 1;
+}
 
 int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
   const int li = (int)e.convs.size() - 1;
@@ -399,7 +403,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       mark(e, s, "stem_wgrad", 0);
     }
   }
-  bump_step_kernel<<<1, 1, 0, s>>>(e.step_dev);
+  B200DP_CUDA(launch_k(bump_step_kernel, dim3(1), dim3(1), 0, s, e.step_dev));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -593,11 +597,14 @@ int b200dp_engine_profile_step(void* h, const uint8_t* images, const int64_t* la
   Engine* e = static_cast<Engine*>(h);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   e->profiling = true;
+  const bool pdl_saved = g_pdl;
+  g_pdl = false;                 // per-kernel event timing needs fully serialised launches
   e->prof_events.clear();
   mark(*e, s, "start");
   int rc = b200dp_engine_train_step(h, images, labels, aug, n, stream);
   mark(*e, s, "end");
   e->profiling = false;
+  g_pdl = pdl_saved;
   if (rc != B200DP_OK) return rc;
   B200DP_CUDA(cudaStreamSynchronize(s));
   std::string all;

@@ -14,6 +14,8 @@ __global__ void __launch_bounds__(128)
 softmax_xent_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels,
                     float* __restrict__ loss_out, float* __restrict__ dlogits, double* __restrict__ metrics,
                     int batch, int classes, float inv_mean) {
+  pdl_trigger();
+  pdl_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   __shared__ float s_loss[4];
@@ -129,6 +131,8 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
 __global__ void __launch_bounds__(256)
 head_pool_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ coef, float* __restrict__ pooled,
                  float* __restrict__ drop, int B, int HW, int C, float p_drop, uint32_t seed, const int* step) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const int b = blockIdx.y;
   if (c >= C) return;
@@ -152,6 +156,8 @@ head_pool_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restrict_
 __global__ void __launch_bounds__(512)
 head_fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w, const float* __restrict__ bias,
                float* __restrict__ logits, int C, int classes) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int j = warp; j < classes; j += blockDim.x >> 5) {
@@ -168,6 +174,8 @@ __global__ void __launch_bounds__(128)
 head_bwd_fc_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, const float* __restrict__ drop,
                    const float* __restrict__ w, float* __restrict__ dpool, float* __restrict__ dw,
                    float* __restrict__ dbias, int B, int HW, int C, int classes) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float s_dl[];    // [B][classes]
   for (int i = threadIdx.x; i < B * classes; i += blockDim.x) s_dl[i] = dlogits[i];
   __syncthreads();
@@ -205,6 +213,8 @@ __global__ void __launch_bounds__(256)
 head_bwd_mask_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ coef,
                      const float* __restrict__ dpool, __nv_bfloat16* __restrict__ dz, float* __restrict__ sums,
                      int stride, int B, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float s_red[];   // [2][C]
   const int CG = C >> 3;
   const int ipb = blockDim.x / CG;
@@ -256,15 +266,15 @@ head_bwd_mask_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restr
 int head_pool_launch(const void* raw, const float* coef, float* pooled, float* drop, int B, int HW, int C,
                      float p_drop, uint32_t seed, const int* step, cudaStream_t s) {
   dim3 grid((C + 255) / 256, B);
-  head_pool_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(raw), coef, pooled, drop, B, HW, C, p_drop,
-                                        seed, step);
+  B200DP_CUDA(launch_k(head_pool_kernel, grid, dim3(256), 0, s, static_cast<const __nv_bfloat16*>(raw), coef, pooled, drop, B,
+                       HW, C, p_drop, seed, step));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int head_fc_launch(const float* pooled, const float* w, const float* bias, float* logits, int B, int C, int classes,
                    cudaStream_t s) {
-  head_fc_kernel<<<B, 32 * (classes < 16 ? classes : 16), 0, s>>>(pooled, w, bias, logits, C, classes);
+  B200DP_CUDA(launch_k(head_fc_kernel, dim3(B), dim3(32 * (classes < 16 ? classes : 16)), 0, s, pooled, w, bias, logits, C, classes));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -274,8 +284,8 @@ int head_bwd_launch(const float* dlogits, const float* pooled, const float* drop
                     int B, int HW, int C, int classes, cudaStream_t s) {
   B200DP_REQUIRE(classes <= HEAD_MAX_CLASSES, "head: at most %d classes", HEAD_MAX_CLASSES);
   B200DP_REQUIRE((size_t)B * classes * 4 <= 48 * 1024, "head: batch too large for the shared dlogits tile");
-  head_bwd_fc_kernel<<<(C + 127) / 128, 128, (size_t)B * classes * sizeof(float), s>>>(dlogits, pooled, drop, w, dpool,
-                                                                                       dw, dbias, B, HW, C, classes);
+  B200DP_CUDA(launch_k(head_bwd_fc_kernel, dim3((C + 127) / 128), dim3(128), (size_t)B * classes * sizeof(float), s, dlogits,
+                       pooled, drop, w, dpool, dw, dbias, B, HW, C, classes));
   B200DP_CHECK_LAUNCH();
   const int CG = C / 8;
   B200DP_REQUIRE(C % 8 == 0 && CG <= 256, "head: C=%d unsupported", C);
@@ -285,9 +295,9 @@ int head_bwd_launch(const float* dlogits, const float* pooled, const float* drop
   long long blocks = (rows + ipb - 1) / ipb;
   const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
-  head_bwd_mask_kernel<<<(int)blocks, threads, 2 * C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(raw), coef,
-                                                                          dpool, static_cast<__nv_bfloat16*>(dz), sums,
-                                                                          stride, B, HW, C);
+  B200DP_CUDA(launch_k(head_bwd_mask_kernel, dim3((unsigned)blocks), dim3(threads), 2 * C * sizeof(float), s,
+                       static_cast<const __nv_bfloat16*>(raw), coef, (const float*)dpool, static_cast<__nv_bfloat16*>(dz), sums, stride,
+                       B, HW, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -301,8 +311,8 @@ extern "C" int b200dp_softmax_xent(const float* logits, const int64_t* labels, f
                                    float mean_over, void* stream) {
   B200DP_REQUIRE(logits && labels && batch > 0 && classes > 0, "softmax_xent: bad arguments");
   const float inv = mean_over > 0.f ? 1.f / mean_over : 1.f;
-  softmax_xent_kernel<<<(batch + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      logits, labels, loss_out, dlogits_out, metrics, batch, classes, inv);
+  B200DP_CUDA(launch_k(softmax_xent_kernel, dim3((batch + 3) / 4), dim3(128), 0, static_cast<cudaStream_t>(stream), logits, labels,
+                       loss_out, dlogits_out, metrics, batch, classes, inv));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

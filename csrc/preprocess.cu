@@ -78,6 +78,8 @@ template <int OC>
 __global__ void __launch_bounds__(256)
 preprocess_plain_kernel(const uint8_t* __restrict__ images, __nv_bfloat16* __restrict__ out, int size,
                         int rows_per_cta) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ unsigned char s_src[SRC * SRC * 3];
   const int img = blockIdx.y;
   const uint32_t* g = reinterpret_cast<const uint32_t*>(images + (size_t)img * SRC * SRC * 3);
@@ -188,6 +190,8 @@ template <int OC>
 __global__ void __launch_bounds__(1024)
 preprocess_aug_kernel(const uint8_t* __restrict__ images, const float* __restrict__ params,
                       __nv_bfloat16* __restrict__ out, int S) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ unsigned char smem[];
   unsigned char* s_src = smem;                      // 3072 B
   unsigned char* s_res = smem + SRC * SRC * 3;      // S*S*3 B
@@ -271,8 +275,8 @@ extern "C" int b200dp_preprocess(const uint8_t* images, const float* params, voi
   if (params == nullptr) {
     const int rows = 16;
     dim3 grid((size + rows - 1) / rows, batch);
-    if (out_channels == 4) preprocess_plain_kernel<4><<<grid, 256, 0, s>>>(images, out, size, rows);
-    else preprocess_plain_kernel<3><<<grid, 256, 0, s>>>(images, out, size, rows);
+    if (out_channels == 4) B200DP_CUDA(launch_k(preprocess_plain_kernel<4>, grid, dim3(256), 0, s, images, out, size, rows));
+    else B200DP_CUDA(launch_k(preprocess_plain_kernel<3>, grid, dim3(256), 0, s, images, out, size, rows));
     B200DP_CHECK_LAUNCH();
     return B200DP_OK;
   }
@@ -280,8 +284,8 @@ extern "C" int b200dp_preprocess(const uint8_t* images, const float* params, voi
   // per-device attribute; cheap enough to set on every call
   B200DP_CUDA(cudaFuncSetAttribute(preprocess_aug_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   B200DP_CUDA(cudaFuncSetAttribute(preprocess_aug_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  if (out_channels == 4) preprocess_aug_kernel<4><<<batch, 1024, smem, s>>>(images, params, out, size);
-  else preprocess_aug_kernel<3><<<batch, 1024, smem, s>>>(images, params, out, size);
+  if (out_channels == 4) B200DP_CUDA(launch_k(preprocess_aug_kernel<4>, dim3(batch), dim3(1024), smem, s, images, params, out, size));
+  else B200DP_CUDA(launch_k(preprocess_aug_kernel<3>, dim3(batch), dim3(1024), smem, s, images, params, out, size));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

@@ -148,6 +148,9 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  // everything above is on-chip set-up and overlaps the previous kernel's tail (PDL); global data from here on
+  pdl_trigger();
+  pdl_wait();
   for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) s_acoef[i] = P.acoef[i];
   for (int i = threadIdx.x; i < n_ecoef; i += blockDim.x) s_ecoef[i] = P.ecoef[i];
   for (int i = threadIdx.x; i < n_stats; i += blockDim.x) s_stats[i] = 0.f;
@@ -433,7 +436,8 @@ int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
   // always the architectural maximum: the attribute is function-global state, and CUDA-graph replays must not
   // depend on which layer set it last
   B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  kern<<<pl.grid, Layout<AMODE>::kThreads, pl.smem_bytes, s>>>(pl.tmA, pl.tmB, pl.tmAt, pl.tmBt, pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p);
+  B200DP_CUDA(launch_k(kern, dim3(pl.grid), dim3(Layout<AMODE>::kThreads), pl.smem_bytes, s, pl.tmA, pl.tmB, pl.tmAt, pl.tmBt,
+                       pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

@@ -119,9 +119,12 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc(tmem_slot, TMEM_COLS);
-  for (int i = threadIdx.x; i < ncoef; i += blockDim.x) s_coef[i] = P.coef[i];
   // operand tiles are zero-padded past the channels a chunk covers: start from all-zero stages
   for (int o = threadIdx.x * 16; o < stages * stage_bytes; o += blockDim.x * 16) sts16(smem_u32(base) + o, make_uint4(0u, 0u, 0u, 0u));
+  // on-chip set-up above overlaps the previous kernel's tail (PDL); global data from here on
+  pdl_trigger();
+  pdl_wait();
+  for (int i = threadIdx.x; i < ncoef; i += blockDim.x) s_coef[i] = P.coef[i];
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -380,10 +383,10 @@ int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure
   const int grid = items < cap ? items : cap;
   if (mode == 0) {
     B200DP_CUDA(cudaFuncSetAttribute(pw_wgrad_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    pw_wgrad_kernel<0><<<grid, 512, smem, s>>>(p);
+    B200DP_CUDA(launch_k(pw_wgrad_kernel<0>, dim3(grid), dim3(512), smem, s, p));
   } else {
     B200DP_CUDA(cudaFuncSetAttribute(pw_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    pw_wgrad_kernel<1><<<grid, 512, smem, s>>>(p);
+    B200DP_CUDA(launch_k(pw_wgrad_kernel<1>, dim3(grid), dim3(512), smem, s, p));
   }
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;

@@ -26,6 +26,8 @@ struct StemFwdParams {
 
 __global__ void __launch_bounds__(256)
 stem_fwd_kernel(const StemFwdParams P) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ __align__(16) float s_w[KT * CO];
   __shared__ float s_red[2 * CO];
   for (int i = threadIdx.x; i < KT * CO; i += blockDim.x) s_w[i] = P.w[i];
@@ -114,6 +116,8 @@ constexpr int DY_LD = 36;    // 32 channels + 4 pad: conflict-light float4 rows
 
 __global__ void __launch_bounds__(WG_WARPS * 32)
 stem_wgrad_kernel(const StemWgradParams P) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ __align__(16) float s_x[WG_WARPS][32][XS_LD];
   __shared__ __align__(16) float s_dy[WG_WARPS][32][DY_LD];
   __shared__ float s_dw[28 * CO];
@@ -214,7 +218,7 @@ int stem_fwd_launch(const void* x, const float* w, void* y, float* stats, int st
   long long blocks = (npix + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  stem_fwd_kernel<<<(int)blocks, 256, 0, s>>>(P);
+  B200DP_CUDA(launch_k(stem_fwd_kernel, dim3((unsigned)blocks), dim3(256), 0, s, P));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -229,7 +233,7 @@ int stem_wgrad_launch(const void* x, const void* dz, const void* yraw, const flo
   long long blocks = (nchunks + WG_WARPS - 1) / WG_WARPS;
   const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
-  stem_wgrad_kernel<<<(int)blocks, WG_WARPS * 32, 0, s>>>(P);
+  B200DP_CUDA(launch_k(stem_wgrad_kernel, dim3((unsigned)blocks), dim3(WG_WARPS * 32), 0, s, P));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
