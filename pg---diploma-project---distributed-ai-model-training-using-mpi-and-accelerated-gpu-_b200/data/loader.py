@@ -36,8 +36,16 @@ class Batch:
     ready: Optional["torch.cuda.Event"] = None   # recorded on the copy stream; wait before use
 
     def wait(self, stream: Optional["torch.cuda.Stream"] = None) -> "Batch":
+        """Make ``stream`` (default: current) wait for the H2D copies, and tell the caching allocator that the
+        tensors are used there.  Without ``record_stream`` the memory -- allocated on the copy stream -- is handed
+        to a later batch's copy as soon as Python drops this one, while the compute stream (which runs many steps
+        behind the host) has not read it yet: the GPU would then train on whichever batches were copied last."""
         if self.ready is not None:
-            (stream or torch.cuda.current_stream()).wait_event(self.ready)
+            st = stream or torch.cuda.current_stream()
+            st.wait_event(self.ready)
+            for t in (self.images, self.labels, self.params):
+                if t.is_cuda:
+                    t.record_stream(st)
         return self
 
 

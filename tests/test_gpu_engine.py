@@ -152,3 +152,27 @@ def test_native_engine_learns_and_roundtrips_checkpoint(env, tmp_path):
     assert (got - rl).abs().max().item() < 0.05 * rl.abs().max().item() + 0.1
     eng.fused.check_error()
     eng.close()
+
+
+def test_loader_batches_survive_host_running_ahead(env):
+    """The host enqueues steps far faster than the GPU executes them; a batch's device tensors must not be
+    recycled for a later H2D copy before the compute stream has consumed them (Batch.wait -> record_stream)."""
+    ops, en = env
+    from b200dp.data.datasets import SyntheticCIFAR10
+    from b200dp.data.loader import BatchLoader
+    from b200dp.parallel.sampler import PartitionSampler
+    ds = SyntheticCIFAR10(64 * 40, True).pin()
+    ld = BatchLoader(ds, PartitionSampler(len(ds), 1, 0, shuffle=False), 64, torch.device("cuda", 0), train=True,
+                     augment=False)
+    slow = torch.randn(4096, 4096, device="cuda")
+    sums = []
+    for b in ld:
+        b.wait()
+        for _ in range(6):                       # keep the compute stream busy so it lags behind the copies
+            slow = (slow @ slow).clamp_(-1, 1)
+        sums.append(b.labels.double().sum() + b.images.double().sum())
+    torch.cuda.synchronize()
+    got = torch.stack(sums).cpu()
+    want = torch.stack([ds.labels[i * 64:(i + 1) * 64].double().sum() + ds.images[i * 64:(i + 1) * 64].double().sum()
+                        for i in range(40)])
+    assert torch.equal(got, want)
