@@ -131,6 +131,6 @@ for name, mk in cases.items():
         continue
     fn, nbytes = mk()
     ms = timeit(fn)
-    print(f"{name:32s} {ms * 1e3:8.1f} us  {nbytes / 1e6:8.1f} MB  {nbytes / ms / 1e6:7.1f} GB/s  {nbytes / ms / 1e3 / HBM * 100:5.1f}% of measured HBM copy bw")
+    print(f"{name:32s} {ms * 1e3:8.1f} us  {nbytes / 1e6:8.1f} MB  {nbytes / ms / 1e6:7.1f} GB/s  {nbytes / (ms * 1e-3) / HBM * 100:5.1f}% of measured HBM copy bw")
     del fn
     torch.cuda.empty_cache()
