@@ -14,6 +14,10 @@ int dw_fwd_launch(const void* x, const float* scale, const float* shift, const f
 int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
                   const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
                   int H, int W, int C, int stride, cudaStream_t s);
+// dw_tc.cu: the same forward contract on the tensor cores (nine tap-shifted MMAs with diagonal weight matrices)
+bool dw_tc_supported(int B, int H, int W, int C, int stride);
+int dw_tc_fwd_launch(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
+                     int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s);
 // stem.cu
 int stem_fwd_launch(const void* x, const float* w, void* y, float* stats, int stats_stride, int B, int H, int W,
                     cudaStream_t s);

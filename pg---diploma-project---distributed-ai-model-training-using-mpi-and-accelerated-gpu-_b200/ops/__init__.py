@@ -165,15 +165,18 @@ def pw_wgrad(dw: torch.Tensor, *, a: Optional[torch.Tensor] = None, dz: Optional
 
 
 def dw_fwd(x: torch.Tensor, coef: torch.Tensor, w: torch.Tensor, stride: int,
-           stats: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Depthwise 3x3 on NHWC bf16 ``x`` [B,H,W,C] with relu6(coef[0]*x+coef[1]) applied on load; ``w`` fp32 [9,C]."""
+           stats: Optional[torch.Tensor] = None, impl: str = "simt") -> torch.Tensor:
+    """Depthwise 3x3 on NHWC bf16 ``x`` [B,H,W,C] with relu6(coef[0]*x+coef[1]) applied on load; ``w`` fp32 [9,C].
+
+    ``impl``: "simt" = register sliding-window kernel (dwconv.cu), "tc" = tcgen05 tap-shifted MMAs (dw_tc.cu)."""
     lib = _lib.require()
+    fn = lib.b200dp_dw_fwd_tc if impl == "tc" else lib.b200dp_dw_fwd
     _chk(x, torch.bfloat16, "x"); _chk(coef, torch.float32, "coef"); _chk(w, torch.float32, "w")
     B, H, W, Cn = x.shape
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     y = torch.empty((B, Ho, Wo, Cn), dtype=torch.bfloat16, device=x.device)
-    check(lib.b200dp_dw_fwd(ptr(x), ptr(coef), coef.data_ptr() + 4 * Cn, ptr(w), ptr(y), ptr(stats), Cn, B, H, W, Cn,
-                            stride, current_stream()))
+    check(fn(ptr(x), ptr(coef), coef.data_ptr() + 4 * Cn, ptr(w), ptr(y), ptr(stats), Cn, B, H, W, Cn, stride,
+             current_stream()))
     return y
 
 

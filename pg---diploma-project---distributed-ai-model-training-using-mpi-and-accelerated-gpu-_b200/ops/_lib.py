@@ -15,7 +15,7 @@ COMM_MAX_BLOCKS = 256
 AUG_NPARAM = 12
 
 _PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG_DIR, "lib", "libb200dp.so")
+LIB_PATH = os.environ.get("B200DP_LIB") or os.path.join(_PKG_DIR, "lib", "libb200dp.so")   # override: A/B runs of two builds
 
 _lib: Optional[C.CDLL] = None
 _load_error: Optional[str] = None
@@ -62,6 +62,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_pw_gemm": [i, i, i, i, i, vp, i, vp, vp, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
         "b200dp_pw_wgrad": [i, i, i, i, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
         "b200dp_dw_fwd": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
+        "b200dp_dw_fwd_tc": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "b200dp_dw_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, i, i, i, i, i, vp],
         "b200dp_stem_fwd": [vp, vp, vp, vp, i, i, i, i, vp],
         "b200dp_stem_wgrad": [vp, vp, vp, vp, vp, i, i, i, vp],

@@ -85,13 +85,13 @@ def pw_wgrad_project(h, hidden, cout):
     return (lambda: ops.pw_wgrad(dw, g=g, a_raw=d, coef=coef)), M * (hidden + cout) * 2
 
 
-def dw_fwd(h, c, stride):
+def dw_fwd(h, c, stride, impl="simt"):
     x = bf(B, h, h, c)
     coef = torch.rand(2, c, device=dev)
     w = torch.randn(9, c, device=dev)
     stats = torch.zeros(2, c, device=dev)
     ho = (h - 1) // stride + 1
-    return (lambda: ops.dw_fwd(x, coef, w, stride, stats)), B * (h * h + ho * ho) * c * 2
+    return (lambda: ops.dw_fwd(x, coef, w, stride, stats, impl=impl)), B * (h * h + ho * ho) * c * 2
 
 
 def dw_bwd(h, c, stride):
@@ -122,12 +122,29 @@ cases = {
     "dw_fwd_56_144_s1": lambda: dw_fwd(56, 144, 1),
     "dw_fwd_112_96_s2": lambda: dw_fwd(112, 96, 2),
     "dw_fwd_14_384_s1": lambda: dw_fwd(14, 384, 1),
+    "dw_fwd_tc_112_32_s1": lambda: dw_fwd(112, 32, 1, "tc"),
+    "dw_fwd_tc_112_96_s2": lambda: dw_fwd(112, 96, 2, "tc"),
+    "dw_fwd_tc_56_144_s1": lambda: dw_fwd(56, 144, 1, "tc"),
+    "dw_fwd_tc_56_144_s2": lambda: dw_fwd(56, 144, 2, "tc"),
+    "dw_fwd_tc_28_192_s1": lambda: dw_fwd(28, 192, 1, "tc"),
+    "dw_fwd_tc_28_192_s2": lambda: dw_fwd(28, 192, 2, "tc"),
+    "dw_fwd_tc_14_384_s1": lambda: dw_fwd(14, 384, 1, "tc"),
+    "dw_fwd_tc_14_576_s1": lambda: dw_fwd(14, 576, 1, "tc"),
+    "dw_fwd_tc_14_576_s2": lambda: dw_fwd(14, 576, 2, "tc"),
+    "dw_fwd_tc_7_960_s1": lambda: dw_fwd(7, 960, 1, "tc"),
+    "dw_fwd_simt_112_32_s1": lambda: dw_fwd(112, 32, 1),
+    "dw_fwd_simt_56_144_s2": lambda: dw_fwd(56, 144, 2),
+    "dw_fwd_simt_28_192_s1": lambda: dw_fwd(28, 192, 1),
+    "dw_fwd_simt_28_192_s2": lambda: dw_fwd(28, 192, 2),
+    "dw_fwd_simt_14_576_s1": lambda: dw_fwd(14, 576, 1),
+    "dw_fwd_simt_14_576_s2": lambda: dw_fwd(14, 576, 2),
+    "dw_fwd_simt_7_960_s1": lambda: dw_fwd(7, 960, 1),
     "dw_bwd_56_144_s1": lambda: dw_bwd(56, 144, 1),
     "dw_bwd_112_96_s2": lambda: dw_bwd(112, 96, 2),
     "dw_bwd_14_384_s1": lambda: dw_bwd(14, 384, 1),
 }
 for name, mk in cases.items():
-    if ns.only and ns.only != name:
+    if ns.only and ns.only not in name:
         continue
     fn, nbytes = mk()
     ms = timeit(fn)
