@@ -11,6 +11,7 @@
 //   x (finished, bf16) --expand GEMM [TMA A, stats epilogue]--> e_raw --dw conv [BN+ReLU6 on load, stats]--> d_raw
 //     --project GEMM [BN+ReLU6 prologue, stats epilogue]--> p_raw --affine (+x)--> next x
 // and the mirror image backwards; every expanded tensor is written once and read once per direction.
+#include <cstdlib>
 #include <map>
 #include <string>
 #include <vector>
@@ -81,6 +82,7 @@ struct Engine {
   WPrepEntry* wprep_dev = nullptr;
   int n_pw = 0;
   bool use_graphs = true;
+  bool dw_tiled = true;     // stride-1 depthwise convs on the TMA-tiled kernels (B200DP_DW_IMPL=simt: sliding-window kernels)
   cudaStream_t cap_stream = nullptr;   // graphs are captured here (the caller's stream may be the legacy default stream)
   bool eval_coef_valid = false;
   std::map<int, Plans> plans;
@@ -297,8 +299,12 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
       if (train) ENG_TRY(bn_fin_f(e, ce, (float)n * ce.hout * ce.hout, s));
       cin_raw = &ce;
     }
-    ENG_TRY(dw_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w, cd.raw,
-                          train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, cd.stride, s));
+    if (e.dw_tiled && dw_tile_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
+      ENG_TRY(dw_tile_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w,
+                                 cd.raw, train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, s));
+    else
+      ENG_TRY(dw_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w, cd.raw,
+                            train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, cd.stride, s));
     mark(e, s, "dw_fwd", b.cd);
     if (train) ENG_TRY(bn_fin_f(e, cd, (float)n * cd.hout * cd.hout, s));
     ENG_TRY(pw_gemm_launch(train ? pl.fwd[b.cp] : pl.fwd_eval[b.cp], s));
@@ -449,6 +455,10 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   e->params = params; e->grads = grads; e->buffers = buffers;
   e->param_total = param_total; e->buffer_total = buffer_total;
   e->use_graphs = use_graphs != 0;
+  {
+    const char* impl = getenv("B200DP_DW_IMPL");
+    e->dw_tiled = !(impl != nullptr && std::string(impl) == "simt");
+  }
   build_spec(*e, offsets);
   e->ws_bytes = layout_workspace(*e, nullptr) + 1024;
   cudaError_t err = cudaMalloc(&e->ws, e->ws_bytes);

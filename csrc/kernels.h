@@ -18,6 +18,10 @@ int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, c
 bool dw_tc_supported(int B, int H, int W, int C, int stride);
 int dw_tc_fwd_launch(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
                      int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s);
+// dw_tile.cu: stride-1 forward, TMA halo tiles in shared memory + register-window stencil on the CUDA cores
+bool dw_tile_supported(int B, int H, int W, int C, int stride);
+int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
+                       int stats_stride, int B, int H, int W, int C, cudaStream_t s);
 // stem.cu
 int stem_fwd_launch(const void* x, const float* w, void* y, float* stats, int stats_stride, int B, int H, int W,
                     cudaStream_t s);

@@ -139,6 +139,12 @@ cases = {
     "dw_fwd_simt_14_576_s1": lambda: dw_fwd(14, 576, 1),
     "dw_fwd_simt_14_576_s2": lambda: dw_fwd(14, 576, 2),
     "dw_fwd_simt_7_960_s1": lambda: dw_fwd(7, 960, 1),
+    "dw_fwd_tile_112_32_s1": lambda: dw_fwd(112, 32, 1, "tile"),
+    "dw_fwd_tile_56_144_s1": lambda: dw_fwd(56, 144, 1, "tile"),
+    "dw_fwd_tile_28_192_s1": lambda: dw_fwd(28, 192, 1, "tile"),
+    "dw_fwd_tile_14_384_s1": lambda: dw_fwd(14, 384, 1, "tile"),
+    "dw_fwd_tile_14_576_s1": lambda: dw_fwd(14, 576, 1, "tile"),
+    "dw_fwd_tile_7_960_s1": lambda: dw_fwd(7, 960, 1, "tile"),
     "dw_bwd_56_144_s1": lambda: dw_bwd(56, 144, 1),
     "dw_bwd_112_96_s2": lambda: dw_bwd(112, 96, 2),
     "dw_bwd_14_384_s1": lambda: dw_bwd(14, 384, 1),
