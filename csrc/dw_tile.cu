@@ -56,6 +56,10 @@ struct DwTileParams {
   int nstrips, par;         // strips per tile = NI*Ht*NSEG; strips processed concurrently = CONSUMERS / (w/4)
   int tiles_x, tiles_y, ntiles;
   uint32_t magic_wp, magic_hp, magic_tx, magic_ty, magic_nseg, magic_ht;
+  // backward only
+  const float* dcoef;       // [3][C] ca, cb, cc of the BatchNorm backward of THIS conv's output
+  float* dwg;               // [9][C] weight gradient (accumulated)
+  int Wq;                   // pixel pitch of the un-haloed e_raw box
 };
 
 __device__ __forceinline__ int fastdiv(int r, uint32_t m, int d) { return d == 1 ? r : (int)__umulhi((uint32_t)r, m); }
@@ -111,6 +115,20 @@ __device__ __forceinline__ uint32_t f2_to_bf16x2_relu(f2 a) {        // max(x, 0
 __device__ __forceinline__ uint32_t bf16x2_relu6(uint32_t v) {
   uint32_t r;
   asm("{\n\t.reg .b32 t;\n\tmax.bf16x2 t, %1, %2;\n\tmin.bf16x2 %0, t, %3;\n\t}" : "=r"(r) : "r"(v), "r"(0u), "r"(0x40C040C0u));
+  return r;
+}
+__device__ __forceinline__ f2 f2_pair(uint32_t lo_bits, uint32_t hi_bits) {
+  f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo_bits), "r"(hi_bits));
+  return r;
+}
+__device__ __forceinline__ void f2_split(f2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// NaN -> 0, everything else unchanged: max / min return the non-NaN operand, and one of max(v,0), min(v,0) is zero
+__device__ __forceinline__ uint32_t bf16x2_nan0(uint32_t v) {
+  uint32_t r;
+  asm("{\n\t.reg .b32 p, q;\n\tmax.bf16x2 p, %1, %2;\n\tmin.bf16x2 q, %1, %2;\n\tor.b32 %0, p, q;\n\t}" : "=r"(r) : "r"(v), "r"(0u));
   return r;
 }
 __device__ __forceinline__ void red_shared_f2(uint32_t addr, f2 v) {
@@ -304,6 +322,252 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Backward, stride 1 (same contract as dw_bwd_kernel<1> in dwconv.cu).  Per tile the copy engine lands three boxes:
+// the haloed dz and d_raw tiles of the conv OUTPUT side and the un-haloed e_raw tile of the input side.
+//   pass 1 (16 warps)  dd = ca*dz + cb*d_raw + cc -> bf16, in place of dz; the NaN halo becomes 0 (max(v,0) | min(v,0))
+//   pass 2, warps 0-7  data gradient: 3x3 window of dd against the flipped weights, ReLU6 mask from e_raw, store,
+//                      sums (dz_e, dz_e * e_raw) for the producer's BatchNorm backward
+//           warps 8-15 weight gradient: the same window times a = relu6(scale*e_raw + shift), 36 fp32 accumulators
+//                      per thread that live for the whole kernel
+// The two halves read the same shared-memory tile concurrently; neither has to fit both register sets.
+constexpr int BW_THREADS = 512, BW_GROUP = 256, BW_NST = 2;
+constexpr int HALO_BYTES = 36 * 1024, PLAIN_BYTES = 28 * 1024, BW_STAGE = 2 * HALO_BYTES + PLAIN_BYTES;
+
+__global__ void __launch_bounds__(BW_THREADS, 1)
+dw_tile_bwd_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ CUtensorMap tmG,
+                   const __grid_constant__ CUtensorMap tmE, const __grid_constant__ DwTileParams P) {
+  pdl_trigger();
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + BW_NST * BW_STAGE);
+  uint64_t* empty = full + BW_NST;
+  float* s_stats = reinterpret_cast<float*>(empty + BW_NST);     // [2][64]
+  float* s_ecoef = s_stats + 128;                                 // [2][64] scale, shift of the input-side BatchNorm
+  float* s_dcoef = s_ecoef + 128;                                 // [3][64] ca, cb, cc
+  float* s_dw = s_dcoef + 192;                                    // [9][64]
+
+  const int lane = threadIdx.x & 31;
+  const int w = P.w, rowbytes = 2 * w;
+  const int chunk = (int)blockIdx.x % P.nchunks, c0 = chunk * w;
+  const int tile0 = (int)blockIdx.x / P.nchunks, tstep = (int)gridDim.x / P.nchunks;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < BW_NST; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], BW_THREADS / 32);
+    }
+    fence_barrier_init();
+  }
+  for (int i = threadIdx.x; i < 128 + 9 * 64; i += BW_THREADS) (i < 128 ? s_stats[i] : s_dw[i - 128]) = 0.f;
+  pdl_wait();
+  if (threadIdx.x < w) {
+    s_ecoef[threadIdx.x] = P.scale[c0 + threadIdx.x];
+    s_ecoef[64 + threadIdx.x] = P.shift[c0 + threadIdx.x];
+    s_dcoef[threadIdx.x] = P.dcoef[c0 + threadIdx.x];
+    s_dcoef[64 + threadIdx.x] = P.dcoef[P.C + c0 + threadIdx.x];
+    s_dcoef[128 + threadIdx.x] = P.dcoef[2 * P.C + c0 + threadIdx.x];
+  }
+  __syncthreads();
+
+  const uint32_t halo_bytes = (uint32_t)(P.NI * P.Hp * P.Wp * rowbytes);
+  const uint32_t plain_bytes = (uint32_t)(P.NI * P.Ht * P.Wq * rowbytes);
+  auto issue = [&](int tile, int stage) {
+    int n0, y0, x0;
+    decode_tile(P, tile, n0, y0, x0);
+    uint8_t* st = base + stage * BW_STAGE;
+    mbar_arrive_expect_tx(&full[stage], 2 * halo_bytes + plain_bytes);
+    tma_load_4d(st, &tmZ, &full[stage], c0, x0 - 1, y0 - 1, n0);
+    tma_load_4d(st + HALO_BYTES, &tmG, &full[stage], c0, x0 - 1, y0 - 1, n0);
+    tma_load_4d(st + 2 * HALO_BYTES, &tmE, &full[stage], c0, x0, y0, n0);
+  };
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmZ); prefetch_tmap(&tmG); prefetch_tmap(&tmE);
+    for (int k = 0; k < BW_NST; ++k)
+      if (tile0 + k * tstep < P.ntiles) issue(tile0 + k * tstep, k);
+  }
+
+  const bool grp_b = threadIdx.x >= BW_GROUP;         // warps 8-15: weight gradient
+  const int t = threadIdx.x - (grp_b ? BW_GROUP : 0);
+  const int Q = w >> 2;
+  const int j = t % Q, sidx = t / Q;
+  const int cq = c0 + 4 * j;
+  int st_img, st_yy, st_xs;
+  {
+    const int q1 = fastdiv(sidx, P.magic_nseg, P.NSEG);
+    st_xs = (sidx - q1 * P.NSEG) * P.SL;
+    st_img = fastdiv(q1, P.magic_ht, P.Ht);
+    st_yy = q1 - st_img * P.Ht;
+  }
+  const bool active = sidx < P.nstrips;
+  const int st_xe = min(st_xs + P.SL, P.Wt);
+  const uint32_t st_off = ((st_img * P.Hp + st_yy) * P.Wp + st_xs) * rowbytes + (j << 3);
+  const uint32_t e_off = 2 * HALO_BYTES + ((st_img * P.Ht + st_yy) * P.Wq + st_xs) * rowbytes + (j << 3);
+  const uint32_t rpitch = P.Wp * rowbytes;
+  const size_t ystep = (size_t)P.C * 2;
+  // group A: flipped weights; group B: weight-gradient accumulators.  Same registers, different meaning.
+  f2 wa[9][2];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    float4 wv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!grp_b && active) wv = *reinterpret_cast<const float4*>(P.wts + (8 - k) * P.C + cq);
+    wa[k][0] = f2_make(wv.x, wv.y);
+    wa[k][1] = f2_make(wv.z, wv.w);
+  }
+  f2 s0[2], s1[2];
+  s0[0] = s0[1] = s1[0] = s1[1] = 0ull;
+  const f2 esc0 = f2_make(s_ecoef[4 * j], s_ecoef[4 * j + 1]), esc1 = f2_make(s_ecoef[4 * j + 2], s_ecoef[4 * j + 3]);
+  const f2 esh0 = f2_make(s_ecoef[64 + 4 * j], s_ecoef[64 + 4 * j + 1]);
+  const f2 esh1 = f2_make(s_ecoef[64 + 4 * j + 2], s_ecoef[64 + 4 * j + 3]);
+  // pass-1 role (all 512 threads): 16-byte units of the haloed tiles
+  const int U = w >> 3;
+  const int uj = threadIdx.x % U, ur0 = threadIdx.x / U, urstep = BW_THREADS / U;
+  const bool xf_active = ur0 < urstep;
+  const uint32_t xf_off = ur0 * rowbytes + (uj << 4), xf_step = urstep * rowbytes;
+  const uint32_t dc_addr = smem_u32(s_dcoef) + 32 * uj;
+
+  int it = 0;
+#pragma unroll 1
+  for (int tile = tile0; tile < P.ntiles; tile += tstep, ++it) {
+    const int stage = it % BW_NST, par = (it / BW_NST) & 1;
+    int n0, y0, x0;
+    decode_tile(P, tile, n0, y0, x0);
+    const uint32_t sbase = smem_u32(base + stage * BW_STAGE);
+    mbar_wait(&full[stage], par);
+    // ---- pass 1: dd = ca*dz + cb*d_raw + cc, in place of dz; NaN (halo outside the image) -> 0
+    if (xf_active) {
+      const uint4 ka0 = lds16(dc_addr), ka1 = lds16(dc_addr + 16);
+      const uint4 kb0 = lds16(dc_addr + 256), kb1 = lds16(dc_addr + 272);
+      const uint4 kc0 = lds16(dc_addr + 512), kc1 = lds16(dc_addr + 528);
+      const f2 ca[4] = {f2_pair(ka0.x, ka0.y), f2_pair(ka0.z, ka0.w), f2_pair(ka1.x, ka1.y), f2_pair(ka1.z, ka1.w)};
+      const f2 cb[4] = {f2_pair(kb0.x, kb0.y), f2_pair(kb0.z, kb0.w), f2_pair(kb1.x, kb1.y), f2_pair(kb1.z, kb1.w)};
+      const f2 cc[4] = {f2_pair(kc0.x, kc0.y), f2_pair(kc0.z, kc0.w), f2_pair(kc1.x, kc1.y), f2_pair(kc1.z, kc1.w)};
+#pragma unroll 2
+      for (uint32_t o = xf_off; o < halo_bytes; o += xf_step) {
+        const uint4 z = lds16(sbase + o), g = lds16(sbase + HALO_BYTES + o);
+        uint4 v;
+        v.x = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[0], f2_from_bf16x2(z.x), f2_fma(cb[0], f2_from_bf16x2(g.x), cc[0]))));
+        v.y = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[1], f2_from_bf16x2(z.y), f2_fma(cb[1], f2_from_bf16x2(g.y), cc[1]))));
+        v.z = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[2], f2_from_bf16x2(z.z), f2_fma(cb[2], f2_from_bf16x2(g.z), cc[2]))));
+        v.w = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[3], f2_from_bf16x2(z.w), f2_fma(cb[3], f2_from_bf16x2(g.w), cc[3]))));
+        sts16(sbase + o, v);
+      }
+    }
+    named_bar_sync(1, BW_THREADS);
+    // ---- pass 2
+    const int oy = y0 + st_yy, on = n0 + st_img;
+    const int xe = min(st_xe, P.W - x0);
+    if (active && oy < P.H && on < P.B && st_xs < xe) {
+      uint32_t a0 = sbase + st_off;
+      uint32_t a1 = a0 + rpitch, a2 = a1 + rpitch;
+      uint32_t ae = sbase + e_off;
+      f2 win[3][3][2];
+      auto load_col = [&](int slot) {
+        const uint2 v0 = lds8(a0), v1 = lds8(a1), v2 = lds8(a2);
+        a0 += rowbytes; a1 += rowbytes; a2 += rowbytes;
+        win[slot][0][0] = f2_from_bf16x2(v0.x); win[slot][0][1] = f2_from_bf16x2(v0.y);
+        win[slot][1][0] = f2_from_bf16x2(v1.x); win[slot][1][1] = f2_from_bf16x2(v1.y);
+        win[slot][2][0] = f2_from_bf16x2(v2.x); win[slot][2][1] = f2_from_bf16x2(v2.y);
+      };
+      if (!grp_b) {
+        char* yp = reinterpret_cast<char*>(P.y + (((size_t)on * P.H + oy) * P.W + x0 + st_xs) * P.C + cq);
+        auto emit = [&](int sl, int sm, int sr) {   // window slots holding dd columns x-1, x, x+1
+          const uint2 ev = lds8(ae);
+          ae += rowbytes;
+          const f2 e[2] = {f2_from_bf16x2(ev.x), f2_from_bf16x2(ev.y)};
+          const f2 z[2] = {f2_fma(e[0], esc0, esh0), f2_fma(e[1], esc1, esh1)};
+          uint2 o;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            f2 a = 0ull;
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+              a = f2_fma(wa[r * 3 + 0][h], win[sl][r][h], a);
+              a = f2_fma(wa[r * 3 + 1][h], win[sm][r][h], a);
+              a = f2_fma(wa[r * 3 + 2][h], win[sr][r][h], a);
+            }
+            float alo, ahi, zlo, zhi;
+            f2_split(a, alo, ahi);
+            f2_split(z[h], zlo, zhi);
+            alo = (zlo > 0.f && zlo < 6.f) ? alo : 0.f;
+            ahi = (zhi > 0.f && zhi < 6.f) ? ahi : 0.f;
+            const f2 m = f2_make(alo, ahi);
+            s0[h] = f2_add(s0[h], m);
+            s1[h] = f2_fma(m, e[h], s1[h]);
+            (h == 0 ? o.x : o.y) = f2_to_bf16x2(m);
+          }
+          *reinterpret_cast<uint2*>(yp) = o;
+          yp += ystep;
+        };
+        load_col(0);
+        load_col(1);
+        int x = st_xs;
+#pragma unroll 1
+        for (; x + 3 <= xe; x += 3) {
+          load_col(2); emit(0, 1, 2);
+          load_col(0); emit(1, 2, 0);
+          load_col(1); emit(2, 0, 1);
+        }
+        if (x < xe) { load_col(2); emit(0, 1, 2); ++x; }
+        if (x < xe) { load_col(0); emit(1, 2, 0); ++x; }
+      } else {
+        auto accum = [&](int sl, int sm, int sr) {
+          const uint2 ev = lds8(ae);
+          ae += rowbytes;
+          // a = the activation the forward pass fed to the conv: relu6 of the bf16-rounded BatchNorm output
+          const f2 act[2] = {f2_from_bf16x2(bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(ev.x), esc0, esh0)))),
+                             f2_from_bf16x2(bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(ev.y), esc1, esh1))))};
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+              // window (row r, column slot c) is dd[h+1-ky][w+1-kx] for ky = 2-r, kx = 2-c
+              wa[8 - (r * 3 + 0)][h] = f2_fma(act[h], win[sl][r][h], wa[8 - (r * 3 + 0)][h]);
+              wa[8 - (r * 3 + 1)][h] = f2_fma(act[h], win[sm][r][h], wa[8 - (r * 3 + 1)][h]);
+              wa[8 - (r * 3 + 2)][h] = f2_fma(act[h], win[sr][r][h], wa[8 - (r * 3 + 2)][h]);
+            }
+        };
+        load_col(0);
+        load_col(1);
+        int x = st_xs;
+#pragma unroll 1
+        for (; x + 3 <= xe; x += 3) {
+          load_col(2); accum(0, 1, 2);
+          load_col(0); accum(1, 2, 0);
+          load_col(1); accum(2, 0, 1);
+        }
+        if (x < xe) { load_col(2); accum(0, 1, 2); ++x; }
+        if (x < xe) { load_col(0); accum(1, 2, 0); ++x; }
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[stage]);
+    if (threadIdx.x == 0 && tile + BW_NST * tstep < P.ntiles) {
+      mbar_wait(&empty[stage], par);
+      issue(tile + BW_NST * tstep, stage);
+    }
+  }
+  if (active) {
+    if (!grp_b) {
+      const uint32_t sa = smem_u32(s_stats) + 16 * j;
+      red_shared_f2(sa, s0[0]); red_shared_f2(sa + 8, s0[1]);
+      red_shared_f2(sa + 256, s1[0]); red_shared_f2(sa + 264, s1[1]);
+    } else {
+      const uint32_t sa = smem_u32(s_dw) + 16 * j;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { red_shared_f2(sa + 256 * k, wa[k][0]); red_shared_f2(sa + 256 * k + 8, wa[k][1]); }
+    }
+  }
+  named_bar_sync(1, BW_THREADS);
+  for (int i = threadIdx.x; i < 11 * w; i += BW_THREADS) {
+    const int h = i / w, c = i - h * w;
+    if (h < 2) atomicAdd(P.stats + h * P.stats_stride + c0 + c, s_stats[h * 64 + c]);
+    else atomicAdd(P.dwg + (h - 2) * P.C + c0 + c, s_dw[(h - 2) * 64 + c]);
+  }
+}
+
+
 uint32_t magic(int d) { return (uint32_t)(((1ull << 32) + (uint64_t)d - 1) / (uint64_t)d); }
 
 int encode_nhwc(CUtensorMap* out, const void* base, int B, int H, int W, int C, int box_c, int box_w, int box_h, int box_n) {
@@ -346,10 +610,10 @@ int chunk_width(int C) {
 }
 
 // tile shape: maximise (thread utilisation) x (useful fraction of the haloed box) x (segment prologue) x (edge waste)
-void pick_tile(DwTileParams& P) {
+void pick_tile(DwTileParams& P, int halo_limit = STAGE_BYTES, int plain_limit = 0) {
   const int Q = P.wbox / 4;
   P.par = CONSUMERS / Q;
-  const int max_px = STAGE_BYTES / (2 * P.wbox);
+  const int max_px = halo_limit / (2 * P.wbox);
   double best = -1.0;
   const int wcand[4] = {P.W < 28 ? P.W : 28, 21, 14, 7};
   for (int wi = 0; wi < 4; ++wi) {
@@ -361,6 +625,7 @@ void pick_tile(DwTileParams& P) {
       for (int NI = 1; NI <= 4 && NI <= P.B; ++NI) {
         const int Hp = Ht + 2;
         if (NI * Hp * Wp > max_px) continue;
+        if (plain_limit > 0 && NI * Ht * (Wp - 2) * 2 * P.wbox > plain_limit) continue;
         for (int NSEG = 1; NSEG <= 4; ++NSEG) {
           const int SL = (Wt + NSEG - 1) / NSEG;
           if (SL < 5 && NSEG > 1) continue;
@@ -380,6 +645,7 @@ void pick_tile(DwTileParams& P) {
         }
       }
   }
+  P.Wq = P.Wp - 2;           // un-haloed box: same pitch parity as the haloed one
   P.nstrips = P.NI * P.Ht * P.NSEG;
   P.tiles_x = (P.W + P.Wt - 1) / P.Wt;
   P.tiles_y = (P.H + P.Ht - 1) / P.Ht;
@@ -420,6 +686,36 @@ int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, co
   return B200DP_OK;
 }
 
+int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
+                       const float* dcoef, const float* wts, void* dze, float* stats, int stats_stride, float* dw, int B,
+                       int H, int W, int C, cudaStream_t s) {
+  B200DP_REQUIRE(dw_tile_supported(B, H, W, C, 1), "dw_tile_bwd: B=%d H=%d W=%d C=%d unsupported", B, H, W, C);
+  B200DP_REQUIRE(stats != nullptr && dw != nullptr, "dw_tile_bwd: stats / dw missing");
+  DwTileParams P{};
+  P.scale = escale; P.shift = eshift; P.wts = wts; P.y = static_cast<__nv_bfloat16*>(dze);
+  P.stats = stats; P.stats_stride = stats_stride; P.dcoef = dcoef; P.dwg = dw;
+  P.B = B; P.H = H; P.W = W; P.C = C;
+  P.w = chunk_width(C);
+  P.nchunks = C / P.w;
+  P.wbox = P.w;
+  pick_tile(P, HALO_BYTES, PLAIN_BYTES);
+  P.magic_wp = magic(P.Wp); P.magic_hp = magic(P.Hp); P.magic_tx = magic(P.tiles_x); P.magic_ty = magic(P.tiles_y);
+  P.magic_nseg = magic(P.NSEG); P.magic_ht = magic(P.Ht);
+  CUtensorMap tmZ, tmG, tmE;
+  if (int rc = encode_nhwc(&tmZ, dzd, B, H, W, C, P.w, P.Wp, P.Hp, P.NI)) return rc;
+  if (int rc = encode_nhwc(&tmG, d_raw, B, H, W, C, P.w, P.Wp, P.Hp, P.NI)) return rc;
+  if (int rc = encode_nhwc(&tmE, e_raw, B, H, W, C, P.w, P.Wq, P.Ht, P.NI)) return rc;
+  int groups = num_sms() / P.nchunks;
+  if (groups < 1) groups = 1;
+  if (groups > P.ntiles) groups = P.ntiles;
+  const int grid = groups * P.nchunks;
+  const size_t smem = 128 + BW_NST * BW_STAGE + 2 * BW_NST * 8 + (128 + 128 + 192 + 576) * 4;
+  B200DP_CUDA(cudaFuncSetAttribute(dw_tile_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  B200DP_CUDA(launch_k(dw_tile_bwd_kernel, dim3((unsigned)grid), dim3(BW_THREADS), smem, s, tmZ, tmG, tmE, P));
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
 }  // namespace b200dp
 
 using namespace b200dp;
@@ -428,4 +724,12 @@ extern "C" int b200dp_dw_fwd_tile(const void* x, const float* scale, const float
                                   float* stats, int stats_stride, int B, int H, int W, int C, int stride, void* stream) {
   B200DP_REQUIRE(stride == 1, "dw_fwd_tile: stride 1 only");
   return dw_tile_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int b200dp_dw_bwd_tile(const void* e_raw, const float* escale, const float* eshift, const void* dzd,
+                                  const void* d_raw, const float* dcoef, const float* w, void* dze, float* stats,
+                                  int stats_stride, float* dw, int B, int H, int W, int C, int stride, void* stream) {
+  B200DP_REQUIRE(stride == 1, "dw_bwd_tile: stride 1 only");
+  return dw_tile_bwd_launch(e_raw, escale, eshift, dzd, d_raw, dcoef, w, dze, stats, stats_stride, dw, B, H, W, C,
+                            static_cast<cudaStream_t>(stream));
 }

@@ -384,9 +384,14 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     ENG_TRY(bn_fin_b(e, cd, (float)rows_out, s));
     // ---- depthwise conv backward (data + weight gradient, mask, statistics for the producer's BatchNorm)
     Conv& cin_raw = b.ce >= 0 ? e.convs[b.ce] : e.convs[0];
-    ENG_TRY(dw_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
-                          e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
-                          cd.hin, cd.coutp, cd.stride, s));
+    if (e.dw_tiled && dw_tile_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
+      ENG_TRY(dw_tile_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
+                                 e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                                 cd.hin, cd.coutp, s));
+    else
+      ENG_TRY(dw_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
+                            e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                            cd.hin, cd.coutp, cd.stride, s));
     mark(e, s, "dw_bwd", b.cd);
     const long long rows_in = (long long)n * b.hin * b.hin;
     ENG_TRY(bn_fin_b(e, cin_raw, (float)rows_in, s));

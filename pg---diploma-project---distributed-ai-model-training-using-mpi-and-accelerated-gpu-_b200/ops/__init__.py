@@ -182,11 +182,12 @@ def dw_fwd(x: torch.Tensor, coef: torch.Tensor, w: torch.Tensor, stride: int,
 
 
 def dw_bwd(e_raw: torch.Tensor, ecoef: torch.Tensor, dzd: torch.Tensor, d_raw: torch.Tensor, dcoef: torch.Tensor,
-           w: torch.Tensor, stride: int, stats: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
+           w: torch.Tensor, stride: int, stats: torch.Tensor, dw: torch.Tensor, impl: str = "simt") -> torch.Tensor:
     lib = _lib.require()
+    fn = lib.b200dp_dw_bwd_tile if impl == "tile" else lib.b200dp_dw_bwd
     B, H, W, Cn = e_raw.shape
     dze = torch.empty_like(e_raw)
-    check(lib.b200dp_dw_bwd(ptr(e_raw), ptr(ecoef), ecoef.data_ptr() + 4 * Cn, ptr(dzd), ptr(d_raw), ptr(dcoef), ptr(w),
+    check(fn(ptr(e_raw), ptr(ecoef), ecoef.data_ptr() + 4 * Cn, ptr(dzd), ptr(d_raw), ptr(dcoef), ptr(w),
                             ptr(dze), ptr(stats), Cn, ptr(dw), B, H, W, Cn, stride, current_stream()))
     return dze
 

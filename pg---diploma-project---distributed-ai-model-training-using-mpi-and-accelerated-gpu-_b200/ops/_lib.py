@@ -65,6 +65,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_dw_fwd_tc": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "b200dp_dw_fwd_tile": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "b200dp_dw_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, i, i, i, i, i, vp],
+        "b200dp_dw_bwd_tile": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, i, i, i, i, i, vp],
         "b200dp_stem_fwd": [vp, vp, vp, vp, i, i, i, i, vp],
         "b200dp_stem_wgrad": [vp, vp, vp, vp, vp, i, i, i, vp],
         "b200dp_bn_fwd_finalize": [vp, i, vp, vp, f, f, f, vp, vp, vp, vp, i, vp],

@@ -94,13 +94,13 @@ def dw_fwd(h, c, stride, impl="simt"):
     return (lambda: ops.dw_fwd(x, coef, w, stride, stats, impl=impl)), B * (h * h + ho * ho) * c * 2
 
 
-def dw_bwd(h, c, stride):
+def dw_bwd(h, c, stride, impl="simt"):
     ho = (h - 1) // stride + 1
     e, dzd, d = bf(B, h, h, c), bf(B, ho, ho, c), bf(B, ho, ho, c)
     ecoef, dcoef = torch.rand(2, c, device=dev), torch.rand(3, c, device=dev)
     w = torch.randn(9, c, device=dev)
     stats, dw = torch.zeros(2, c, device=dev), torch.zeros(9, c, device=dev)
-    return (lambda: ops.dw_bwd(e, ecoef, dzd, d, dcoef, w, stride, stats, dw)), B * (2 * h * h + 2 * ho * ho) * c * 2
+    return (lambda: ops.dw_bwd(e, ecoef, dzd, d, dcoef, w, stride, stats, dw, impl=impl)), B * (2 * h * h + 2 * ho * ho) * c * 2
 
 
 cases = {
@@ -148,6 +148,18 @@ cases = {
     "dw_bwd_56_144_s1": lambda: dw_bwd(56, 144, 1),
     "dw_bwd_112_96_s2": lambda: dw_bwd(112, 96, 2),
     "dw_bwd_14_384_s1": lambda: dw_bwd(14, 384, 1),
+    "dw_bwd_simt_112_32_s1": lambda: dw_bwd(112, 32, 1, "simt"),
+    "dw_bwd_simt_56_144_s1": lambda: dw_bwd(56, 144, 1, "simt"),
+    "dw_bwd_simt_28_192_s1": lambda: dw_bwd(28, 192, 1, "simt"),
+    "dw_bwd_simt_14_384_s1": lambda: dw_bwd(14, 384, 1, "simt"),
+    "dw_bwd_simt_14_576_s1": lambda: dw_bwd(14, 576, 1, "simt"),
+    "dw_bwd_simt_7_960_s1": lambda: dw_bwd(7, 960, 1, "simt"),
+    "dw_bwd_tile_112_32_s1": lambda: dw_bwd(112, 32, 1, "tile"),
+    "dw_bwd_tile_56_144_s1": lambda: dw_bwd(56, 144, 1, "tile"),
+    "dw_bwd_tile_28_192_s1": lambda: dw_bwd(28, 192, 1, "tile"),
+    "dw_bwd_tile_14_384_s1": lambda: dw_bwd(14, 384, 1, "tile"),
+    "dw_bwd_tile_14_576_s1": lambda: dw_bwd(14, 576, 1, "tile"),
+    "dw_bwd_tile_7_960_s1": lambda: dw_bwd(7, 960, 1, "tile"),
 }
 for name, mk in cases.items():
     if ns.only and ns.only not in name:

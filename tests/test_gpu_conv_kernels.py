@@ -44,9 +44,13 @@ def test_dw_fwd(ops, B, H, C, stride, impl):
     assert torch.allclose(stats[1], (y.float() ** 2).sum((0, 1, 2)), rtol=2e-3, atol=0.5)
 
 
+@pytest.mark.parametrize("impl", ["simt", "tile"])
 @pytest.mark.parametrize("B,H,C,stride", [(4, 28, 192, 1), (3, 56, 96, 2), (2, 14, 576, 1), (3, 7, 960, 1),
-                                          (2, 112, 32, 1), (3, 15, 144, 2), (70, 14, 384, 1)])
-def test_dw_bwd(ops, B, H, C, stride):
+                                          (2, 112, 32, 1), (3, 15, 144, 2), (70, 14, 384, 1), (2, 56, 144, 1),
+                                          (5, 7, 960, 1)])
+def test_dw_bwd(ops, B, H, C, stride, impl):
+    if impl == "tile" and stride != 1:
+        pytest.skip("the tiled kernel is stride 1 only")
     torch.manual_seed(C + H + 1)
     Ho = (H - 1) // stride + 1
     e_raw = _bf(torch.randn(B, H, H, C, device="cuda") * 2)
@@ -57,7 +61,7 @@ def test_dw_bwd(ops, B, H, C, stride):
     w = (torch.randn(9, C, device="cuda") * 0.3).contiguous()
     stats = torch.zeros(2, C, device="cuda")
     dw = torch.zeros(9, C, device="cuda")
-    dze = ops.dw_bwd(e_raw, ecoef, dzd, d_raw, dcoef, w, stride, stats, dw)
+    dze = ops.dw_bwd(e_raw, ecoef, dzd, d_raw, dcoef, w, stride, stats, dw, impl=impl)
     # reference with autograd
     z = e_raw.float() * ecoef[0] + ecoef[1]
     a = z.clamp(0, 6).permute(0, 3, 1, 2).detach().requires_grad_(True)
