@@ -82,124 +82,188 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
                     pack_bf16x2(f[6], f[7]));
 }
 
-// out = c0*a + c1 (+ res)            (forward block output)
-// out = c0*a + c1*b + c2             (three = 1: BatchNorm backward apply)
+// The three passes below share one shape.  A thread owns one 8-channel group for its whole life (its coefficients
+// and partial sums stay in registers), a block owns a contiguous range of rows, and every trip issues FOUR
+// independent 16-byte loads per operand before touching any of them -- these tensors are small (<= 51 MB), the
+// kernels are latency-bound, and bytes in flight are what buys bandwidth.  Per-channel sums are reduced through a
+// [row slot][C] staging array in shared memory and one atomic per channel per block (the earlier version did
+// blockDim.x shared atomics onto C <= 32 addresses, a 64- to 128-way serialisation per block).
+constexpr int NP_UNROLL = 4;
+
+struct RowRange { long long begin, end; };
+__device__ __forceinline__ RowRange block_rows(long long rows) {
+  const long long per = (rows + gridDim.x - 1) / gridDim.x;
+  RowRange r;
+  r.begin = (long long)blockIdx.x * per;
+  r.end = r.begin + per < rows ? r.begin + per : rows;
+  return r;
+}
+
+// s_part[ti][C] holds this block's partial sums for `nstat` statistics; add them to dst[k * stride + c]
+__device__ __forceinline__ void flush_partials(const float* s_part, int nstat, int ipb, int C, float* dst, int stride) {
+  __syncthreads();
+  for (int i = threadIdx.x; i < nstat * C; i += blockDim.x) {
+    const int k = i / C, c = i - k * C;
+    const float* p = s_part + (size_t)k * ipb * C + c;
+    float a = 0.f;
+    for (int t = 0; t < ipb; ++t) a += p[(size_t)t * C];
+    atomicAdd(dst + (size_t)k * stride + c, a);
+  }
+}
+
+// out = c0*a + c1*b + c2             (BatchNorm backward apply of the projection conv)
 __global__ void __launch_bounds__(256)
 affine_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
               const float* __restrict__ coef, int three, __nv_bfloat16* __restrict__ out, long long rows, int C) {
   pdl_trigger();
   pdl_wait();
   const int CG = C >> 3;
-  const long long total = rows * CG;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % CG);
-    const int c0 = cg * 8;
-    float x[8], y[8], o[8];
-    unpack8(ldg_stream(a + i * 8), x);
-    const bool hasb = b != nullptr;
-    if (hasb) unpack8(ldg_stream(b + i * 8), y);
+  const int ipb = blockDim.x / CG;
+  const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
+  float k0[8], k1[8], k2[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float k0 = __ldg(coef + c0 + j), k1 = __ldg(coef + C + c0 + j);
-      if (three) o[j] = fmaf(k0, x[j], fmaf(k1, y[j], __ldg(coef + 2 * C + c0 + j)));
-      else o[j] = fmaf(k0, x[j], k1) + (hasb ? y[j] : 0.f);
+  for (int j = 0; j < 8; ++j) {
+    k0[j] = coef[cg * 8 + j];
+    k1[j] = coef[C + cg * 8 + j];
+    k2[j] = three ? coef[2 * C + cg * 8 + j] : 0.f;
+  }
+  const bool hasb = b != nullptr;
+  const RowRange rr = block_rows(rows);
+  for (long long r0 = rr.begin + ti; r0 < rr.end; r0 += (long long)ipb * NP_UNROLL) {
+    uint4 va[NP_UNROLL], vb[NP_UNROLL];
+#pragma unroll
+    for (int u = 0; u < NP_UNROLL; ++u) {
+      const long long r = r0 + (long long)u * ipb;
+      if (r < rr.end) {
+        va[u] = ldg_stream(a + r * C + cg * 8);
+        if (hasb) vb[u] = ldg_stream(b + r * C + cg * 8);
+      }
     }
-    stg_stream(out + i * 8, pack8(o));
+#pragma unroll
+    for (int u = 0; u < NP_UNROLL; ++u) {
+      const long long r = r0 + (long long)u * ipb;
+      if (r < rr.end) {
+        float x[8], y[8], o[8];
+        unpack8(va[u], x);
+        if (hasb) unpack8(vb[u], y);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (three) o[j] = fmaf(k0[j], x[j], fmaf(k1[j], y[j], k2[j]));
+          else o[j] = fmaf(k0[j], x[j], k1[j]) + (hasb ? y[j] : 0.f);
+        }
+        stg_stream(out + r * C + cg * 8, pack8(o));
+      }
+    }
   }
 }
 
 // dout = g1 (+ g2) [written only when g2 != null], sums += (sum dout, sum dout*x) per channel.
-// Each thread keeps one 8-channel group for its whole life (grid stride is a multiple of CG).
 __global__ void __launch_bounds__(256)
 grad_join_stats_kernel(const __nv_bfloat16* __restrict__ g1, const __nv_bfloat16* __restrict__ g2,
                        const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dout,
                        float* __restrict__ sums, int stride, long long rows, int C) {
-  extern __shared__ float s_red[];   // [2][C]
+  extern __shared__ float s_part[];   // [2][ipb][C]
   pdl_trigger();
   pdl_wait();
   const int CG = C >> 3;
   const int ipb = blockDim.x / CG;
   const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_red[i] = 0.f;
-  __syncthreads();
-  if (ti < ipb) {
-    float s0[8], s1[8];
+  float s0[8], s1[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
-    for (long long r = (long long)blockIdx.x * ipb + ti; r < rows; r += (long long)gridDim.x * ipb) {
-      const long long off = r * C + cg * 8;
-      float a[8], xv[8];
-      unpack8(ldg_stream(g1 + off), a);
-      unpack8(ldg_stream(x + off), xv);
-      if (g2 != nullptr) {
-        float b[8];
-        unpack8(ldg_stream(g2 + off), b);
+  for (int j = 0; j < 8; ++j) s0[j] = s1[j] = 0.f;
+  const bool join = g2 != nullptr;
+  const RowRange rr = block_rows(rows);
+  for (long long r0 = rr.begin + ti; r0 < rr.end; r0 += (long long)ipb * NP_UNROLL) {
+    uint4 va[NP_UNROLL], vx[NP_UNROLL], vb[NP_UNROLL];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] += b[j];
-        const uint4 pk = pack8(a);
-        stg_stream(dout + off, pk);
-        unpack8(pk, a);
+    for (int u = 0; u < NP_UNROLL; ++u) {
+      const long long r = r0 + (long long)u * ipb;
+      if (r < rr.end) {
+        va[u] = ldg_stream(g1 + r * C + cg * 8);
+        vx[u] = ldg_stream(x + r * C + cg * 8);
+        if (join) vb[u] = ldg_stream(g2 + r * C + cg * 8);
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { s0[j] += a[j]; s1[j] = fmaf(a[j], xv[j], s1[j]); }
     }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&s_red[cg * 8 + j], s0[j]);
-      atomicAdd(&s_red[C + cg * 8 + j], s1[j]);
+    for (int u = 0; u < NP_UNROLL; ++u) {
+      const long long r = r0 + (long long)u * ipb;
+      if (r < rr.end) {
+        float a[8], xv[8];
+        unpack8(va[u], a);
+        unpack8(vx[u], xv);
+        if (join) {
+          float bq[8];
+          unpack8(vb[u], bq);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a[j] += bq[j];
+          const uint4 pk = pack8(a);
+          stg_stream(dout + r * C + cg * 8, pk);
+          unpack8(pk, a);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s0[j] += a[j]; s1[j] = fmaf(a[j], xv[j], s1[j]); }
+      }
     }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(sums + i, s_red[i]);
-    atomicAdd(sums + stride + i, s_red[C + i]);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    s_part[(size_t)ti * C + cg * 8 + j] = s0[j];
+    s_part[(size_t)(ipb + ti) * C + cg * 8 + j] = s1[j];
   }
+  flush_partials(s_part, 2, ipb, C, sums, stride);
 }
-
 
 // Block output: out = scale*raw + shift (+ res), and the per-channel column sums of the ROUNDED result.  The next
 // expand conv's weight gradient factors its BatchNorm-backward affine out of the reduction and needs sum_m x[m][k].
-// Each thread keeps one 8-channel group for its whole life (like grad_join_stats_kernel).
 __global__ void __launch_bounds__(256)
 block_out_kernel(const __nv_bfloat16* __restrict__ raw, const __nv_bfloat16* __restrict__ res,
                  const float* __restrict__ coef, __nv_bfloat16* __restrict__ out, float* __restrict__ colsum,
                  long long rows, int C) {
-  extern __shared__ float s_red[];   // [C]
+  extern __shared__ float s_part[];   // [ipb][C]
   pdl_trigger();
   pdl_wait();
   const int CG = C >> 3;
   const int ipb = blockDim.x / CG;
   const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_red[i] = 0.f;
-  __syncthreads();
-  if (ti < ipb) {
-    float k0[8], k1[8], acc[8];
+  float k0[8], k1[8], acc[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { k0[j] = coef[cg * 8 + j]; k1[j] = coef[C + cg * 8 + j]; acc[j] = 0.f; }
-    for (long long r = (long long)blockIdx.x * ipb + ti; r < rows; r += (long long)gridDim.x * ipb) {
-      const long long off = r * C + cg * 8;
-      float x[8], y[8], o[8];
-      unpack8(ldg_stream(raw + off), x);
-      if (res != nullptr) unpack8(ldg_stream(res + off), y);
+  for (int j = 0; j < 8; ++j) { k0[j] = coef[cg * 8 + j]; k1[j] = coef[C + cg * 8 + j]; acc[j] = 0.f; }
+  const bool hasr = res != nullptr;
+  const RowRange rr = block_rows(rows);
+  for (long long r0 = rr.begin + ti; r0 < rr.end; r0 += (long long)ipb * NP_UNROLL) {
+    uint4 va[NP_UNROLL], vr[NP_UNROLL];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = fmaf(k0[j], x[j], k1[j]) + (res != nullptr ? y[j] : 0.f);
-      const uint4 pk = pack8(o);
-      stg_stream(out + off, pk);
-      if (colsum != nullptr) {
-        unpack8(pk, o);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += o[j];
+    for (int u = 0; u < NP_UNROLL; ++u) {
+      const long long r = r0 + (long long)u * ipb;
+      if (r < rr.end) {
+        va[u] = ldg_stream(raw + r * C + cg * 8);
+        if (hasr) vr[u] = ldg_stream(res + r * C + cg * 8);
       }
     }
-    if (colsum != nullptr) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(&s_red[cg * 8 + j], acc[j]);
+    for (int u = 0; u < NP_UNROLL; ++u) {
+      const long long r = r0 + (long long)u * ipb;
+      if (r < rr.end) {
+        float x[8], y[8], o[8];
+        unpack8(va[u], x);
+        if (hasr) unpack8(vr[u], y);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = fmaf(k0[j], x[j], k1[j]) + (hasr ? y[j] : 0.f);
+        const uint4 pk = pack8(o);
+        stg_stream(out + r * C + cg * 8, pk);
+        if (colsum != nullptr) {
+          unpack8(pk, o);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += o[j];
+        }
+      }
     }
   }
-  __syncthreads();
-  if (colsum != nullptr)
-    for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(colsum + i, s_red[i]);
+  if (colsum != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s_part[(size_t)ti * C + cg * 8 + j] = acc[j];
+    flush_partials(s_part, 1, ipb, C, colsum, 0);
+  }
 }
 
 // Weight preparation: fp32 master [N][K] -> bf16 [N][K] and bf16 transposed [K][N] for every pointwise conv.
@@ -245,19 +309,26 @@ int bn_bwd_finalize_launch(const float* sums, int stride, const float* saved, co
   return B200DP_OK;
 }
 
+// grid: enough blocks for two per SM, fewer when the tensor is tiny (every block pays one reduction tail)
+static int narrow_grid(long long rows, int ipb) {
+  long long blocks = (rows + (long long)ipb * NP_UNROLL - 1) / ((long long)ipb * NP_UNROLL);
+  const long long cap = (long long)num_sms() * 2;
+  if (blocks > cap) blocks = cap;
+  return blocks < 1 ? 1 : (int)blocks;
+}
+
 int affine_launch(const void* a, const void* b, const float* coef, int three, void* out, long long rows, int C,
                   cudaStream_t s) {
-  B200DP_REQUIRE(C % 8 == 0, "affine: C must be a multiple of 8");
-  const long long total = rows * (C / 8);
-  long long blocks = (total + 255) / 256;
-  const long long cap = (long long)num_sms() * 8;
-  if (blocks > cap) blocks = cap;
-  B200DP_CUDA(launch_k(affine_kernel, dim3((unsigned)blocks), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(a),
-                       static_cast<const __nv_bfloat16*>(b), coef, three, static_cast<__nv_bfloat16*>(out), rows, C));
+  B200DP_REQUIRE(C % 8 == 0 && C / 8 <= 256, "affine: C=%d unsupported", C);
+  const int CG = C / 8;
+  const int threads = (256 / CG) * CG;
+  const int ipb = threads / CG;
+  B200DP_CUDA(launch_k(affine_kernel, dim3((unsigned)narrow_grid(rows, ipb)), dim3(threads), 0, s,
+                       static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), coef, three,
+                       static_cast<__nv_bfloat16*>(out), rows, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
-
 
 int block_out_launch(const void* raw, const void* res, const float* coef, void* out, float* colsum, long long rows,
                      int C, cudaStream_t s) {
@@ -265,12 +336,9 @@ int block_out_launch(const void* raw, const void* res, const float* coef, void* 
   const int CG = C / 8;
   const int threads = (256 / CG) * CG;
   const int ipb = threads / CG;
-  long long blocks = (rows + ipb - 1) / ipb;
-  const long long cap = (long long)num_sms() * 8;
-  if (blocks > cap) blocks = cap;
-  B200DP_CUDA(launch_k(block_out_kernel, dim3((unsigned)blocks), dim3(threads), C * sizeof(float), s,
-                       static_cast<const __nv_bfloat16*>(raw), static_cast<const __nv_bfloat16*>(res), coef,
-                       static_cast<__nv_bfloat16*>(out), colsum, rows, C));
+  B200DP_CUDA(launch_k(block_out_kernel, dim3((unsigned)narrow_grid(rows, ipb)), dim3(threads),
+                       (size_t)ipb * C * sizeof(float), s, static_cast<const __nv_bfloat16*>(raw),
+                       static_cast<const __nv_bfloat16*>(res), coef, static_cast<__nv_bfloat16*>(out), colsum, rows, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -281,12 +349,10 @@ int grad_join_stats_launch(const void* g1, const void* g2, const void* x, void* 
   const int CG = C / 8;
   const int threads = (256 / CG) * CG;
   const int ipb = threads / CG;
-  long long blocks = (rows + ipb - 1) / ipb;
-  const long long cap = (long long)num_sms() * 4;
-  if (blocks > cap) blocks = cap;
-  B200DP_CUDA(launch_k(grad_join_stats_kernel, dim3((unsigned)blocks), dim3(threads), 2 * C * sizeof(float), s,
-                       static_cast<const __nv_bfloat16*>(g1), static_cast<const __nv_bfloat16*>(g2),
-                       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(dout), sums, stride, rows, C));
+  B200DP_CUDA(launch_k(grad_join_stats_kernel, dim3((unsigned)narrow_grid(rows, ipb)), dim3(threads),
+                       2 * (size_t)ipb * C * sizeof(float), s, static_cast<const __nv_bfloat16*>(g1),
+                       static_cast<const __nv_bfloat16*>(g2), static_cast<const __nv_bfloat16*>(x),
+                       static_cast<__nv_bfloat16*>(dout), sums, stride, rows, C));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -321,4 +387,8 @@ extern "C" int b200dp_affine(const void* a, const void* b, const float* coef, in
 extern "C" int b200dp_grad_join_stats(const void* g1, const void* g2, const void* x, void* dout, float* sums,
                                       int stride, long long rows, int C, void* stream) {
   return grad_join_stats_launch(g1, g2, x, dout, sums, stride, rows, C, static_cast<cudaStream_t>(stream));
+}
+extern "C" int b200dp_block_out(const void* raw, const void* res, const float* coef, void* out, float* colsum,
+                                long long rows, int C, void* stream) {
+  return block_out_launch(raw, res, coef, out, colsum, rows, C, static_cast<cudaStream_t>(stream));
 }

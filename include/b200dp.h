@@ -181,6 +181,10 @@ int b200dp_affine(const void* a, const void* b, const float* coef, int three, vo
                   void* stream);
 int b200dp_grad_join_stats(const void* g1, const void* g2, const void* x, void* dout, float* sums, int stride,
                            long long rows, int C, void* stream);
+/* Block output of an inverted residual: out = coef[0]*raw + coef[1] (+ res); colsum (may be NULL) [C] += column sums of
+ * the rounded result (the next expand conv's factored weight gradient needs them). */
+int b200dp_block_out(const void* raw, const void* res, const float* coef, void* out, float* colsum, long long rows,
+                     int C, void* stream);
 
 /* Depthwise conv + the BatchNorm coefficients of its output, with NO device allocation by anyone.
  * This entry point has no counterpart in the reference.

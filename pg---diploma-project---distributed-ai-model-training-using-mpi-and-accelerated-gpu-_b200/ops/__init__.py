@@ -205,3 +205,33 @@ def stem_wgrad(x4: torch.Tensor, dz: torch.Tensor, yraw: torch.Tensor, coef: tor
     B, H, W, _ = x4.shape
     check(lib.b200dp_stem_wgrad(ptr(x4), ptr(dz), ptr(yraw), ptr(coef), ptr(dw), B, H, W, current_stream()))
     return dw
+
+
+def affine(a: torch.Tensor, b: Optional[torch.Tensor], coef: torch.Tensor, three: bool) -> torch.Tensor:
+    """``three``: out = coef[0]*a + coef[1]*b + coef[2] (BatchNorm backward apply); else out = coef[0]*a + coef[1] (+ b)."""
+    lib = _lib.require()
+    C = a.shape[-1]
+    out = torch.empty_like(a)
+    check(lib.b200dp_affine(ptr(a), ptr(b), ptr(coef), int(three), ptr(out), a.numel() // C, C, current_stream()))
+    return out
+
+
+def grad_join_stats(g1: torch.Tensor, g2: Optional[torch.Tensor], x: torch.Tensor, sums: torch.Tensor):
+    """dout = g1 (+ g2); sums[0] += sum dout, sums[1] += sum dout*x per channel.  Returns dout (g1 itself if g2 is None)."""
+    lib = _lib.require()
+    C = g1.shape[-1]
+    dout = torch.empty_like(g1) if g2 is not None else None
+    check(lib.b200dp_grad_join_stats(ptr(g1), ptr(g2), ptr(x), ptr(dout), ptr(sums), C, g1.numel() // C, C,
+                                     current_stream()))
+    return dout if dout is not None else g1
+
+
+def block_out(raw: torch.Tensor, res: Optional[torch.Tensor], coef: torch.Tensor,
+              colsum: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out = coef[0]*raw + coef[1] (+ res); colsum[C] += column sums of the rounded result."""
+    lib = _lib.require()
+    C = raw.shape[-1]
+    out = torch.empty_like(raw)
+    check(lib.b200dp_block_out(ptr(raw), ptr(res), ptr(coef), ptr(out), ptr(colsum), raw.numel() // C, C,
+                               current_stream()))
+    return out

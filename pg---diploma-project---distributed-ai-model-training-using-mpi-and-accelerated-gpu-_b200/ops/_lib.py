@@ -71,6 +71,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_bn_fwd_finalize": [vp, i, vp, vp, f, f, f, vp, vp, vp, vp, i, vp],
         "b200dp_bn_bwd_finalize": [vp, i, vp, vp, f, vp, vp, vp, i, vp],
         "b200dp_affine": [vp, vp, vp, i, vp, ll, i, vp],
+        "b200dp_block_out": [vp, vp, vp, vp, vp, ll, i, vp],
         "b200dp_grad_join_stats": [vp, vp, vp, vp, vp, i, ll, i, vp],
     }
     for name, args in sigs.items():

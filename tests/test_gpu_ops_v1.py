@@ -155,3 +155,34 @@ def test_fused_allreduce_adam_multi_rank(world):
                        timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-4000:] + r.stderr[-4000:]
     assert "COMM CHECK OK" in r.stdout
+
+
+@pytest.mark.parametrize("rows,C", [(1000, 16), (12544 * 3, 32), (777, 96), (49 * 5, 320), (5, 64), (3136 * 2, 160)])
+def test_narrow_passes(rows, C):
+    """block output / gradient join / BatchNorm-backward apply over the bottleneck tensors (csrc/bn_ops.cu)."""
+    from b200dp import ops
+    torch.manual_seed(rows + C)
+    dev = "cuda"
+    bf = lambda *s: torch.randn(*s, device=dev).to(torch.bfloat16)
+    raw, res, g1, g2 = bf(rows, C), bf(rows, C), bf(rows, C), bf(rows, C)
+    coef2 = torch.randn(2, C, device=dev)
+    coef3 = torch.randn(3, C, device=dev)
+    # block_out, with and without residual
+    for r in (None, res):
+        colsum = torch.zeros(C, device=dev)
+        out = ops.block_out(raw, r, coef2, colsum)
+        ref = raw.float() * coef2[0] + coef2[1] + (r.float() if r is not None else 0)
+        assert torch.allclose(out.float(), ref, rtol=1e-2, atol=2e-2)
+        assert torch.allclose(colsum, out.float().sum(0), rtol=1e-3, atol=0.05)
+    # grad_join_stats, with and without the second branch
+    for b in (None, g2):
+        sums = torch.zeros(2, C, device=dev)
+        dout = ops.grad_join_stats(g1, b, raw, sums)
+        ref = g1.float() + (b.float() if b is not None else 0)
+        assert torch.allclose(dout.float(), ref, rtol=1e-2, atol=2e-2)
+        assert torch.allclose(sums[0], dout.float().sum(0), rtol=1e-3, atol=0.05)
+        assert torch.allclose(sums[1], (dout.float() * raw.float()).sum(0), rtol=1e-3, atol=0.1)
+    # affine: three-term form
+    out = ops.affine(g1, raw, coef3, True)
+    ref = coef3[0] * g1.float() + coef3[1] * raw.float() + coef3[2]
+    assert torch.allclose(out.float(), ref, rtol=1e-2, atol=3e-2)
