@@ -92,6 +92,14 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ PwGemmParams P) {
   using L = Layout<AMODE>;
   constexpr int NG = L::kEpiGroups;
+  auto stamp = [&](int slot) {
+    if (P.trace != nullptr && blockIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      P.trace[slot] = t;
+    }
+  };
+  if (threadIdx.x == 0) stamp(0);
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // ---- carve shared memory (tile buffers 1024-byte aligned for the 128-byte swizzle) ------------
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -107,8 +115,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int n_acoef = (AMODE == A_BNRELU ? 2 : (AMODE == A_BNGRAD ? 3 : 0)) * P.K;
   float* s_ecoef = s_acoef + n_acoef;
   const int n_ecoef = (EMODE == E_MASKSTATS ? 2 : 0) * P.N;
-  float* s_stats = s_ecoef + n_ecoef;                                          // [2][N] (absolute columns)
-  const int n_stats = (EMODE != E_PLAIN ? 2 : 0) * P.N;
+  float* s_stats = s_ecoef + n_ecoef;                                          // [8 epilogue warps][2][128]
+  const int n_stats = EMODE != E_PLAIN ? 4 * NG * 2 * 128 : 0;
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_stats + ((n_stats + 1) & ~1));
   uint64_t* full = bars;
   uint64_t* empty = bars + MAX_STAGES;
@@ -121,7 +129,11 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_tiles = P.m_tiles * P.n_tiles;
+  // A CTA keeps ONE block of output columns for its whole life (b % n_tiles) and walks the row tiles with stride
+  // gridDim / n_tiles: the per-column sums stay in registers until the end, and CTAs b, b+1, ... work on the same
+  // rows at the same time (the A tile is fetched from HBM once and hit in L2 by the others).
+  const int n0 = ((int)blockIdx.x % P.n_tiles) * P.block_n;
+  const int mt0 = (int)blockIdx.x / P.n_tiles, mt_step = (int)gridDim.x / P.n_tiles;
 
   // ---- one-time set-up ---------------------------------------------------------------------------
   if (warp == 0 && lane == 0) {
@@ -158,6 +170,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) stamp(1);
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
@@ -165,8 +178,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-        const int m0 = (t / P.n_tiles) * BM, n0 = (t % P.n_tiles) * P.block_n;
+      for (int mt = mt0; mt < P.m_tiles; mt += mt_step, ++it) {
+        const int m0 = mt * BM;
         if (EMODE == E_MASKSTATS) {     // raw forward activation tile for the ReLU6 mask, read by the epilogue
           const int ab = it & 1;
           mbar_wait(&aux_empty[ab], ((it >> 1) & 1) ^ 1);
@@ -192,6 +205,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_arrive_expect_tx(&full[s], (uint32_t)P.block_n * w * 2);
           }
           tma_load_2d(stage_b + (size_t)s * b_stage, last ? &tmBt : &tmB, &full[s], kc * KCH, n0);
+          if (it == 0 && kc == 0) stamp(2);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
@@ -203,7 +217,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      for (int mt = mt0; mt < P.m_tiles; mt += mt_step, ++it) {
         const int as = it & 1;
         mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -211,6 +225,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kc = 0; kc < P.kc; ++kc) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
+          if (it == 0 && kc == 0) stamp(3);
           const int w = kc == P.kc - 1 ? P.tail_w : KCH;
           const uint64_t da = umma_desc_kmajor(smem_u32(stage_a + (size_t)s * A_STAGE), w);
           const uint64_t db = umma_desc_kmajor(smem_u32(stage_b + (size_t)s * b_stage), w);
@@ -221,6 +236,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (++s == stages) { s = 0; ph ^= 1; }
         }
         umma_commit(&tmem_full[as]);  // accumulator complete
+        if (it == 0) stamp(4);
       }
     }
   } else if (warp >= 4 && warp < L::kProdWarp0) {
@@ -238,49 +254,51 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
       for (int j = 0; j < 8; ++j) s0[c][j] = s1[c][j] = 0.f;
     float esc[2][8], esh[2][8];
-    int prev_n = -1;
 
-    auto flush = [&](int n0) {     // registers -> shared [2][N] (absolute columns); global flush after the main loop
+    // my 32 rows' per-column sums -> my own slot of shared memory (plain stores: shared-memory atomics cost ~280
+    // cycles apiece here and made this a 4.6 us stall per column-block change, see scripts/trace_pw.py); the slots
+    // are added up and sent to global memory after the main loop
+    auto flush = [&]() {
       if (EMODE == E_PLAIN) return;
+      float* slot = s_stats + (size_t)(warp - 4) * 256;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float a[8], b[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          a[j] = s0[c][j]; b[j] = s1[c][j];
+          a[j] += __shfl_xor_sync(0xffffffffu, a[j], 8);
+          a[j] += __shfl_xor_sync(0xffffffffu, a[j], 16);
+          b[j] += __shfl_xor_sync(0xffffffffu, b[j], 8);
+          b[j] += __shfl_xor_sync(0xffffffffu, b[j], 16);
+        }
+        if (lane < 8) {
+          float4* d0 = reinterpret_cast<float4*>(slot + c * 64 + lane * 8);
+          float4* d1 = reinterpret_cast<float4*>(slot + 128 + c * 64 + lane * 8);
+          d0[0] = make_float4(a[0], a[1], a[2], a[3]); d0[1] = make_float4(a[4], a[5], a[6], a[7]);
+          d1[0] = make_float4(b[0], b[1], b[2], b[3]); d1[1] = make_float4(b[4], b[5], b[6], b[7]);
+        }
+      }
+    };
+    if (EMODE == E_MASKSTATS) {
 #pragma unroll
       for (int c = 0; c < 2; ++c)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          float a = s0[c][j], b = s1[c][j];
-          a += __shfl_xor_sync(0xffffffffu, a, 8);
-          a += __shfl_xor_sync(0xffffffffu, a, 16);
-          b += __shfl_xor_sync(0xffffffffu, b, 8);
-          b += __shfl_xor_sync(0xffffffffu, b, 16);
-          const int col = n0 + c * 64 + lane * 8 + j;
-          if (lane < 8 && (c * 64 + lane * 8) < P.block_n && col < P.N) {
-            atomicAdd(&s_stats[col], a);
-            atomicAdd(&s_stats[P.N + col], b);
-          }
-          s0[c][j] = s1[c][j] = 0.f;
+          const int col = n0 + c * 64 + p * 8 + j;
+          esc[c][j] = col < P.N ? s_ecoef[col] : 0.f;
+          esh[c][j] = col < P.N ? s_ecoef[P.N + col] : 0.f;
         }
-    };
+    }
 
-    for (int it = eg, t = blockIdx.x + eg * gridDim.x; t < total_tiles; it += NG, t += NG * gridDim.x) {
-      const int m0 = (t / P.n_tiles) * BM, n0 = (t % P.n_tiles) * P.block_n;
-      if (n0 != prev_n) {
-        if (prev_n >= 0) flush(prev_n);
-        prev_n = n0;
-        if (EMODE == E_MASKSTATS) {
-#pragma unroll
-          for (int c = 0; c < 2; ++c)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int col = n0 + c * 64 + p * 8 + j;
-              esc[c][j] = col < P.N ? s_ecoef[col] : 0.f;
-              esh[c][j] = col < P.N ? s_ecoef[P.N + col] : 0.f;
-            }
-        }
-      }
+    for (int it = eg, mt = mt0 + eg * mt_step; mt < P.m_tiles; it += NG, mt += NG * mt_step) {
+      const int m0 = mt * BM;
       const int as = it & 1;
       uint8_t* ob = out_buf + (size_t)as * nch * OUT_CHUNK;
       const uint32_t ob_u32 = smem_u32(ob);
       mbar_wait(&tmem_full[as], (it >> 1) & 1);
       tc_fence_after();
+      if (it == 0 && warp == 4 && lane == 0) stamp(5);
       // this warp's previous TMA store out of the same staging rows must have finished reading them
       if (lane == 0) {
         if (NG == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>();
@@ -357,18 +375,22 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int c = 0; c < nch; ++c)
           tma_store_2d(&tmO, ob + (size_t)c * OUT_CHUNK + row0 * 128, n0 + c * 64, m0 + row0);
         tma_store_commit();
+        if (it == 0 && warp == 4) stamp(6);
       }
     }
-    if (prev_n >= 0) flush(prev_n);
+    if (warp == 4 && lane == 0) stamp(10);
+    flush();
+    if (warp == 4 && lane == 0) stamp(11);
     if (lane == 0) tma_store_wait_all<0>();
+    if (warp == 4 && lane == 0) stamp(12);
   } else if (AMODE != A_TMA && warp >= L::kProdWarp0) {
     // =========================== transform warps: raw tile -> operand tile, in place ===========================
     const int pt = threadIdx.x - L::kProdWarp0 * 32;   // 0..127
     const int p = pt & 7, rb = pt >> 3;                // 16-byte piece p of rows rb + 16 i
     int s = 0;
     uint32_t ph = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int m0 = (t / P.n_tiles) * BM;
+    for (int mt = mt0; mt < P.m_tiles; mt += mt_step) {
+      const int m0 = mt * BM;
       for (int kc = 0; kc < P.kc; ++kc) {
         const int w = kc == P.kc - 1 ? P.tail_w : KCH;   // chunk width: row pitch 2w bytes, w/8 pieces per row
         const int wsh = w == 64 ? 0 : (w == 32 ? 1 : 2);
@@ -416,17 +438,26 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   // ---- teardown: per-channel sums shared -> global, TMEM release ------------------------------------
+  if (threadIdx.x == 0) stamp(7);
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) stamp(8);
   if (EMODE != E_PLAIN) {
-    for (int i = threadIdx.x; i < P.N; i += blockDim.x) {
-      atomicAdd(P.stats + i, s_stats[i]);
-      atomicAdd(P.stats + P.stats_stride + i, s_stats[P.N + i]);
+    for (int i = threadIdx.x; i < 2 * P.block_n; i += blockDim.x) {
+      const int h = i / P.block_n, col = i - h * P.block_n;
+      if (n0 + col < P.N) {
+        float a = 0.f;
+#pragma unroll
+        for (int wq = 0; wq < 4 * NG; ++wq) a += s_stats[wq * 256 + h * 128 + col];
+        atomicAdd(P.stats + (size_t)h * P.stats_stride + n0 + col, a);
+      }
     }
   }
   if (warp == 2) {
+    if (lane == 0) stamp(13);
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+    if (lane == 0) stamp(9);
   }
 }
 
@@ -503,7 +534,7 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   const int nch = (p.block_n + 63) / 64;
   const size_t fixed = (emode == E_MASKSTATS ? 4 : 2) * (size_t)nch * OUT_CHUNK +
                        ((amode == A_BNRELU ? 2 : amode == A_BNGRAD ? 3 : 0) * (size_t)K +
-                        (emode == E_MASKSTATS ? 4 : emode == E_STATS ? 2 : 0) * (size_t)N + 8) * 4 +
+                        (emode == E_MASKSTATS ? 2 : 0) * (size_t)N + (emode != E_PLAIN ? 2048 : 0) + 8) * 4 +
                        (3 * MAX_STAGES + 8) * 8 + 16 + 1024;
   const size_t per_stage = (amode == A_BNGRAD ? 2 : 1) * (size_t)A_STAGE + (size_t)p.block_n * 128;
   const size_t budget = 220 * 1024;
@@ -513,9 +544,11 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   p.stages = stages;
   pl->smem_bytes = fixed + stages * per_stage;
   pl->amode = amode; pl->emode = emode;
-  const int tiles = p.m_tiles * p.n_tiles;
   const int cap = max_ctas > 0 ? max_ctas : num_sms();
-  pl->grid = tiles < cap ? tiles : cap;
+  int groups = cap / p.n_tiles;                // CTAs per column block
+  if (groups < 1) groups = 1;
+  if (groups > p.m_tiles) groups = p.m_tiles;
+  pl->grid = groups * p.n_tiles;
   const int tail = K % KCH;
   B200DP_REQUIRE(tail == 0 || tail == 16 || tail == 32, "pw_gemm: K %% 64 must be 0, 16 or 32 (K=%d)", K);
   p.tail_w = tail == 0 ? KCH : tail;
@@ -542,7 +575,11 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   return B200DP_OK;
 }
 
-int pw_gemm_launch(const PwGemmPlan& pl, cudaStream_t s) {
+unsigned long long* g_pw_trace = nullptr;
+
+int pw_gemm_launch(const PwGemmPlan& pl_in, cudaStream_t s) {
+  PwGemmPlan pl = pl_in;
+  pl.p.trace = g_pw_trace;
   switch (pl.amode * 3 + pl.emode) {
     case 0: return launch_t<A_TMA, E_PLAIN>(pl, s);
     case 1: return launch_t<A_TMA, E_STATS>(pl, s);
@@ -571,3 +608,5 @@ extern "C" int b200dp_pw_gemm(int amode, int emode, int M, int N, int K, const v
     return rc;
   return pw_gemm_launch(pl, static_cast<cudaStream_t>(stream));
 }
+
+extern "C" void b200dp_debug_pw_trace(void* buf) { b200dp::g_pw_trace = static_cast<unsigned long long*>(buf); }

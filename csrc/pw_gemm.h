@@ -24,6 +24,7 @@ struct PwGemmParams {
   const float* ecoef;           // E_MASKSTATS: [2][N] scale, shift of that activation's BatchNorm
   float* stats;                 // E_STATS: sum y, sum y^2   E_MASKSTATS: sum dz, sum dz*aux   ([2] x stats_stride)
   int stats_stride;
+  unsigned long long* trace;    // debugging: CTA 0 writes %globaltimer at its pipeline milestones (null = off)
 };
 
 struct PwGemmPlan {

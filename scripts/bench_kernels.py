@@ -32,7 +32,7 @@ def timeit(fn):
 
 
 cases = {}
-B = 128
+B = int(os.environ.get("BENCH_B", "128"))
 
 
 def pw_fwd_expand(h, cin, cout):
@@ -119,6 +119,9 @@ cases = {
     "pw_wgrad_project_112_32_16": lambda: pw_wgrad_project(112, 32, 16),
     "pw_wgrad_project_56_144_32": lambda: pw_wgrad_project(56, 144, 32),
     "pw_wgrad_project_14_576_96": lambda: pw_wgrad_project(14, 576, 96),
+    "pw_fwd_expand_7_160_960": lambda: pw_fwd_expand(7, 160, 960),
+    "pw_fwd_project_7_960_160": lambda: pw_fwd_project(7, 960, 160),
+    "pw_fwd_expand_14_96_576": lambda: pw_fwd_expand(14, 96, 576),
     "dw_fwd_56_144_s1": lambda: dw_fwd(56, 144, 1),
     "dw_fwd_112_96_s2": lambda: dw_fwd(112, 96, 2),
     "dw_fwd_14_384_s1": lambda: dw_fwd(14, 384, 1),

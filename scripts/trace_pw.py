@@ -1,0 +1,34 @@
+"""Where does the fixed cost of a small pointwise-conv GEMM go?  CTA 0 stamps %globaltimer at its milestones."""
+import os, sys, ctypes
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from b200dp import ops
+from b200dp.ops import _lib
+
+lib = _lib.require()
+lib.b200dp_debug_pw_trace.argtypes = [ctypes.c_void_p]
+lib.b200dp_debug_pw_trace.restype = None
+dev = torch.device("cuda", 0)
+trace = torch.zeros(16, dtype=torch.int64, device=dev)
+names = ["entry", "setup done", "first TMA issued", "first tile landed (MMA sees full)", "MMAs of tile 0 committed",
+         "epilogue sees tmem_full", "epilogue tile 0 stored (TMA store issued)", "roles done (thread 0)",
+         "teardown barrier passed", "TMEM released", "epilogue warp: tile loop done", "epilogue warp: sums flushed to smem",
+         "epilogue warp: TMA stores complete", "warp 2: after stats atomics, before dealloc"]
+for (B, h, cin, cout) in [(2, 7, 160, 960), (128, 7, 160, 960), (128, 14, 96, 576), (128, 28, 32, 192)]:
+    M = B * h * h
+    a = torch.randn(M, cin, device=dev).to(torch.bfloat16)
+    w = torch.randn(cout, cin, device=dev).to(torch.bfloat16)
+    stats = torch.zeros(2, cout, device=dev)
+    out = torch.empty(M, cout, dtype=torch.bfloat16, device=dev)
+    for _ in range(3):
+        ops.pw_gemm(w, a=a, emode=ops.E_STATS, stats=stats, out=out)
+    torch.cuda.synchronize()
+    lib.b200dp_debug_pw_trace(trace.data_ptr())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); ops.pw_gemm(w, a=a, emode=ops.E_STATS, stats=stats, out=out); e1.record()
+    torch.cuda.synchronize()
+    lib.b200dp_debug_pw_trace(None)
+    t = trace.cpu().tolist()
+    print(f"--- M={M} K={cin} N={cout}: events {e0.elapsed_time(e1) * 1e3:.1f} us")
+    for i in sorted(range(len(names)), key=lambda i: t[i]):
+        print(f"  {names[i]:48s} +{(t[i] - t[0]) / 1e3:7.2f} us")
