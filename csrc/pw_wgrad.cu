@@ -53,6 +53,7 @@ struct WgradParams {
   const __nv_bfloat16* t1;     // hidden raw tensor 1 (MODE 0: y_raw)
   const __nv_bfloat16* qsrc;   // narrow tensor
   const float* asum;           // MODE 0: [narrow] column sums of the narrow tensor over all M rows
+  unsigned long long* trace;   // debugging: CTA 0 writes %globaltimer at its pipeline milestones (null = off)
 };
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
@@ -103,6 +104,14 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  auto stamp = [&](int slot) {
+    if (P.trace != nullptr && blockIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      P.trace[slot] = t;
+    }
+  };
+  if (threadIdx.x == 0) stamp(0);
   const int items = P.hchunks * P.qchunks * P.msplit;
   const int total_chunks = (P.M + MK - 1) / MK;
 
@@ -130,6 +139,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) stamp(1);
 
   // item -> hidden chunk (h0, hw <= 128), narrow chunk q0, m-chunk range.  Hidden chunk fastest: CTAs running side
   // by side read the same narrow rows, which stay in L2.
@@ -161,21 +171,26 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
         for (int c = c_lo; c < c_hi; ++c) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
+          if (it == 0 && c == c_lo) stamp(3);
           const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
           const uint32_t sq = st + h_bytes * (MODE == 0 ? 2 : 1);
           const uint64_t dh = umma_desc_mnmajor_sw128(st, (uint32_t)MK * 128);
           const uint64_t dh2 = umma_desc_mnmajor_sw128(st + h_bytes, (uint32_t)MK * 128);   // MODE 0: y_raw tile
           const uint64_t dq = umma_desc_mnmajor_sw128(sq, (uint32_t)MK * 128);
-          for (int k = 0; k < (MK >> 4); ++k) {                // 16 m-rows per MMA = 2048 B of 128-byte lines
-            const uint32_t acc = (c > c_lo) | (k > 0);
-            umma_bf16(d_tmem, dh + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, acc);
-            if (MODE == 0) umma_bf16(d_tmem + 128, dh2 + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, acc);
-          }
+          // 16 m-rows per MMA = 2048 B of 128-byte lines.  All MMAs of one accumulator back to back: alternating
+          // between two accumulators costs about twice as much per instruction (measured in dw_tc.cu).
+          for (int k = 0; k < (MK >> 4); ++k)
+            umma_bf16(d_tmem, dh + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, (c > c_lo) | (k > 0));
+          if (MODE == 0)
+            for (int k = 0; k < (MK >> 4); ++k)
+              umma_bf16(d_tmem + 128, dh2 + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, (c > c_lo) | (k > 0));
           umma_commit(&empty[s]);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
         umma_commit(&tmem_full[as]);
+        if (it == 0) stamp(4);
       }
+      stamp(8);
     }
   } else if (warp >= 4 && warp < 8) {
     // =========================== epilogue: TMEM -> red.global.add ===========================
@@ -187,6 +202,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
       const int as = it & 1;
       mbar_wait(&tmem_full[as], (it >> 1) & 1);
       tc_fence_after();
+      if (it == 0 && warp == 4 && lane == 0) stamp(5);
       const int hl = q * 32 + lane;                    // lane within the hidden chunk
       const bool ok = hl < hw && c_hi > c_lo;
       const int h = h0 + hl;
@@ -223,7 +239,9 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
+      if (it == 0 && warp == 4 && lane == 0) stamp(6);
     }
+    if (warp == 4 && lane == 0) stamp(7);
   } else if (warp >= 8 && warp < 12) {
     // =========================== transform warps ===========================
     // MODE 1: rewrite the raw hidden tile in place with relu6(scale*x + shift).  MODE 0: nothing to compute (the
@@ -332,10 +350,13 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+    if (lane == 0) stamp(9);
   }
 }
 
 }  // namespace
+
+extern unsigned long long* g_pw_trace;
 
 // mode 0: hidden side = G = ca*t0 + cb*t1 + cc with t0 = dz, t1 = y_raw [M][N];  narrow side = `pure` = A [M][K]
 // mode 1: hidden side = A = relu6(scale*t0 + shift) with t0 = d_raw [M][K];      narrow side = `pure` = G [M][N]
@@ -379,6 +400,7 @@ int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure
   p.t1 = static_cast<const __nv_bfloat16*>(t1);
   p.qsrc = static_cast<const __nv_bfloat16*>(pure);
   p.asum = asum;
+  p.trace = g_pw_trace;
   const int items = hq * p.msplit;
   const int grid = items < cap ? items : cap;
   if (mode == 0) {

@@ -32,3 +32,35 @@ for (B, h, cin, cout) in [(2, 7, 160, 960), (128, 7, 160, 960), (128, 14, 96, 57
     print(f"--- M={M} K={cin} N={cout}: events {e0.elapsed_time(e1) * 1e3:.1f} us")
     for i in sorted(range(len(names)), key=lambda i: t[i]):
         print(f"  {names[i]:48s} +{(t[i] - t[0]) / 1e3:7.2f} us")
+
+
+print("=== weight gradient (pw_wgrad) ===")
+wnames = ["entry", "setup done", "-", "first stage ready (MMA sees full)", "MMAs of item 0 committed",
+          "epilogue sees tmem_full", "epilogue item 0 done (red.adds issued)", "epilogue loop done", "MMA loop done",
+          "TMEM released"]
+for (B, h, cin, cout, mode) in [(128, 7, 160, 960, 0), (128, 14, 96, 576, 0), (128, 14, 576, 96, 1), (128, 28, 192, 32, 1),
+                                (128, 112, 32, 16, 1)]:
+    M = B * h * h
+    hidden, narrow = (cout, cin) if mode == 0 else (cin, cout)
+    bf = lambda *s: torch.randn(*s, device=dev).to(torch.bfloat16)
+    dw = torch.zeros(cout, cin, device=dev)
+    if mode == 0:
+        a, dz, y = bf(M, cin), bf(M, cout), bf(M, cout)
+        coef = torch.rand(3, cout, device=dev)
+        fn = lambda: ops.pw_wgrad(dw, a=a, dz=dz, y_raw=y, coef=coef)
+    else:
+        g, d = bf(M, cout), bf(M, cin)
+        coef = torch.rand(2, cin, device=dev)
+        fn = lambda: ops.pw_wgrad(dw, g=g, a_raw=d, coef=coef)
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    trace.zero_()
+    lib.b200dp_debug_pw_trace(trace.data_ptr())
+    fn()
+    torch.cuda.synchronize()
+    lib.b200dp_debug_pw_trace(None)
+    t = trace.cpu().tolist()
+    print(f"--- mode {mode} M={M} {cin}->{cout}")
+    for i in sorted([i for i in range(len(wnames)) if t[i]], key=lambda i: t[i]):
+        print(f"  {wnames[i]:48s} +{(t[i] - t[0]) / 1e3:7.2f} us")
