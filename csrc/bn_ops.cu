@@ -267,11 +267,13 @@ block_out_kernel(const __nv_bfloat16* __restrict__ raw, const __nv_bfloat16* __r
 }
 
 // Weight preparation: fp32 master [N][K] -> bf16 [N][K] and bf16 transposed [K][N] for every pointwise conv.
-struct WPrepEntry { long long off; int n, k; };
+// For row-packed layers (pw_gemm.h) also the block-diagonal copies blockdiag_r(W) [rN][rK] (forward) and
+// blockdiag_r(W^T) [rK][rN] (data gradient); their off-diagonal blocks are zero from allocation and never written.
+struct WPrepEntry { long long off; int n, k; int rf, rd; long long off_pf, off_pd; };
 
 __global__ void __launch_bounds__(256)
 weight_prep_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt,
-                   const WPrepEntry* __restrict__ table) {
+                   __nv_bfloat16* __restrict__ wpack, const WPrepEntry* __restrict__ table) {
   pdl_trigger();
   pdl_wait();
   const WPrepEntry e = table[blockIdx.y];
@@ -281,6 +283,10 @@ weight_prep_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__
     const __nv_bfloat16 v = __float2bfloat16(master[e.off + i]);
     if (w != nullptr) w[e.off + i] = v;
     wt[e.off + (long long)k * e.n + n] = v;
+    for (int p = 0; p < e.rf && e.rf > 1; ++p)
+      wpack[e.off_pf + (long long)(p * e.n + n) * (e.rf * e.k) + p * e.k + k] = v;
+    for (int p = 0; p < e.rd && e.rd > 1; ++p)
+      wpack[e.off_pd + (long long)(p * e.k + k) * (e.rd * e.n) + p * e.n + n] = v;
   }
 }
 
@@ -357,10 +363,12 @@ int grad_join_stats_launch(const void* g1, const void* g2, const void* x, void* 
   return B200DP_OK;
 }
 
-int weight_prep_launch(const float* master, void* w, void* wt, const void* table_dev, int nlayers, cudaStream_t s) {
+int weight_prep_launch(const float* master, void* w, void* wt, void* wpack, const void* table_dev, int nlayers,
+                       cudaStream_t s) {
   dim3 grid(32, nlayers);
   B200DP_CUDA(launch_k(weight_prep_kernel, grid, dim3(256), 0, s, master, static_cast<__nv_bfloat16*>(w),
-                       static_cast<__nv_bfloat16*>(wt), static_cast<const WPrepEntry*>(table_dev)));
+                       static_cast<__nv_bfloat16*>(wt), static_cast<__nv_bfloat16*>(wpack),
+                       static_cast<const WPrepEntry*>(table_dev)));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

@@ -34,6 +34,8 @@ struct Conv {
   int role;            // 0 stem, 1 expand, 2 dw, 3 project, 4 last
   int cin, cout, cinp, coutp, stride, hin, hout, block;
   long long off_w, off_g, off_b, off_rm, off_rv;    // element offsets: params arena (w, gamma, beta), buffer arena
+  int pack_f = 1, pack_d = 1;                        // row packing of the forward / data-gradient GEMM (pw_gemm.h)
+  long long off_pf = 0, off_pd = 0;                  // block-diagonal weight copies inside w_pack
   // workspace
   __nv_bfloat16* raw = nullptr;                      // raw conv output [B, hout, hout, coutp]
   float *sums_f = nullptr, *sums_b = nullptr, *coef_f = nullptr, *saved = nullptr, *coef_b = nullptr;
@@ -47,13 +49,14 @@ struct Block {
   float* xsum = nullptr;           // per-channel column sums of xout (for the consumer's factored weight gradient)
 };
 
-struct WPrepEntry { long long off; int n, k; };
+struct WPrepEntry { long long off; int n, k; int rf, rd; long long off_pf, off_pd; };
 
 struct Plans {            // per batch size
   int n = 0;
   std::vector<PwGemmPlan> fwd, fwd_eval, dgrad;    // indexed by conv
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_aug = -1;      // augmentation flag the train graph was captured with
+  unsigned long long train_kernels = 0, eval_kernels = 0;   // kernel nodes in each graph (for the launch counter)
 };
 
 }  // namespace
@@ -72,7 +75,8 @@ struct Engine {
   uint8_t* in_images = nullptr;
   int64_t* in_labels = nullptr;
   float* in_aug = nullptr;
-  __nv_bfloat16 *x0 = nullptr, *w_bf16 = nullptr, *wt_bf16 = nullptr;
+  __nv_bfloat16 *x0 = nullptr, *w_bf16 = nullptr, *wt_bf16 = nullptr, *w_pack = nullptr;
+  long long pack_total = 0;
   __nv_bfloat16 *dzd = nullptr, *dze = nullptr, *dp = nullptr, *gx[2] = {nullptr, nullptr}, *dout[2] = {nullptr, nullptr};
   float *sums_all = nullptr;
   size_t sums_bytes = 0;
@@ -155,6 +159,7 @@ size_t layout_workspace(Engine& e, char* base) {
   e.x0 = carve<__nv_bfloat16>(p, B * e.S * e.S * 4);
   e.w_bf16 = carve<__nv_bfloat16>(p, e.param_total);
   e.wt_bf16 = carve<__nv_bfloat16>(p, e.param_total);
+  e.w_pack = carve<__nv_bfloat16>(p, e.pack_total > 0 ? e.pack_total : 8);
   size_t max_d = 0, max_e = 0, max_x = 0;
   // statistics region first (one memset per step)
   char* sums0 = p;
@@ -217,6 +222,9 @@ int build_plans(Engine& e, Plans& pl, int n) {
   pl.fwd.assign(nc, PwGemmPlan{});
   pl.fwd_eval.assign(nc, PwGemmPlan{});
   pl.dgrad.assign(nc, PwGemmPlan{});
+  // forward / data-gradient weights of a conv: the plain bf16 copy, or its block-diagonal copy when the layer is packed
+  auto wf = [&](const Conv& c) { return c.pack_f > 1 ? e.w_pack + c.off_pf : e.w_bf16 + c.off_w; };
+  auto wd = [&](const Conv& c) { return c.pack_d > 1 ? e.w_pack + c.off_pd : e.wt_bf16 + c.off_w; };
   for (auto& b : e.blocks) {
     const Conv& cp = e.convs[b.cp];
     const Conv& cd = e.convs[b.cd];
@@ -227,19 +235,19 @@ int build_plans(Engine& e, Plans& pl, int n) {
       const Conv& ce = e.convs[b.ce];
       for (int ev = 0; ev < 2; ++ev)
         ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[b.ce] : &pl.fwd[b.ce], A_TMA, ev ? E_PLAIN : E_STATS, Min, ce.coutp,
-                             ce.cinp, xin, ce.cinp, nullptr, nullptr, nullptr, 0, e.w_bf16 + ce.off_w, ce.raw, ce.coutp,
-                             nullptr, nullptr, ce.sums_f, ce.coutp, 0));
+                             ce.cinp, xin, ce.cinp, nullptr, nullptr, nullptr, 0, wf(ce), ce.raw, ce.coutp,
+                             nullptr, nullptr, ce.sums_f, ce.coutp, 0, ce.pack_f));
       // dgrad: dx[M, cin] = BNgrad(dze, e_raw)[M, hidden] * W[hidden, cin]   (weights transposed: [cin][hidden])
       ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp, e.dze, ce.raw,
-                           ce.coef_b, 0, e.wt_bf16 + ce.off_w, e.gx[0], ce.cinp, nullptr, nullptr, nullptr, 0, 0));
+                           ce.coef_b, 0, wd(ce), e.gx[0], ce.cinp, nullptr, nullptr, nullptr, 0, 0, ce.pack_d));
     }
     for (int ev = 0; ev < 2; ++ev)
       ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[b.cp] : &pl.fwd[b.cp], A_BNRELU, ev ? E_PLAIN : E_STATS, Mout, cp.coutp,
-                           cp.cinp, nullptr, cp.cinp, cd.raw, nullptr, cd.coef_f, 1, e.w_bf16 + cp.off_w, cp.raw,
-                           cp.coutp, nullptr, nullptr, cp.sums_f, cp.coutp, 0));
+                           cp.cinp, nullptr, cp.cinp, cd.raw, nullptr, cd.coef_f, 1, wf(cp), cp.raw,
+                           cp.coutp, nullptr, nullptr, cp.sums_f, cp.coutp, 0, cp.pack_f));
     // project dgrad: dzd[M, hidden] = mask(dp[M, cout] * W[cout, hidden])   (weights transposed: [hidden][cout])
     ENG_TRY(pw_gemm_plan(&pl.dgrad[b.cp], A_TMA, E_MASKSTATS, Mout, cp.cinp, cp.coutp, e.dp, cp.coutp, nullptr, nullptr,
-                         nullptr, 0, e.wt_bf16 + cp.off_w, e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, 0));
+                         nullptr, 0, wd(cp), e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, 0, cp.pack_d));
   }
   {
     const int li = nc - 1;
@@ -272,7 +280,7 @@ int bn_fin_b(Engine& e, Conv& c, float count, cudaStream_t s) {
 }
 
 int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t s) {
-  ENG_TRY(weight_prep_launch(e.params, e.w_bf16, e.wt_bf16, e.wprep_dev, e.n_pw, s));
+  ENG_TRY(weight_prep_launch(e.params, e.w_bf16, e.wt_bf16, e.w_pack, e.wprep_dev, e.n_pw, s));
   mark(e, s, "weight_prep");
   if (train) {
     B200DP_CUDA(cudaMemsetAsync(e.sums_all, 0, e.sums_bytes, s));
@@ -465,6 +473,16 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
     e->dw_tiled = !(impl != nullptr && std::string(impl) == "simt");
   }
   build_spec(*e, offsets);
+  if (!(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0)) {
+    for (auto& c : e->convs) {
+      if (c.kind != 2) continue;
+      const int rows = c.hout * c.hout;      // per image; every packed layer has rows % 4 == 0, so any batch divides
+      c.pack_f = pw_gemm_pick_pack(rows, c.coutp, c.cinp);
+      c.pack_d = pw_gemm_pick_pack(rows, c.cinp, c.coutp);
+      if (c.pack_f > 1) { c.off_pf = e->pack_total; e->pack_total += (long long)c.pack_f * c.pack_f * c.coutp * c.cinp; }
+      if (c.pack_d > 1) { c.off_pd = e->pack_total; e->pack_total += (long long)c.pack_d * c.pack_d * c.coutp * c.cinp; }
+    }
+  }
   e->ws_bytes = layout_workspace(*e, nullptr) + 1024;
   cudaError_t err = cudaMalloc(&e->ws, e->ws_bytes);
   if (err != cudaSuccess) {
@@ -476,7 +494,7 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   layout_workspace(*e, e->ws);
   std::vector<WPrepEntry> table;
   for (auto& c : e->convs)
-    if (c.kind == 2) table.push_back(WPrepEntry{c.off_w, c.coutp, c.cinp});
+    if (c.kind == 2) table.push_back(WPrepEntry{c.off_w, c.coutp, c.cinp, c.pack_f, c.pack_d, c.off_pf, c.off_pd});
   e->n_pw = (int)table.size();
   B200DP_CUDA(cudaMemcpy(e->wprep_dev, table.data(), table.size() * sizeof(WPrepEntry), cudaMemcpyHostToDevice));
   B200DP_CUDA(cudaStreamCreateWithFlags(&e->cap_stream, cudaStreamNonBlocking));
@@ -555,10 +573,13 @@ int b200dp_engine_train_step(void* h, const uint8_t* images, const int64_t* labe
     if (g) { cudaGraphExecDestroy(g); g = nullptr; }
     cudaGraph_t graph;
     cudaStream_t cs = e->cap_stream;
+    const unsigned long long before = g_launches.load();
     B200DP_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
     int rc = forward(*e, *pl, n, true, has_aug, cs);
     if (rc == B200DP_OK) rc = backward(*e, *pl, n, cs);
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+    pl->train_kernels = g_launches.load() - before;     // counted while capturing, executed on every replay
+    g_launches.store(before);
     if (rc != B200DP_OK) { if (ce == cudaSuccess) cudaGraphDestroy(graph); return rc; }
     B200DP_CUDA(ce);
     B200DP_CUDA(cudaGraphInstantiate(&g, graph, 0));
@@ -566,7 +587,7 @@ int b200dp_engine_train_step(void* h, const uint8_t* images, const int64_t* labe
     pl->train_aug = (int)has_aug;
   }
   B200DP_CUDA(cudaGraphLaunch(g, s));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
+  g_launches.fetch_add(pl->train_kernels, std::memory_order_relaxed);
   return B200DP_OK;
 }
 
@@ -587,16 +608,19 @@ int b200dp_engine_eval_step(void* h, const uint8_t* images, const int64_t* label
   if (g == nullptr) {
     cudaGraph_t graph;
     cudaStream_t cs = e->cap_stream;
+    const unsigned long long before = g_launches.load();
     B200DP_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
     int rc = forward(*e, *pl, n, false, false, cs);
     cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+    pl->eval_kernels = g_launches.load() - before;
+    g_launches.store(before);
     if (rc != B200DP_OK) { if (ce == cudaSuccess) cudaGraphDestroy(graph); return rc; }
     B200DP_CUDA(ce);
     B200DP_CUDA(cudaGraphInstantiate(&g, graph, 0));
     cudaGraphDestroy(graph);
   }
   B200DP_CUDA(cudaGraphLaunch(g, s));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
+  g_launches.fetch_add(pl->eval_kernels, std::memory_order_relaxed);
   return B200DP_OK;
 }
 

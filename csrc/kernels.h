@@ -47,7 +47,8 @@ int block_out_launch(const void* raw, const void* res, const float* coef, void* 
                      int C, cudaStream_t s);
 int grad_join_stats_launch(const void* g1, const void* g2, const void* x, void* dout, float* sums, int stride,
                            long long rows, int C, cudaStream_t s);
-int weight_prep_launch(const float* master, void* w, void* wt, const void* table_dev, int nlayers, cudaStream_t s);
+int weight_prep_launch(const float* master, void* w, void* wt, void* wpack, const void* table_dev, int nlayers,
+                       cudaStream_t s);
 // head.cu
 int head_pool_launch(const void* raw, const float* coef, float* pooled, float* drop, int B, int HW, int C,
                      float p_drop, uint32_t seed, const int* step, cudaStream_t s);

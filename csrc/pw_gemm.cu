@@ -163,8 +163,15 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // everything above is on-chip set-up and overlaps the previous kernel's tail (PDL); global data from here on
   pdl_trigger();
   pdl_wait();
-  for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) s_acoef[i] = P.acoef[i];
-  for (int i = threadIdx.x; i < n_ecoef; i += blockDim.x) s_ecoef[i] = P.ecoef[i];
+  // coefficient arrays have the unpacked lengths; packed column c belongs to channel c % true width
+  for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) {
+    const int j = i / P.K, c = i - j * P.K;
+    s_acoef[i] = P.acoef[j * P.k_true + c % P.k_true];
+  }
+  for (int i = threadIdx.x; i < n_ecoef; i += blockDim.x) {
+    const int j = i / P.N, c = i - j * P.N;
+    s_ecoef[i] = P.ecoef[j * P.n_true + c % P.n_true];
+  }
   for (int i = threadIdx.x; i < n_stats; i += blockDim.x) s_stats[i] = 0.f;
   tc_fence_before();
   __syncthreads();
@@ -449,7 +456,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float a = 0.f;
 #pragma unroll
         for (int wq = 0; wq < 4 * NG; ++wq) a += s_stats[wq * 256 + h * 128 + col];
-        atomicAdd(P.stats + (size_t)h * P.stats_stride + n0 + col, a);
+        atomicAdd(P.stats + (size_t)h * P.stats_stride + (n0 + col) % P.n_true, a);
       }
     }
   }
@@ -508,15 +515,35 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   return B200DP_OK;
 }
 
+// Row packing pays when a side of the GEMM is narrower than a 128-byte row: r = 64 / min(K, N), at most 4, as long
+// as the packed K still splits into 64-wide chunks plus a 16/32 tail and the rows divide evenly.
+int pw_gemm_pick_pack(int M, int N, int K) {
+  const int narrow = K < N ? K : N;
+  for (int r = 4; r > 1; r >>= 1) {
+    if (narrow * r > 64 || M % r != 0) continue;
+    const int tail = (K * r) % KCH;
+    if (tail != 0 && tail != 16 && tail != 32) continue;
+    return r;
+  }
+  return 1;
+}
+
 int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, const void* a_tma, int lda,
                  const void* a0, const void* a1, const float* acoef, int a_relu6, const void* w, void* out, int ldo,
-                 const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas) {
+                 const void* aux, const float* ecoef, float* stats, int stats_stride, int max_ctas, int pack) {
   B200DP_REQUIRE(M > 0 && N > 0 && K > 0 && (N % 16) == 0 && (K % 16) == 0, "pw_gemm: M=%d N=%d K=%d invalid", M, N, K);
+  B200DP_REQUIRE(pack >= 1 && pack <= 8 && M % pack == 0, "pw_gemm: pack=%d does not divide M=%d", pack, M);
+  const int n_true = N, k_true = K;
+  if (pack > 1) {
+    B200DP_REQUIRE(lda == K && ldo == N, "pw_gemm: row packing needs dense tensors (lda=%d K=%d ldo=%d N=%d)", lda, K, ldo, N);
+    M /= pack; N *= pack; K *= pack; lda *= pack; ldo *= pack;
+  }
   B200DP_REQUIRE((lda % 8) == 0 && (ldo % 8) == 0, "pw_gemm: row pitches must be multiples of 8 elements");
   B200DP_REQUIRE(amode >= 0 && amode <= 2 && emode >= 0 && emode <= 2, "pw_gemm: bad mode");
   PwGemmParams& p = pl->p;
   p = PwGemmParams{};
   p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldo = ldo;
+  p.n_true = n_true; p.k_true = k_true;
   p.block_n = N < 128 ? N : 128;
   p.n_tiles = (N + p.block_n - 1) / p.block_n;
   p.m_tiles = (M + BM - 1) / BM;
@@ -608,5 +635,18 @@ extern "C" int b200dp_pw_gemm(int amode, int emode, int M, int N, int K, const v
     return rc;
   return pw_gemm_launch(pl, static_cast<cudaStream_t>(stream));
 }
+
+// Same with row packing: `w` is blockdiag_pack(W), [pack*N][pack*K]; everything else as above (true sizes).
+extern "C" int b200dp_pw_gemm_packed(int amode, int emode, int M, int N, int K, const void* a_tma, const void* a0,
+                                     const void* a1, const float* acoef, int a_relu6, const void* w_blockdiag,
+                                     void* out, const void* aux, const float* ecoef, float* stats, int stats_stride,
+                                     int max_ctas, int pack, void* stream) {
+  PwGemmPlan pl;
+  if (int rc = pw_gemm_plan(&pl, amode, emode, M, N, K, a_tma, K, a0, a1, acoef, a_relu6, w_blockdiag, out, N, aux,
+                            ecoef, stats, stats_stride, max_ctas, pack))
+    return rc;
+  return pw_gemm_launch(pl, static_cast<cudaStream_t>(stream));
+}
+extern "C" int b200dp_pw_gemm_pick_pack(int M, int N, int K) { return pw_gemm_pick_pack(M, N, K); }
 
 extern "C" void b200dp_debug_pw_trace(void* buf) { b200dp::g_pw_trace = static_cast<unsigned long long*>(buf); }

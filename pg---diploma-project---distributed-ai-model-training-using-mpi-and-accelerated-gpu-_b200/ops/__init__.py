@@ -98,8 +98,8 @@ E_PLAIN, E_STATS, E_MASKSTATS = 0, 1, 2
 def pw_gemm(w: torch.Tensor, *, a: Optional[torch.Tensor] = None, a_raw: Optional[torch.Tensor] = None,
             a_dz: Optional[torch.Tensor] = None, acoef: Optional[torch.Tensor] = None, relu6: bool = True,
             emode: int = E_PLAIN, aux: Optional[torch.Tensor] = None, ecoef: Optional[torch.Tensor] = None,
-            stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, max_ctas: int = 0
-            ) -> torch.Tensor:
+            stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, max_ctas: int = 0,
+            pack: int = 1) -> torch.Tensor:
     """Pointwise-conv GEMM ``out[M,N] = Aeff[M,K] @ w[N,K]^T`` on tcgen05 (csrc/pw_gemm.cu).
 
     A operand: ``a`` (bf16 [M,K], TMA path), or ``a_raw`` + ``acoef`` [2,K] (BatchNorm scale/shift
@@ -136,6 +136,12 @@ def pw_gemm(w: torch.Tensor, *, a: Optional[torch.Tensor] = None, a_raw: Optiona
         _chk(ecoef, torch.float32, "ecoef")
     a0 = a_dz if amode == A_BNGRAD else a_raw
     a1 = a_raw if amode == A_BNGRAD else None
+    if pack > 1:     # r consecutive rows as one row of r*K channels against blockdiag_r(w) (narrow layers)
+        wbd = torch.block_diag(*([w.float()] * pack)).to(torch.bfloat16).contiguous()
+        check(lib.b200dp_pw_gemm_packed(amode, emode, M, N, K, ptr(a), ptr(a0), ptr(a1), ptr(acoef), 1 if relu6 else 0,
+                                        ptr(wbd), ptr(out), ptr(aux), ptr(ecoef), ptr(stats), N, max_ctas, pack,
+                                        current_stream()))
+        return out
     check(lib.b200dp_pw_gemm(amode, emode, M, N, K, ptr(a), K, ptr(a0), ptr(a1), ptr(acoef), 1 if relu6 else 0,
                              ptr(w), ptr(out), N, ptr(aux), ptr(ecoef), ptr(stats), N, max_ctas,
                              current_stream()))

@@ -98,3 +98,59 @@ def test_small_grid_many_tiles_per_cta(ops):
     ref = a.float() @ w.float().t()
     assert (out.float() - ref).abs().max().item() <= 0.02 * ref.abs().max().item() + 1e-2
     assert torch.allclose(stats[0], out.float().sum(0), rtol=2e-3, atol=0.5)
+
+
+# ---- row packing: r consecutive pixels as one row against blockdiag_r(W) (narrow layers) ----------------------------
+@pytest.mark.parametrize("M,K,N,pack", [(128 * 6, 16, 96, 4), (1000, 32, 16, 4), (1284, 32, 144, 2), (2048, 16, 32, 4),
+                                        (128 * 100, 16, 96, 4), (770, 32, 192, 2)])
+def test_packed_fwd_tma_stats(ops, M, K, N, pack):
+    torch.manual_seed(M + K + N)
+    a, w = _rand((M, K)), _rand((N, K), 0.2)
+    stats = torch.zeros(2, N, device="cuda")
+    out = ops.pw_gemm(w, a=a, emode=ops.E_STATS, stats=stats, pack=pack)
+    ref = a.float() @ w.float().t()
+    assert (out.float() - ref).abs().max().item() <= 0.02 * ref.abs().max().item() + 1e-2
+    o = out.float()
+    assert torch.allclose(stats[0], o.sum(0), rtol=2e-3, atol=2e-2 * (M ** 0.5))
+    assert torch.allclose(stats[1], (o * o).sum(0), rtol=2e-3, atol=1e-2 * M ** 0.5)
+
+
+@pytest.mark.parametrize("M,K,N,pack", [(1000, 32, 16, 4), (640, 96, 32, 2), (1284, 144, 32, 2), (2048, 192, 32, 2)])
+def test_packed_fwd_bnrelu_stats(ops, M, K, N, pack):
+    torch.manual_seed(5)
+    raw, w = _rand((M, K), 2.0), _rand((N, K), 0.2)
+    coef = torch.stack([torch.rand(K, device="cuda") + 0.5, torch.randn(K, device="cuda")]).contiguous()
+    stats = torch.zeros(2, N, device="cuda")
+    out = ops.pw_gemm(w, a_raw=raw, acoef=coef, relu6=True, emode=ops.E_STATS, stats=stats, pack=pack)
+    act = (raw.float() * coef[0] + coef[1]).clamp(0, 6)
+    ref = act.to(torch.bfloat16).float() @ w.float().t()
+    assert (out.float() - ref).abs().max().item() <= 0.02 * ref.abs().max().item() + 1e-2
+    assert torch.allclose(stats[0], out.float().sum(0), rtol=2e-3, atol=0.5)
+
+
+@pytest.mark.parametrize("M,K,N,pack", [(640, 96, 16, 4), (1000, 144, 32, 2), (2048, 192, 32, 2)])
+def test_packed_dgrad_bngrad(ops, M, K, N, pack):
+    torch.manual_seed(6)
+    dz, x, w = _rand((M, K)), _rand((M, K), 2.0), _rand((N, K), 0.2)
+    coef = torch.randn(3, K, device="cuda").contiguous()
+    out = ops.pw_gemm(w, a_dz=dz, a_raw=x, acoef=coef, pack=pack)
+    a = (coef[0] * dz.float() + coef[1] * x.float() + coef[2]).to(torch.bfloat16).float()
+    ref = a @ w.float().t()
+    assert (out.float() - ref).abs().max().item() <= 0.02 * ref.abs().max().item() + 1e-2
+
+
+@pytest.mark.parametrize("M,K,N,pack", [(640, 16, 32, 4), (1000, 32, 144, 2), (128 * 40 + 6, 32, 192, 2), (2048, 16, 96, 4)])
+def test_packed_dgrad_maskstats(ops, M, K, N, pack):
+    torch.manual_seed(7)
+    g, w = _rand((M, K)), _rand((N, K), 0.2)
+    aux = _rand((M, N), 2.0)
+    ecoef = torch.stack([torch.rand(N, device="cuda") + 0.5, torch.randn(N, device="cuda")]).contiguous()
+    stats = torch.zeros(2, N, device="cuda")
+    out = ops.pw_gemm(w, a=g, emode=ops.E_MASKSTATS, aux=aux, ecoef=ecoef, stats=stats, pack=pack)
+    z = aux.float() * ecoef[0] + ecoef[1]
+    mask = ((z > 0) & (z < 6)).float()
+    ref = (g.float() @ w.float().t()) * mask
+    assert (out.float() - ref).abs().max().item() <= 0.02 * ref.abs().max().item() + 1e-2
+    o = out.float()
+    assert torch.allclose(stats[0], o.sum(0), rtol=2e-3, atol=0.5)
+    assert torch.allclose(stats[1], (o * aux.float()).sum(0), rtol=2e-3, atol=1.0)
