@@ -86,6 +86,7 @@ struct Engine {
   WPrepEntry* wprep_dev = nullptr;
   int n_pw = 0;
   bool use_graphs = true;
+  bool pw_pack = true;      // row packing of narrow pointwise layers (B200DP_PW_PACK=0: off)
   bool dw_tiled = true;     // stride-1 depthwise convs on the TMA-tiled kernels (B200DP_DW_IMPL=simt: sliding-window kernels)
   cudaStream_t cap_stream = nullptr;   // graphs are captured here (the caller's stream may be the legacy default stream)
   bool eval_coef_valid = false;
@@ -385,7 +386,8 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     mark(e, s, "bn_bwd_apply", b.cp);
     // ---- projection conv: weight gradient, then data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
     ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, e.dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
-                            nullptr, e.grads + cp.off_w, cp.cinp, 0, s));
+                            nullptr, e.grads + cp.off_w, cp.cinp, 0, s,
+                            e.pw_pack ? pw_wgrad_pick_pack(1, (int)rows_out, cp.coutp, cp.cinp) : 1));
     mark(e, s, "pw_wgrad_project", b.cp);
     ENG_TRY(pw_gemm_launch(pl.dgrad[b.cp], s));
     mark(e, s, "pw_dgrad_project", b.cp);
@@ -407,7 +409,8 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       Conv& ce = e.convs[b.ce];
       const __nv_bfloat16* xin = e.blocks[bi - 1].xout;
       ENG_TRY(pw_wgrad_launch(0, (int)rows_in, ce.coutp, ce.cinp, xin, ce.cinp, e.dze, ce.raw, ce.coutp, ce.coef_b,
-                              e.blocks[bi - 1].xsum, e.grads + ce.off_w, ce.cinp, 0, s));
+                              e.blocks[bi - 1].xsum, e.grads + ce.off_w, ce.cinp, 0, s,
+                              e.pw_pack ? pw_wgrad_pick_pack(0, (int)rows_in, ce.coutp, ce.cinp) : 1));
       mark(e, s, "pw_wgrad_expand", b.ce);
       gxi ^= 1;
       ENG_TRY(retarget_out(pl.dgrad[b.ce], e.gx[gxi]));
@@ -473,7 +476,8 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
     e->dw_tiled = !(impl != nullptr && std::string(impl) == "simt");
   }
   build_spec(*e, offsets);
-  if (!(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0)) {
+  e->pw_pack = !(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0);
+  if (e->pw_pack) {
     for (auto& c : e->convs) {
       if (c.kind != 2) continue;
       const int rows = c.hout * c.hout;      // per image; every packed layer has rows % 4 == 0, so any batch divides

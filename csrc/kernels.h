@@ -32,7 +32,9 @@ int stem_wgrad_launch(const void* x, const void* dz, const void* yraw, const flo
                       int W, cudaStream_t s);
 // pw_wgrad.cu
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
-                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s);
+                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s,
+                    int pack = 1);
+int pw_wgrad_pick_pack(int mode, int M, int N, int K);
 // bn_ops.cu
 int bn_fwd_finalize_launch(const float* sums, int stride, const float* gamma, const float* beta, float count,
                            float eps, float momentum, float* rmean, float* rvar, float* coef, float* saved, int C,

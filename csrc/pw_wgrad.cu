@@ -42,7 +42,9 @@ constexpr int TMEM_COLS = 512;         // 2 accumulator stages x 256 columns
 
 struct WgradParams {
   int M;                       // rows
-  int hidden, narrow;          // channel counts of the wide / narrow side
+  int hidden, narrow;          // channel counts of the wide / narrow side (after row packing)
+  int hidden_true, narrow_true, pack;   // before packing: r consecutive rows are one row of r*C channels, only the
+                               // r diagonal (hidden slot == narrow slot) blocks of the product are weight gradient
   int ldh, ldq, ldw;           // row pitches (elements): hidden tensors, narrow tensor, dW
   int mk;                      // m rows per pipeline stage (64 / 128 / 256)
   int nq, qblks, qchunks;      // narrow chunk width (multiple of 16), its 64-wide blocks, number of chunks
@@ -133,7 +135,10 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   // on-chip set-up above overlaps the previous kernel's tail (PDL); global data from here on
   pdl_trigger();
   pdl_wait();
-  for (int i = threadIdx.x; i < ncoef; i += blockDim.x) s_coef[i] = P.coef[i];
+  for (int i = threadIdx.x; i < ncoef; i += blockDim.x) {
+    const int j = i / P.hidden, c = i - j * P.hidden;
+    s_coef[i] = P.coef[j * P.hidden_true + c % P.hidden_true];
+  }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -206,6 +211,8 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
       const int hl = q * 32 + lane;                    // lane within the hidden chunk
       const bool ok = hl < hw && c_hi > c_lo;
       const int h = h0 + hl;
+      const int hslot = h / P.hidden_true, ht = h - hslot * P.hidden_true;   // pixel slot / true channel of my lane
+      const float inv_pack = 1.f / (float)P.pack;
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * 256;
       float ka = 0.f, kb = 0.f, kc = 0.f;
       if (MODE == 0 && ok) {
@@ -221,19 +228,21 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
           tmem_ld_x16(taddr + 128 + c16 * 16, r2);
           tmem_ld_wait();
         }
-        if (ok) {
-          const int qq = q0 + c16 * 16;
+        const int qq = q0 + c16 * 16;
+        const int qslot = qq / P.narrow_true, qt = qq - qslot * P.narrow_true;   // 16 columns never straddle a slot
+        if (ok && qslot == hslot) {
           if (MODE == 0) {           // dW[n = hidden][k = narrow]: this lane's row, 16 consecutive k
-            float* dst = P.dw + (size_t)h * P.ldw + qq;
+            float* dst = P.dw + (size_t)ht * P.ldw + qt;
             float v[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              v[j] = fmaf(ka, __uint_as_float(r[j]), fmaf(kb, __uint_as_float(r2[j]), kc * __ldg(P.asum + qq + j)));
+            for (int j = 0; j < 16; ++j)     // each of the `pack` diagonal blocks adds its share of cc * sum_m A
+              v[j] = fmaf(ka, __uint_as_float(r[j]),
+                          fmaf(kb, __uint_as_float(r2[j]), kc * inv_pack * __ldg(P.asum + qt + j)));
 #pragma unroll
             for (int j = 0; j < 16; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
           } else {                   // dW[n = narrow][k = hidden]: consecutive lanes -> consecutive k
 #pragma unroll
-            for (int j = 0; j < 16; ++j) atomicAdd(P.dw + (size_t)(qq + j) * P.ldw + h, __uint_as_float(r[j]));
+            for (int j = 0; j < 16; ++j) atomicAdd(P.dw + (size_t)(qt + j) * P.ldw + ht, __uint_as_float(r[j]));
           }
         }
       }
@@ -360,15 +369,34 @@ extern unsigned long long* g_pw_trace;
 
 // mode 0: hidden side = G = ca*t0 + cb*t1 + cc with t0 = dz, t1 = y_raw [M][N];  narrow side = `pure` = A [M][K]
 // mode 1: hidden side = A = relu6(scale*t0 + shift) with t0 = d_raw [M][K];      narrow side = `pure` = G [M][N]
+// Row packing for layers whose WIDE side is narrow too (hidden <= 64): r = 128 / hidden consecutive pixels, at most 4.
+// One MMA then reduces over 16 r pixels instead of 16 -- these layers are bound by the per-instruction cost of
+// tcgen05.mma (~120 ns each whatever the shape, scripts/trace_pw.py), not by bandwidth.
+int pw_wgrad_pick_pack(int mode, int M, int N, int K) {
+  const int hidden = mode == 0 ? N : K, narrow = mode == 0 ? K : N;
+  for (int r = 4; r > 1; r >>= 1)
+    if (hidden * r <= 128 && narrow * r <= 128 && M % r == 0) return r;
+  return 1;
+}
+
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
-                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s) {
+                    int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s,
+                    int pack) {
   B200DP_REQUIRE(mode == 0 || mode == 1, "pw_wgrad: bad mode");
   B200DP_REQUIRE(M > 0 && N % 16 == 0 && K % 16 == 0, "pw_wgrad: M=%d N=%d K=%d invalid", M, N, K);
   B200DP_REQUIRE(pure && t0 && coef && dw && (mode == 1 || (t1 && asum)), "pw_wgrad: missing pointers");
+  B200DP_REQUIRE(pack >= 1 && M % pack == 0, "pw_wgrad: pack=%d does not divide M=%d", pack, M);
   WgradParams p{};
+  p.hidden_true = mode == 0 ? N : K;
+  p.narrow_true = mode == 0 ? K : N;
+  p.pack = pack;
+  if (pack > 1) {
+    B200DP_REQUIRE(ld_t == p.hidden_true && ld_pure == p.narrow_true, "pw_wgrad: row packing needs dense tensors");
+    M /= pack; ld_t *= pack; ld_pure *= pack;
+  }
   p.M = M;
-  p.hidden = mode == 0 ? N : K;
-  p.narrow = mode == 0 ? K : N;
+  p.hidden = p.hidden_true * pack;
+  p.narrow = p.narrow_true * pack;
   p.ldh = ld_t; p.ldq = ld_pure; p.ldw = ldw;
   p.coef = coef; p.dw = dw;
   p.hchunks = (p.hidden + 127) / 128;
@@ -422,5 +450,13 @@ extern "C" int b200dp_pw_wgrad(int mode, int M, int N, int K, const void* pure, 
                                const void* t1, int ld_t, const float* coef, const float* asum, float* dw, int ldw,
                                int max_ctas, void* stream) {
   return pw_wgrad_launch(mode, M, N, K, pure, ld_pure, t0, t1, ld_t, coef, asum, dw, ldw, max_ctas,
-                         static_cast<cudaStream_t>(stream));
+                         static_cast<cudaStream_t>(stream), 1);
+}
+// Same with row packing (see pw_wgrad_pick_pack); pack = 0 lets the library choose.
+extern "C" int b200dp_pw_wgrad_packed(int mode, int M, int N, int K, const void* pure, const void* t0, const void* t1,
+                                      const float* coef, const float* asum, float* dw, int max_ctas, int pack,
+                                      void* stream) {
+  if (pack <= 0) pack = pw_wgrad_pick_pack(mode, M, N, K);
+  return pw_wgrad_launch(mode, M, N, K, pure, mode == 0 ? K : N, t0, t1, mode == 0 ? N : K, coef, asum, dw, K, max_ctas,
+                         static_cast<cudaStream_t>(stream), pack);
 }

@@ -149,6 +149,15 @@ int b200dp_pw_gemm(int amode, int emode, int M, int N, int K, const void* a_tma,
  * affine map is factored out of the reduction).  mode 1: `pure` = G [M,N]; A = relu6(coef[0]*t0 + coef[1]); asum unused. */
 int b200dp_pw_wgrad(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
                     int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, void* stream);
+/* Same over dense tensors with row packing: `pack` consecutive pixels are one row of pack*C channels, only the diagonal
+ * blocks of the product are accumulated (pack = 0: chosen by the library; pays when the wide side has <= 64 channels). */
+int b200dp_pw_wgrad_packed(int mode, int M, int N, int K, const void* pure, const void* t0, const void* t1,
+                           const float* coef, const float* asum, float* dw, int max_ctas, int pack, void* stream);
+/* Pointwise GEMM with row packing: `w_blockdiag` = blockdiag_pack(W) [pack*N][pack*K]; dense tensors, true sizes. */
+int b200dp_pw_gemm_packed(int amode, int emode, int M, int N, int K, const void* a_tma, const void* a0, const void* a1,
+                          const float* acoef, int a_relu6, const void* w_blockdiag, void* out, const void* aux,
+                          const float* ecoef, float* stats, int stats_stride, int max_ctas, int pack, void* stream);
+int b200dp_pw_gemm_pick_pack(int M, int N, int K);
 /* Depthwise 3x3 (pad 1, stride 1|2): y = dwconv(relu6(scale*x + shift)), w fp32 [9][C];
  * stats (may be NULL) [2][stats_stride] += sum(y), sum(y^2): a scratch accumulator that must be zero on entry. */
 int b200dp_dw_fwd(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,

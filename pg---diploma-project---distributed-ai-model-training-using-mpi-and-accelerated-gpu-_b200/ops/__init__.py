@@ -150,7 +150,8 @@ def pw_gemm(w: torch.Tensor, *, a: Optional[torch.Tensor] = None, a_raw: Optiona
 
 def pw_wgrad(dw: torch.Tensor, *, a: Optional[torch.Tensor] = None, dz: Optional[torch.Tensor] = None,
              y_raw: Optional[torch.Tensor] = None, g: Optional[torch.Tensor] = None,
-             a_raw: Optional[torch.Tensor] = None, coef: torch.Tensor = None, max_ctas: int = 0) -> torch.Tensor:
+             a_raw: Optional[torch.Tensor] = None, coef: torch.Tensor = None, max_ctas: int = 0,
+             pack: int = 1) -> torch.Tensor:
     """``dw[N,K] += G^T @ A`` on tcgen05 with MN-major operands (csrc/pw_wgrad.cu).
     mode 0: ``a`` pure [M,K], G = coef[0]*dz + coef[1]*y_raw + coef[2] ([M,N]);
     mode 1: ``g`` pure [M,N], A = relu6(coef[0]*a_raw + coef[1]) ([M,K])."""
@@ -165,6 +166,10 @@ def pw_wgrad(dw: torch.Tensor, *, a: Optional[torch.Tensor] = None, dz: Optional
     M = pure.shape[0]
     _chk(coef, torch.float32, "coef")
     asum = a.float().sum(0).contiguous() if mode == 0 else None     # the BN-backward affine is factored out of the reduction
+    if pack != 1:    # row packing (0 = let the library choose)
+        check(lib.b200dp_pw_wgrad_packed(mode, M, N, K, ptr(pure), ptr(t0), ptr(t1), ptr(coef), ptr(asum), ptr(dw),
+                                         max_ctas, pack, current_stream()))
+        return dw
     check(lib.b200dp_pw_wgrad(mode, M, N, K, ptr(pure), ldp, ptr(t0), ptr(t1), ldt, ptr(coef), ptr(asum), ptr(dw), K,
                               max_ctas, current_stream()))
     return dw

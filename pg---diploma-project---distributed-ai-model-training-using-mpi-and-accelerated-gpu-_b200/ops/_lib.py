@@ -62,6 +62,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_pw_gemm": [i, i, i, i, i, vp, i, vp, vp, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
         "b200dp_pw_gemm_packed": [i, i, i, i, i, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, i, i, i, vp],
         "b200dp_pw_gemm_pick_pack": [i, i, i],
+        "b200dp_pw_wgrad_packed": [i, i, i, i, vp, vp, vp, vp, vp, vp, i, i, vp],
         "b200dp_pw_wgrad": [i, i, i, i, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
         "b200dp_dw_fwd": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "b200dp_dw_fwd_tc": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],

@@ -129,3 +129,31 @@ def test_pw_wgrad_mode1(ops, M, N, K):
     a = _bf((draw.float() * coef[0] + coef[1]).clamp(0, 6)).float()
     ref = g.float().t() @ a
     assert _relerr(dw, ref) < 5e-3, _relerr(dw, ref)
+
+
+@pytest.mark.parametrize("M,N,K,pack", [(128 * 64, 16, 32, 4), (4000, 16, 32, 2), (1024, 32, 64, 2), (128 * 98, 16, 32, 0)])
+def test_pw_wgrad_mode1_packed(ops, M, N, K, pack):
+    """project conv with row packing: `pack` consecutive pixels form one row, only diagonal blocks are accumulated"""
+    torch.manual_seed(M + 2)
+    g = _bf(torch.randn(M, N, device="cuda"))
+    draw = _bf(torch.randn(M, K, device="cuda") * 2)
+    coef = torch.stack([torch.rand(K, device="cuda") + 0.5, torch.randn(K, device="cuda")]).contiguous()
+    dw = torch.zeros(N, K, device="cuda")
+    ops.pw_wgrad(dw, g=g, a_raw=draw, coef=coef, pack=pack)
+    a = _bf((draw.float() * coef[0] + coef[1]).clamp(0, 6)).float()
+    ref = g.float().t() @ a
+    assert _relerr(dw, ref) < 5e-3, _relerr(dw, ref)
+
+
+@pytest.mark.parametrize("M,N,K,pack", [(128 * 64, 32, 32, 4), (4000, 32, 16, 2), (128 * 50, 64, 32, 2)])
+def test_pw_wgrad_mode0_packed(ops, M, N, K, pack):
+    """factored BatchNorm-backward form with row packing (the cc * sum_m A term is shared out over the diagonal blocks)"""
+    torch.manual_seed(M + 3)
+    a = _bf(torch.randn(M, K, device="cuda"))
+    dz, yraw = _bf(torch.randn(M, N, device="cuda")), _bf(torch.randn(M, N, device="cuda") * 2)
+    coef = (torch.randn(3, N, device="cuda") * 0.5).contiguous()
+    dw = torch.zeros(N, K, device="cuda")
+    ops.pw_wgrad(dw, a=a, dz=dz, y_raw=yraw, coef=coef, pack=pack)
+    g = _bf(coef[0] * dz.float() + coef[1] * yraw.float() + coef[2]).float()
+    ref = g.t() @ a.float()
+    assert _relerr(dw, ref) < 5e-3, _relerr(dw, ref)
