@@ -53,7 +53,7 @@ struct WPrepEntry { long long off; int n, k; int rf, rd; long long off_pf, off_p
 
 struct Plans {            // per batch size
   int n = 0;
-  std::vector<PwGemmPlan> fwd, fwd_eval, dgrad;    // indexed by conv
+  std::vector<PwGemmPlan> fwd, fwd_eval, dgrad;    // indexed by conv (index 0 = the stem run as an im2col GEMM)
   cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
   int train_aug = -1;      // augmentation flag the train graph was captured with
   unsigned long long train_kernels = 0, eval_kernels = 0;   // kernel nodes in each graph (for the launch counter)
@@ -77,6 +77,12 @@ struct Engine {
   float* in_aug = nullptr;
   __nv_bfloat16 *x0 = nullptr, *w_bf16 = nullptr, *wt_bf16 = nullptr, *w_pack = nullptr;
   long long pack_total = 0;
+  // stem as a GEMM (B200DP_STEM=simt: the CUDA-core stem kernels): im2col matrix, bf16 weights (plain + block
+  // diagonal), column sums of the im2col matrix, [32][32] gradient scratch
+  bool stem_gemm = true;
+  int stem_pack = 1;
+  __nv_bfloat16 *x0col = nullptr, *stem_w = nullptr;
+  float *stem_asum = nullptr, *stem_dw = nullptr;
   __nv_bfloat16 *dzd = nullptr, *dze = nullptr, *dp = nullptr, *gx[2] = {nullptr, nullptr}, *dout[2] = {nullptr, nullptr};
   float *sums_all = nullptr;
   size_t sums_bytes = 0;
@@ -158,6 +164,8 @@ size_t layout_workspace(Engine& e, char* base) {
   e.in_labels = carve<int64_t>(p, B);
   e.in_aug = carve<float>(p, B * B200DP_AUG_NPARAM);
   e.x0 = carve<__nv_bfloat16>(p, B * e.S * e.S * 4);
+  e.x0col = carve<__nv_bfloat16>(p, e.stem_gemm ? B * (e.S / 2) * (e.S / 2) * 32 : 8);
+  e.stem_w = carve<__nv_bfloat16>(p, 1024 + 32 * 32 * 16);
   e.w_bf16 = carve<__nv_bfloat16>(p, e.param_total);
   e.wt_bf16 = carve<__nv_bfloat16>(p, e.param_total);
   e.w_pack = carve<__nv_bfloat16>(p, e.pack_total > 0 ? e.pack_total : 8);
@@ -169,6 +177,8 @@ size_t layout_workspace(Engine& e, char* base) {
     c.sums_b = carve<float>(p, 2 * c.coutp);
   }
   for (auto& b : e.blocks) b.xsum = carve<float>(p, b.coutp);
+  e.stem_asum = carve<float>(p, 32);
+  e.stem_dw = carve<float>(p, 32 * 32);
   e.sums_all = reinterpret_cast<float*>(sums0);
   e.sums_bytes = (size_t)(p - sums0);
   for (auto& c : e.convs) {
@@ -226,6 +236,15 @@ int build_plans(Engine& e, Plans& pl, int n) {
   // forward / data-gradient weights of a conv: the plain bf16 copy, or its block-diagonal copy when the layer is packed
   auto wf = [&](const Conv& c) { return c.pack_f > 1 ? e.w_pack + c.off_pf : e.w_bf16 + c.off_w; };
   auto wd = [&](const Conv& c) { return c.pack_d > 1 ? e.w_pack + c.off_pd : e.wt_bf16 + c.off_w; };
+  if (e.stem_gemm) {
+    const Conv& st = e.convs[0];
+    const int M = n * st.hout * st.hout;
+    const int r = M % e.stem_pack == 0 ? e.stem_pack : 1;
+    for (int ev = 0; ev < 2; ++ev)
+      ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[0] : &pl.fwd[0], A_TMA, ev ? E_PLAIN : E_STATS, M, 32, 32, e.x0col, 32,
+                           nullptr, nullptr, nullptr, 0, r > 1 ? e.stem_w + 1024 : e.stem_w, st.raw, 32, nullptr,
+                           nullptr, st.sums_f, st.coutp, 0, r));
+  }
   for (auto& b : e.blocks) {
     const Conv& cp = e.convs[b.cp];
     const Conv& cd = e.convs[b.cd];
@@ -294,7 +313,14 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
   ENG_TRY(b200dp_preprocess(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0, n, e.S, 4, s));
   mark(e, s, "preprocess");
   Conv& st = e.convs[0];
-  ENG_TRY(stem_fwd_launch(e.x0, e.params + st.off_w, st.raw, train ? st.sums_f : nullptr, st.coutp, n, e.S, e.S, s));
+  if (e.stem_gemm) {
+    ENG_TRY(stem_weight_prep_launch(e.params + st.off_w, e.stem_w, e.stem_pack, s));
+    ENG_TRY(stem_im2col_launch(e.x0, e.x0col, train ? e.stem_asum : nullptr, n, e.S, e.S, s));
+    mark(e, s, "stem_im2col", 0);
+    ENG_TRY(pw_gemm_launch(train ? pl.fwd[0] : pl.fwd_eval[0], s));
+  } else {
+    ENG_TRY(stem_fwd_launch(e.x0, e.params + st.off_w, st.raw, train ? st.sums_f : nullptr, st.coutp, n, e.S, e.S, s));
+  }
   mark(e, s, "stem_fwd", 0);
   if (train) ENG_TRY(bn_fin_f(e, st, (float)n * st.hout * st.hout, s));
   for (auto& b : e.blocks) {
@@ -421,7 +447,14 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       next_res = b.use_res;
     } else {
       Conv& st = e.convs[0];
-      ENG_TRY(stem_wgrad_launch(e.x0, e.dze, st.raw, st.coef_b, e.grads + st.off_w, n, e.S, e.S, s));
+      if (e.stem_gemm) {
+        const int M = n * st.hout * st.hout;
+        ENG_TRY(pw_wgrad_launch(0, M, 32, 32, e.x0col, 32, e.dze, st.raw, 32, st.coef_b, e.stem_asum, e.stem_dw, 32, 0, s,
+                                pw_wgrad_pick_pack(0, M, 32, 32)));
+        ENG_TRY(stem_dw_fold_launch(e.stem_dw, e.grads + st.off_w, s));
+      } else {
+        ENG_TRY(stem_wgrad_launch(e.x0, e.dze, st.raw, st.coef_b, e.grads + st.off_w, n, e.S, e.S, s));
+      }
       mark(e, s, "stem_wgrad", 0);
     }
   }
@@ -477,6 +510,11 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   }
   build_spec(*e, offsets);
   e->pw_pack = !(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0);
+  {
+    const char* st = getenv("B200DP_STEM");
+    e->stem_gemm = !(st != nullptr && std::string(st) == "simt");
+    e->stem_pack = e->pw_pack ? 2 : 1;        // K = N = 32: two pixels per 128-byte row
+  }
   if (e->pw_pack) {
     for (auto& c : e->convs) {
       if (c.kind != 2) continue;

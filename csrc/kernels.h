@@ -30,6 +30,10 @@ int stem_fwd_launch(const void* x, const float* w, void* y, float* stats, int st
                     cudaStream_t s);
 int stem_wgrad_launch(const void* x, const void* dz, const void* yraw, const float* coef, float* dw, int B, int H,
                       int W, cudaStream_t s);
+// the stem as a GEMM: im2col [B*Ho*Wo][32] (+ column sums), bf16 weight layout, gradient fold-back
+int stem_im2col_launch(const void* x, void* col, float* asum, int B, int H, int W, cudaStream_t s);
+int stem_weight_prep_launch(const float* w, void* wout, int pack, cudaStream_t s);
+int stem_dw_fold_launch(const float* scratch, float* dw, cudaStream_t s);
 // pw_wgrad.cu
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
                     int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s,

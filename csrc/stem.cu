@@ -206,6 +206,93 @@ stem_wgrad_kernel(const StemWgradParams P) {
   for (int i = threadIdx.x; i < KT * CO; i += blockDim.x) atomicAdd(P.dw + i, s_dw[i]);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// The stem as a GEMM.  K = 27 is too small for the tensor cores only as long as one row is one pixel: with the
+// row packing of pw_gemm / pw_wgrad (r pixels per row against a block-diagonal weight matrix) a [M, 32] im2col
+// matrix is a perfectly good operand, and both the convolution and its weight gradient become the same tcgen05
+// kernels every pointwise layer uses.  What remains here is the im2col pass itself (51 MB in, 103 MB out), the
+// weight layout change and folding the [32][32] gradient back into the [27][32] arena slot.
+struct StemColParams {
+  const __nv_bfloat16* x;   // [B,H,W,4]
+  __nv_bfloat16* col;       // [B*Ho*Wo][32]: k = (ky*3 + kx)*3 + ci for k < 27, zero above
+  float* asum;              // [32] column sums over all rows (for the factored weight gradient), or null
+  int B, H, W, Ho, Wo;
+};
+
+__global__ void __launch_bounds__(256)
+stem_im2col_kernel(const StemColParams P) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float s_sum[32];
+  if (threadIdx.x < 32) s_sum[threadIdx.x] = 0.f;
+  __syncthreads();
+  float cs[KT];
+#pragma unroll
+  for (int k = 0; k < KT; ++k) cs[k] = 0.f;
+  const long long npix = (long long)P.B * P.Ho * P.Wo;
+  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < npix;
+       pix += (long long)gridDim.x * blockDim.x) {
+    const int wo = (int)(pix % P.Wo);
+    const int ho = (int)((pix / P.Wo) % P.Ho);
+    const int n = (int)(pix / ((long long)P.Wo * P.Ho));
+    const __nv_bfloat16* xin = P.x + (size_t)n * P.H * P.W * 4;
+    uint32_t h[32];              // one bf16 per k in the low half
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int iy = 2 * ho + t / 3 - 1, ix = 2 * wo + t % 3 - 1;
+      uint2 v = make_uint2(0u, 0u);
+      if (iy >= 0 && iy < P.H && ix >= 0 && ix < P.W) v = __ldg(reinterpret_cast<const uint2*>(xin + ((size_t)iy * P.W + ix) * 4));
+      h[3 * t + 0] = v.x & 0xffffu;
+      h[3 * t + 1] = v.x >> 16;
+      h[3 * t + 2] = v.y & 0xffffu;
+    }
+#pragma unroll
+    for (int k = KT; k < 32; ++k) h[k] = 0u;
+    uint4* dst = reinterpret_cast<uint4*>(P.col + (size_t)pix * 32);
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      dst[q] = make_uint4(h[8 * q + 0] | (h[8 * q + 1] << 16), h[8 * q + 2] | (h[8 * q + 3] << 16),
+                          h[8 * q + 4] | (h[8 * q + 5] << 16), h[8 * q + 6] | (h[8 * q + 7] << 16));
+    if (P.asum != nullptr) {
+#pragma unroll
+      for (int k = 0; k < KT; ++k) cs[k] += __uint_as_float(h[k] << 16);
+    }
+  }
+  if (P.asum != nullptr) {
+#pragma unroll
+    for (int k = 0; k < KT; ++k) {
+      const float a = warp_sum(cs[k]);
+      if ((threadIdx.x & 31) == 0) atomicAdd(&s_sum[k], a);
+    }
+    __syncthreads();
+    if (threadIdx.x < KT) atomicAdd(P.asum + threadIdx.x, s_sum[threadIdx.x]);
+  }
+}
+
+// fp32 arena weights [27][32] (k, cout) -> bf16 GEMM weights: plain [32 cout][32 k] at wout, and the block-diagonal
+// [32 r][32 r] copy at wout + 1024 when r > 1 (k >= 27 and off-diagonal blocks stay zero from allocation)
+__global__ void stem_weight_prep_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wout, int r) {
+  pdl_trigger();
+  pdl_wait();
+  for (int i = threadIdx.x; i < KT * CO; i += blockDim.x) {
+    const int k = i / CO, n = i - k * CO;
+    const __nv_bfloat16 v = __float2bfloat16(w[i]);
+    wout[n * 32 + k] = v;
+    for (int p = 0; p < r && r > 1; ++p) wout[1024 + (p * 32 + n) * (32 * r) + p * 32 + k] = v;
+  }
+}
+
+// grads[k][n] += scratch[n][k] for k < 27 (the GEMM produces dW as [cout][k])
+__global__ void stem_dw_fold_kernel(const float* __restrict__ scratch, float* __restrict__ dw) {
+  pdl_trigger();
+  pdl_wait();
+  for (int i = threadIdx.x; i < KT * CO; i += blockDim.x) {
+    const int k = i / CO, n = i - k * CO;
+    dw[i] += scratch[n * 32 + k];
+  }
+}
+
 }  // namespace
 
 int stem_fwd_launch(const void* x, const float* w, void* y, float* stats, int stats_stride, int B, int H, int W,
@@ -250,4 +337,37 @@ extern "C" int b200dp_stem_fwd(const void* x, const float* w, void* y, float* st
 extern "C" int b200dp_stem_wgrad(const void* x, const void* dz, const void* yraw, const float* coef, float* dw,
                                  int B, int H, int W, void* stream) {
   return stem_wgrad_launch(x, dz, yraw, coef, dw, B, H, W, static_cast<cudaStream_t>(stream));
+}
+
+namespace b200dp {
+
+int stem_im2col_launch(const void* x, void* col, float* asum, int B, int H, int W, cudaStream_t s) {
+  StemColParams P;
+  P.x = static_cast<const __nv_bfloat16*>(x); P.col = static_cast<__nv_bfloat16*>(col); P.asum = asum;
+  P.B = B; P.H = H; P.W = W; P.Ho = (H - 1) / 2 + 1; P.Wo = (W - 1) / 2 + 1;
+  const long long npix = (long long)B * P.Ho * P.Wo;
+  long long blocks = (npix + 255) / 256;
+  const long long cap = (long long)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  B200DP_CUDA(launch_k(stem_im2col_kernel, dim3((unsigned)blocks), dim3(256), 0, s, P));
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int stem_weight_prep_launch(const float* w, void* wout, int pack, cudaStream_t s) {
+  B200DP_CUDA(launch_k(stem_weight_prep_kernel, dim3(1), dim3(256), 0, s, w, static_cast<__nv_bfloat16*>(wout), pack));
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+int stem_dw_fold_launch(const float* scratch, float* dw, cudaStream_t s) {
+  B200DP_CUDA(launch_k(stem_dw_fold_kernel, dim3(1), dim3(256), 0, s, scratch, dw));
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+}  // namespace b200dp
+
+extern "C" int b200dp_stem_im2col(const void* x, void* col, float* asum, int B, int H, int W, void* stream) {
+  return b200dp::stem_im2col_launch(x, col, asum, B, H, W, static_cast<cudaStream_t>(stream));
 }
