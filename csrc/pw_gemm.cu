@@ -313,10 +313,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __syncwarp();
       // ---- pass 1: TMEM -> registers -> bf16 -> swizzled staging tile (one row per thread)
       const uint32_t taddr = tmem_base + ((uint32_t)row0 << 16) + as * ACC_COLS;
-      for (int c16 = 0; c16 < (P.block_n >> 4); ++c16) {
-        uint32_t r[16];
-        tmem_ld_x16(taddr + c16 * 16, r);
-        tmem_ld_wait();
+      // two 16-column loads in flight per wait: the TMEM round trip, not the conversion, paces this loop
+      auto stage16 = [&](int c16, const uint32_t (&r)[16]) {
         const uint4 lo = make_uint4(pack_bf16x2(__uint_as_float(r[0]), __uint_as_float(r[1])),
                                     pack_bf16x2(__uint_as_float(r[2]), __uint_as_float(r[3])),
                                     pack_bf16x2(__uint_as_float(r[4]), __uint_as_float(r[5])),
@@ -329,6 +327,16 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int pc = (c16 & 3) * 2;
         sts16(rowaddr + (((pc) ^ (row & 7)) << 4), lo);
         sts16(rowaddr + (((pc + 1) ^ (row & 7)) << 4), hi);
+      };
+      const int n16 = P.block_n >> 4;
+      for (int c16 = 0; c16 < n16; c16 += 2) {
+        uint32_t ra[16], rb[16];
+        tmem_ld_x16(taddr + c16 * 16, ra);
+        const bool two = c16 + 1 < n16;
+        if (two) tmem_ld_x16(taddr + (c16 + 1) * 16, rb);
+        tmem_ld_wait();
+        stage16(c16, ra);
+        if (two) stage16(c16 + 1, rb);
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);   // accumulator stage free for the MMA warp
