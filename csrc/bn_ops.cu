@@ -9,6 +9,7 @@
 //     dout = g1 (+ g2), sums for the projection BN     gradient join of the residual branch
 //     dp = ca*dout + cb*p_raw + cc                     BatchNorm backward of the projection conv
 // Reference behaviour replaced: cuDNN batch-norm forward/backward and ATen add kernels.
+#include "bn_inline.cuh"
 #include "common.cuh"
 
 namespace b200dp {
@@ -114,7 +115,8 @@ __device__ __forceinline__ void flush_partials(const float* s_part, int nstat, i
 // out = c0*a + c1*b + c2             (BatchNorm backward apply of the projection conv)
 __global__ void __launch_bounds__(256)
 affine_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
-              const float* __restrict__ coef, int three, __nv_bfloat16* __restrict__ out, long long rows, int C) {
+              const float* __restrict__ coef, int three, __nv_bfloat16* __restrict__ out, long long rows, int C,
+              const BnBwdSrc src) {
   pdl_trigger();
   pdl_wait();
   const int CG = C >> 3;
@@ -123,9 +125,13 @@ affine_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restri
   float k0[8], k1[8], k2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    k0[j] = coef[cg * 8 + j];
-    k1[j] = coef[C + cg * 8 + j];
-    k2[j] = three ? coef[2 * C + cg * 8 + j] : 0.f;
+    if (src.sums != nullptr) {   // BatchNorm backward finalised here (first consumer); block 0 publishes it
+      bn_bwd_channel(src, cg * 8 + j, blockIdx.x == 0 && ti == 0, k0[j], k1[j], k2[j]);
+    } else {
+      k0[j] = coef[cg * 8 + j];
+      k1[j] = coef[C + cg * 8 + j];
+      k2[j] = three ? coef[2 * C + cg * 8 + j] : 0.f;
+    }
   }
   const bool hasb = b != nullptr;
   const RowRange rr = block_rows(rows);
@@ -218,7 +224,7 @@ grad_join_stats_kernel(const __nv_bfloat16* __restrict__ g1, const __nv_bfloat16
 __global__ void __launch_bounds__(256)
 block_out_kernel(const __nv_bfloat16* __restrict__ raw, const __nv_bfloat16* __restrict__ res,
                  const float* __restrict__ coef, __nv_bfloat16* __restrict__ out, float* __restrict__ colsum,
-                 long long rows, int C) {
+                 long long rows, int C, const BnFwdSrc src) {
   extern __shared__ float s_part[];   // [ipb][C]
   pdl_trigger();
   pdl_wait();
@@ -227,7 +233,11 @@ block_out_kernel(const __nv_bfloat16* __restrict__ raw, const __nv_bfloat16* __r
   const int cg = threadIdx.x % CG, ti = threadIdx.x / CG;
   float k0[8], k1[8], acc[8];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { k0[j] = coef[cg * 8 + j]; k1[j] = coef[C + cg * 8 + j]; acc[j] = 0.f; }
+  for (int j = 0; j < 8; ++j) {
+    if (src.sums != nullptr) bn_fwd_channel(src, cg * 8 + j, blockIdx.x == 0 && ti == 0, k0[j], k1[j]);
+    else { k0[j] = coef[cg * 8 + j]; k1[j] = coef[C + cg * 8 + j]; }
+    acc[j] = 0.f;
+  }
   const bool hasr = res != nullptr;
   const RowRange rr = block_rows(rows);
   for (long long r0 = rr.begin + ti; r0 < rr.end; r0 += (long long)ipb * NP_UNROLL) {
@@ -324,27 +334,28 @@ static int narrow_grid(long long rows, int ipb) {
 }
 
 int affine_launch(const void* a, const void* b, const float* coef, int three, void* out, long long rows, int C,
-                  cudaStream_t s) {
+                  cudaStream_t s, const BnBwdSrc* src) {
   B200DP_REQUIRE(C % 8 == 0 && C / 8 <= 256, "affine: C=%d unsupported", C);
   const int CG = C / 8;
   const int threads = (256 / CG) * CG;
   const int ipb = threads / CG;
   B200DP_CUDA(launch_k(affine_kernel, dim3((unsigned)narrow_grid(rows, ipb)), dim3(threads), 0, s,
                        static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b), coef, three,
-                       static_cast<__nv_bfloat16*>(out), rows, C));
+                       static_cast<__nv_bfloat16*>(out), rows, C, src ? *src : BnBwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int block_out_launch(const void* raw, const void* res, const float* coef, void* out, float* colsum, long long rows,
-                     int C, cudaStream_t s) {
+                     int C, cudaStream_t s, const BnFwdSrc* src) {
   B200DP_REQUIRE(C % 8 == 0 && C / 8 <= 256, "block_out: C=%d unsupported", C);
   const int CG = C / 8;
   const int threads = (256 / CG) * CG;
   const int ipb = threads / CG;
   B200DP_CUDA(launch_k(block_out_kernel, dim3((unsigned)narrow_grid(rows, ipb)), dim3(threads),
                        (size_t)ipb * C * sizeof(float), s, static_cast<const __nv_bfloat16*>(raw),
-                       static_cast<const __nv_bfloat16*>(res), coef, static_cast<__nv_bfloat16*>(out), colsum, rows, C));
+                       static_cast<const __nv_bfloat16*>(res), coef, static_cast<__nv_bfloat16*>(out), colsum, rows, C,
+                       src ? *src : BnFwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -390,7 +401,7 @@ extern "C" int b200dp_bn_bwd_finalize(const float* sums, int stride, const float
 }
 extern "C" int b200dp_affine(const void* a, const void* b, const float* coef, int three, void* out, long long rows,
                              int C, void* stream) {
-  return affine_launch(a, b, coef, three, out, rows, C, static_cast<cudaStream_t>(stream));
+  return affine_launch(a, b, coef, three, out, rows, C, static_cast<cudaStream_t>(stream), nullptr);
 }
 extern "C" int b200dp_grad_join_stats(const void* g1, const void* g2, const void* x, void* dout, float* sums,
                                       int stride, long long rows, int C, void* stream) {
@@ -398,5 +409,5 @@ extern "C" int b200dp_grad_join_stats(const void* g1, const void* g2, const void
 }
 extern "C" int b200dp_block_out(const void* raw, const void* res, const float* coef, void* out, float* colsum,
                                 long long rows, int C, void* stream) {
-  return block_out_launch(raw, res, coef, out, colsum, rows, C, static_cast<cudaStream_t>(stream));
+  return block_out_launch(raw, res, coef, out, colsum, rows, C, static_cast<cudaStream_t>(stream), nullptr);
 }

@@ -162,7 +162,8 @@ __device__ __forceinline__ void decode_tile(const DwTileParams& P, int tile, int
 }
 
 __global__ void __launch_bounds__(TILE_THREADS, 2)
-dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ DwTileParams P) {
+dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ DwTileParams P,
+                   const __grid_constant__ BnFwdSrc bsrc) {
   pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -189,8 +190,15 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   if (threadIdx.x < 128) s_stats[threadIdx.x] = 0.f;
   pdl_wait();
   if (threadIdx.x < w) {
-    s_coef[threadIdx.x] = P.scale[c0 + threadIdx.x];
-    s_coef[64 + threadIdx.x] = P.shift[c0 + threadIdx.x];
+    float sc, sh;
+    if (bsrc.sums != nullptr) {     // the producer's BatchNorm is finalised here; the first CTA of each chunk publishes it
+      bn_fwd_channel(bsrc, c0 + threadIdx.x, tile0 == 0, sc, sh);
+    } else {
+      sc = P.scale[c0 + threadIdx.x];
+      sh = P.shift[c0 + threadIdx.x];
+    }
+    s_coef[threadIdx.x] = sc;
+    s_coef[64 + threadIdx.x] = sh;
   }
   __syncthreads();
 
@@ -351,7 +359,8 @@ constexpr int HALO_BYTES = 36 * 1024, PLAIN_BYTES = 28 * 1024, BW_STAGE = 2 * HA
 
 __global__ void __launch_bounds__(BW_THREADS, 1)
 dw_tile_bwd_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ CUtensorMap tmG,
-                   const __grid_constant__ CUtensorMap tmE, const __grid_constant__ DwTileParams P) {
+                   const __grid_constant__ CUtensorMap tmE, const __grid_constant__ DwTileParams P,
+                   const __grid_constant__ BnBwdSrc bsrc) {
   pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -379,9 +388,17 @@ dw_tile_bwd_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constan
   if (threadIdx.x < w) {
     s_ecoef[threadIdx.x] = P.scale[c0 + threadIdx.x];
     s_ecoef[64 + threadIdx.x] = P.shift[c0 + threadIdx.x];
-    s_dcoef[threadIdx.x] = P.dcoef[c0 + threadIdx.x];
-    s_dcoef[64 + threadIdx.x] = P.dcoef[P.C + c0 + threadIdx.x];
-    s_dcoef[128 + threadIdx.x] = P.dcoef[2 * P.C + c0 + threadIdx.x];
+    float ca, cb, cc;
+    if (bsrc.sums != nullptr) {     // BatchNorm backward of this conv's output, finalised here
+      bn_bwd_channel(bsrc, c0 + threadIdx.x, tile0 == 0, ca, cb, cc);
+    } else {
+      ca = P.dcoef[c0 + threadIdx.x];
+      cb = P.dcoef[P.C + c0 + threadIdx.x];
+      cc = P.dcoef[2 * P.C + c0 + threadIdx.x];
+    }
+    s_dcoef[threadIdx.x] = ca;
+    s_dcoef[64 + threadIdx.x] = cb;
+    s_dcoef[128 + threadIdx.x] = cc;
   }
   __syncthreads();
 
@@ -674,7 +691,7 @@ bool dw_tile_supported(int B, int H, int W, int C, int stride) {
 }
 
 int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, const float* wts, void* y, float* stats,
-                       int stats_stride, int B, int H, int W, int C, cudaStream_t s) {
+                       int stats_stride, int B, int H, int W, int C, cudaStream_t s, const BnFwdSrc* src) {
   B200DP_REQUIRE(dw_tile_supported(B, H, W, C, 1), "dw_tile_fwd: B=%d H=%d W=%d C=%d unsupported", B, H, W, C);
   DwTileParams P{};
   P.scale = scale; P.shift = shift; P.wts = wts; P.y = static_cast<__nv_bfloat16*>(y);
@@ -696,14 +713,15 @@ int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, co
   const int grid = groups * P.nchunks;
   const size_t smem = 128 + NST * STAGE_BYTES + 2 * NST * 8 + 256 * 4;
   B200DP_CUDA(cudaFuncSetAttribute(dw_tile_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
-  B200DP_CUDA(launch_k(dw_tile_fwd_kernel, dim3((unsigned)grid), dim3(TILE_THREADS), smem, s, tm, P));
+  B200DP_CUDA(launch_k(dw_tile_fwd_kernel, dim3((unsigned)grid), dim3(TILE_THREADS), smem, s, tm, P,
+                       src ? *src : BnFwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
                        const float* dcoef, const float* wts, void* dze, float* stats, int stats_stride, float* dw, int B,
-                       int H, int W, int C, cudaStream_t s) {
+                       int H, int W, int C, cudaStream_t s, const BnBwdSrc* src) {
   B200DP_REQUIRE(dw_tile_supported(B, H, W, C, 1), "dw_tile_bwd: B=%d H=%d W=%d C=%d unsupported", B, H, W, C);
   B200DP_REQUIRE(stats != nullptr && dw != nullptr, "dw_tile_bwd: stats / dw missing");
   DwTileParams P{};
@@ -726,7 +744,8 @@ int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshi
   const int grid = groups * P.nchunks;
   const size_t smem = 128 + BW_NST * BW_STAGE + 2 * BW_NST * 8 + (128 + 128 + 192 + 576) * 4;
   B200DP_CUDA(cudaFuncSetAttribute(dw_tile_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  B200DP_CUDA(launch_k(dw_tile_bwd_kernel, dim3((unsigned)grid), dim3(BW_THREADS), smem, s, tmZ, tmG, tmE, P));
+  B200DP_CUDA(launch_k(dw_tile_bwd_kernel, dim3((unsigned)grid), dim3(BW_THREADS), smem, s, tmZ, tmG, tmE, P,
+                       src ? *src : BnBwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -738,7 +757,8 @@ using namespace b200dp;
 extern "C" int b200dp_dw_fwd_tile(const void* x, const float* scale, const float* shift, const float* w, void* y,
                                   float* stats, int stats_stride, int B, int H, int W, int C, int stride, void* stream) {
   B200DP_REQUIRE(stride == 1, "dw_fwd_tile: stride 1 only");
-  return dw_tile_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, static_cast<cudaStream_t>(stream));
+  return dw_tile_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, static_cast<cudaStream_t>(stream),
+                            nullptr);
 }
 
 extern "C" int b200dp_dw_bwd_tile(const void* e_raw, const float* escale, const float* eshift, const void* dzd,
@@ -746,5 +766,5 @@ extern "C" int b200dp_dw_bwd_tile(const void* e_raw, const float* escale, const 
                                   int stats_stride, float* dw, int B, int H, int W, int C, int stride, void* stream) {
   B200DP_REQUIRE(stride == 1, "dw_bwd_tile: stride 1 only");
   return dw_tile_bwd_launch(e_raw, escale, eshift, dzd, d_raw, dcoef, w, dze, stats, stats_stride, dw, B, H, W, C,
-                            static_cast<cudaStream_t>(stream));
+                            static_cast<cudaStream_t>(stream), nullptr);
 }

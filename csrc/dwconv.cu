@@ -16,6 +16,7 @@
 // Mapping: a thread owns 4 channels (8-byte vectors) and sweeps TH=2 rows along W with a 3-column sliding
 // window in registers (each input vector is loaded once per thread); consecutive threads take consecutive
 // channel groups, so a warp reads contiguous NHWC bytes.  Per-channel sums are reduced thread -> shared -> global.
+#include "bn_inline.cuh"
 #include "common.cuh"
 
 namespace b200dp {
@@ -40,7 +41,7 @@ __device__ __forceinline__ uint32_t ldg4(const __nv_bfloat16* p) { return __ldg(
 // iteration ahead (register prefetch), so global latency overlaps the FMAs of the current column.
 template <int S>
 __global__ void __launch_bounds__(256, 2)
-dw_fwd_kernel(const DwFwdParams P) {
+dw_fwd_kernel(const DwFwdParams P, const BnFwdSrc bsrc) {
   pdl_trigger();
   pdl_wait();
   constexpr int R = (TH - 1) * S + 3;
@@ -57,7 +58,14 @@ dw_fwd_kernel(const DwFwdParams P) {
     float wa[9], wb[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k) { wa[k] = P.w[k * P.C + c0]; wb[k] = P.w[k * P.C + c0 + 1]; }
-    const float sca = P.scale[c0], scb = P.scale[c0 + 1], sha = P.shift[c0], shb = P.shift[c0 + 1];
+    float sca, scb, sha, shb;
+    if (bsrc.sums != nullptr) {     // producer's BatchNorm finalised here; (block row 0, first strip slot) publishes it
+      const bool wr = blockIdx.x == 0 && ti == 0;
+      bn_fwd_channel(bsrc, c0, wr, sca, sha);
+      bn_fwd_channel(bsrc, c0 + 1, wr, scb, shb);
+    } else {
+      sca = P.scale[c0]; scb = P.scale[c0 + 1]; sha = P.shift[c0]; shb = P.shift[c0 + 1];
+    }
     const int rblocks = (P.Ho + TH - 1) / TH;
     const long long items = (long long)P.B * rblocks * P.nseg;
     for (long long item = (long long)blockIdx.x * ipb + ti; item < items; item += (long long)gridDim.x * ipb) {
@@ -178,7 +186,7 @@ struct DwBwdParams {
 // iteration ahead.
 template <int S>
 __global__ void __launch_bounds__(256, 2)
-dw_bwd_kernel(const DwBwdParams P) {
+dw_bwd_kernel(const DwBwdParams P, const BnBwdSrc bsrc) {
   pdl_trigger();
   pdl_wait();
   extern __shared__ float s_red[];                 // [2][C] stats + [9][C] dW
@@ -197,9 +205,16 @@ dw_bwd_kernel(const DwBwdParams P) {
       ga[k] = 0.f; gb[k] = 0.f;
     }
     const float sca = P.escale[c0], scb = P.escale[c0 + 1], sha = P.eshift[c0], shb = P.eshift[c0 + 1];
-    const float kaa = P.dcoef[c0], kab = P.dcoef[c0 + 1];
-    const float kba = P.dcoef[P.C + c0], kbb = P.dcoef[P.C + c0 + 1];
-    const float kca = P.dcoef[2 * P.C + c0], kcb = P.dcoef[2 * P.C + c0 + 1];
+    float kaa, kab, kba, kbb, kca, kcb;
+    if (bsrc.sums != nullptr) {
+      const bool wr = blockIdx.x == 0 && ti == 0;
+      bn_bwd_channel(bsrc, c0, wr, kaa, kba, kca);
+      bn_bwd_channel(bsrc, c0 + 1, wr, kab, kbb, kcb);
+    } else {
+      kaa = P.dcoef[c0]; kab = P.dcoef[c0 + 1];
+      kba = P.dcoef[P.C + c0]; kbb = P.dcoef[P.C + c0 + 1];
+      kca = P.dcoef[2 * P.C + c0]; kcb = P.dcoef[2 * P.C + c0 + 1];
+    }
     float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
     const int rblocks = (P.H + TH - 1) / TH;
     const long long items = (long long)P.B * rblocks * P.nseg;
@@ -408,7 +423,7 @@ void pick_segments(int rows, int width, int B, int C, int* nseg, int* seglen) {
 }  // namespace
 
 int dw_fwd_launch(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
-                  int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s) {
+                  int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s, const BnFwdSrc* src) {
   B200DP_REQUIRE(C % 16 == 0 && C <= 1024, "dw_fwd: C=%d unsupported", C);
   B200DP_REQUIRE(stride == 1 || stride == 2, "dw_fwd: stride must be 1 or 2");
   DwFwdParams P;
@@ -429,15 +444,15 @@ int dw_fwd_launch(const void* x, const float* scale, const float* shift, const f
   if (blocks > cap) blocks = cap;
   const size_t smem = 2 * (size_t)C * sizeof(float);
   const dim3 grid((unsigned)blocks, (unsigned)csplit);
-  if (stride == 1) B200DP_CUDA(launch_k(dw_fwd_kernel<1>, grid, dim3(threads), smem, s, P));
-  else B200DP_CUDA(launch_k(dw_fwd_kernel<2>, grid, dim3(threads), smem, s, P));
+  if (stride == 1) B200DP_CUDA(launch_k(dw_fwd_kernel<1>, grid, dim3(threads), smem, s, P, src ? *src : BnFwdSrc{}));
+  else B200DP_CUDA(launch_k(dw_fwd_kernel<2>, grid, dim3(threads), smem, s, P, src ? *src : BnFwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
                   const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
-                  int H, int W, int C, int stride, cudaStream_t s) {
+                  int H, int W, int C, int stride, cudaStream_t s, const BnBwdSrc* src) {
   B200DP_REQUIRE(C % 16 == 0 && C <= 1024, "dw_bwd: C=%d unsupported", C);
   B200DP_REQUIRE(stride == 1 || stride == 2, "dw_bwd: stride must be 1 or 2");
   DwBwdParams P;
@@ -459,8 +474,8 @@ int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, c
   if (blocks > cap) blocks = cap;
   const size_t smem = 11 * (size_t)C * sizeof(float);
   const dim3 grid((unsigned)blocks, (unsigned)csplit);
-  if (stride == 1) B200DP_CUDA(launch_k(dw_bwd_kernel<1>, grid, dim3(threads), smem, s, P));
-  else B200DP_CUDA(launch_k(dw_bwd_kernel<2>, grid, dim3(threads), smem, s, P));
+  if (stride == 1) B200DP_CUDA(launch_k(dw_bwd_kernel<1>, grid, dim3(threads), smem, s, P, src ? *src : BnBwdSrc{}));
+  else B200DP_CUDA(launch_k(dw_bwd_kernel<2>, grid, dim3(threads), smem, s, P, src ? *src : BnBwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -471,14 +486,15 @@ using namespace b200dp;
 
 extern "C" int b200dp_dw_fwd(const void* x, const float* scale, const float* shift, const float* w, void* y,
                              float* stats, int stats_stride, int B, int H, int W, int C, int stride, void* stream) {
-  return dw_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, stride, static_cast<cudaStream_t>(stream));
+  return dw_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, stride, static_cast<cudaStream_t>(stream),
+                       nullptr);
 }
 
 extern "C" int b200dp_dw_bwd(const void* e_raw, const float* escale, const float* eshift, const void* dzd,
                              const void* d_raw, const float* dcoef, const float* w, void* dze, float* stats,
                              int stats_stride, float* dw, int B, int H, int W, int C, int stride, void* stream) {
   return dw_bwd_launch(e_raw, escale, eshift, dzd, d_raw, dcoef, w, dze, stats, stats_stride, dw, B, H, W, C, stride,
-                       static_cast<cudaStream_t>(stream));
+                       static_cast<cudaStream_t>(stream), nullptr);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -545,7 +561,7 @@ extern "C" int b200dp_dw_fwd_bn_noalloc(const void* x, const float* in_scale, co
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // the previous call's sums are still in the array: clear the 2*C entries this call accumulates into
   B200DP_CUDA(cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(float), s));
-  if (int rc = dw_fwd_launch(x, in_scale, in_shift, w, y, sums, C, B, H, W, C, stride, s)) return rc;
+  if (int rc = dw_fwd_launch(x, in_scale, in_shift, w, y, sums, C, B, H, W, C, stride, s, nullptr)) return rc;
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   return bn_fwd_finalize_launch(sums, C, gamma, beta, (float)B * Ho * Wo, eps, 0.f, nullptr, nullptr, coef_out,
                                 saved_out, C, s);

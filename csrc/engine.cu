@@ -92,6 +92,7 @@ struct Engine {
   WPrepEntry* wprep_dev = nullptr;
   int n_pw = 0;
   bool use_graphs = true;
+  bool bn_fuse = true;      // BatchNorm finalisation in the first consumer's prologue (B200DP_BN_FUSE=0: own kernels)
   bool pw_pack = true;      // row packing of narrow pointwise layers (B200DP_PW_PACK=0: off)
   bool dw_tiled = true;     // stride-1 depthwise convs on the TMA-tiled kernels (B200DP_DW_IMPL=simt: sliding-window kernels)
   cudaStream_t cap_stream = nullptr;   // graphs are captured here (the caller's stream may be the legacy default stream)
@@ -227,6 +228,25 @@ void mark(Engine& e, cudaStream_t s, const char* name, int conv = -1) {
   e.prof_events.emplace_back(label, ev);
 }
 
+// Descriptors for "finalise this BatchNorm in your prologue" (bn_inline.cuh), handed to the first consumer of the
+// coefficients instead of launching a finalisation kernel.
+BnFwdSrc src_f(const Engine& e, const Conv& c, float count) {
+  BnFwdSrc b;
+  b.sums = c.sums_f; b.stride = c.coutp; b.C = c.coutp;
+  b.count = count; b.eps = e.eps; b.momentum = e.momentum;
+  b.gamma = e.params + c.off_g; b.beta = e.params + c.off_b;
+  b.rmean = e.buffers + c.off_rm; b.rvar = e.buffers + c.off_rv;
+  b.coef = c.coef_f; b.saved = c.saved;
+  return b;
+}
+BnBwdSrc src_b(const Engine& e, const Conv& c, float count) {
+  BnBwdSrc b;
+  b.sums = c.sums_b; b.stride = c.coutp; b.C = c.coutp; b.count = count;
+  b.saved = c.saved; b.gamma = e.params + c.off_g;
+  b.coef = c.coef_b; b.dgamma = e.grads + c.off_g; b.dbeta = e.grads + c.off_b;
+  return b;
+}
+
 int build_plans(Engine& e, Plans& pl, int n) {
   pl.n = n;
   const int nc = (int)e.convs.size();
@@ -265,6 +285,7 @@ int build_plans(Engine& e, Plans& pl, int n) {
       ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[b.cp] : &pl.fwd[b.cp], A_BNRELU, ev ? E_PLAIN : E_STATS, Mout, cp.coutp,
                            cp.cinp, nullptr, cp.cinp, cd.raw, nullptr, cd.coef_f, 1, wf(cp), cp.raw,
                            cp.coutp, nullptr, nullptr, cp.sums_f, cp.coutp, 0, cp.pack_f));
+    if (e.bn_fuse) pl.fwd[b.cp].asrc = src_f(e, cd, (float)Mout);     // training plan only: eval reads running-stat coefficients
     // project dgrad: dzd[M, hidden] = mask(dp[M, cout] * W[cout, hidden])   (weights transposed: [hidden][cout])
     ENG_TRY(pw_gemm_plan(&pl.dgrad[b.cp], A_TMA, E_MASKSTATS, Mout, cp.cinp, cp.coutp, e.dp, cp.coutp, nullptr, nullptr,
                          nullptr, 0, wd(cp), e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, 0, cp.pack_d));
@@ -322,7 +343,8 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
     ENG_TRY(stem_fwd_launch(e.x0, e.params + st.off_w, st.raw, train ? st.sums_f : nullptr, st.coutp, n, e.S, e.S, s));
   }
   mark(e, s, "stem_fwd", 0);
-  if (train) ENG_TRY(bn_fin_f(e, st, (float)n * st.hout * st.hout, s));
+  const bool fuse = train && e.bn_fuse;
+  if (train && !fuse) ENG_TRY(bn_fin_f(e, st, (float)n * st.hout * st.hout, s));
   for (auto& b : e.blocks) {
     Conv& cd = e.convs[b.cd];
     Conv& cp = e.convs[b.cp];
@@ -331,33 +353,38 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
       Conv& ce = e.convs[b.ce];
       ENG_TRY(pw_gemm_launch(train ? pl.fwd[b.ce] : pl.fwd_eval[b.ce], s));
       mark(e, s, "pw_fwd_expand", b.ce);
-      if (train) ENG_TRY(bn_fin_f(e, ce, (float)n * ce.hout * ce.hout, s));
+      if (train && !fuse) ENG_TRY(bn_fin_f(e, ce, (float)n * ce.hout * ce.hout, s));
       cin_raw = &ce;
     }
+    const BnFwdSrc in_src = src_f(e, *cin_raw, (float)n * cin_raw->hout * cin_raw->hout);
     if (e.dw_tiled && dw_tile_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
       ENG_TRY(dw_tile_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w,
-                                 cd.raw, train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, s));
+                                 cd.raw, train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, s,
+                                 fuse ? &in_src : nullptr));
     else
       ENG_TRY(dw_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w, cd.raw,
-                            train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, cd.stride, s));
+                            train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, cd.stride, s,
+                            fuse ? &in_src : nullptr));
     mark(e, s, "dw_fwd", b.cd);
-    if (train) ENG_TRY(bn_fin_f(e, cd, (float)n * cd.hout * cd.hout, s));
-    ENG_TRY(pw_gemm_launch(train ? pl.fwd[b.cp] : pl.fwd_eval[b.cp], s));
+    if (train && !fuse) ENG_TRY(bn_fin_f(e, cd, (float)n * cd.hout * cd.hout, s));
+    ENG_TRY(pw_gemm_launch(train ? pl.fwd[b.cp] : pl.fwd_eval[b.cp], s));       // fused: its plan carries src_f(cd)
     mark(e, s, "pw_fwd_project", b.cp);
-    if (train) ENG_TRY(bn_fin_f(e, cp, (float)n * cp.hout * cp.hout, s));
+    if (train && !fuse) ENG_TRY(bn_fin_f(e, cp, (float)n * cp.hout * cp.hout, s));
     const void* res = b.use_res ? e.blocks[b.index - 2].xout : nullptr;
+    const BnFwdSrc cp_src = src_f(e, cp, (float)n * cp.hout * cp.hout);
     ENG_TRY(block_out_launch(cp.raw, res, cp.coef_f, b.xout, train ? b.xsum : nullptr, (long long)n * b.hout * b.hout,
-                             cp.coutp, s));
+                             cp.coutp, s, fuse ? &cp_src : nullptr));
     mark(e, s, "block_out", b.cp);
   }
   const int li = (int)e.convs.size() - 1;
   Conv& cl = e.convs[li];
   ENG_TRY(pw_gemm_launch(train ? pl.fwd[li] : pl.fwd_eval[li], s));
   mark(e, s, "pw_fwd_last", li);
-  if (train) ENG_TRY(bn_fin_f(e, cl, (float)n * cl.hout * cl.hout, s));
+  if (train && !fuse) ENG_TRY(bn_fin_f(e, cl, (float)n * cl.hout * cl.hout, s));
   const int HW = cl.hout * cl.hout;
+  const BnFwdSrc cl_src = src_f(e, cl, (float)n * HW);
   ENG_TRY(head_pool_launch(cl.raw, cl.coef_f, e.pooled, train ? e.drop : nullptr, n, HW, cl.coutp, train ? e.p_drop : 0.f,
-                           e.seed, e.step_dev, s));
+                           e.seed, e.step_dev, s, fuse ? &cl_src : nullptr));
   ENG_TRY(head_fc_launch(e.pooled, e.params + e.off_fcw, e.params + e.off_fcb, e.logits, n, cl.coutp, e.classes, s));
   ENG_TRY(b200dp_softmax_xent(e.logits, e.in_labels, nullptr, train ? e.dlogits : nullptr,
                               train ? e.metrics_train : e.metrics_eval, n, e.classes, (float)n, s));
@@ -379,11 +406,13 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
                           e.grads + e.off_fcb, cl.raw, cl.coef_f, e.dze, cl.sums_b, cl.coutp, n, HW, cl.coutp,
                           e.classes, s));
   mark(e, s, "head_bwd");
-  ENG_TRY(bn_fin_b(e, cl, (float)n * HW, s));
+  const bool fuse = e.bn_fuse;
+  if (!fuse) ENG_TRY(bn_fin_b(e, cl, (float)n * HW, s));
   Block& lb = e.blocks.back();
   const int Ml = n * HW;
+  const BnBwdSrc cl_src = src_b(e, cl, (float)n * HW);
   ENG_TRY(pw_wgrad_launch(0, Ml, cl.coutp, cl.cinp, lb.xout, cl.cinp, e.dze, cl.raw, cl.coutp, cl.coef_b, lb.xsum,
-                          e.grads + cl.off_w, cl.cinp, 0, s));
+                          e.grads + cl.off_w, cl.cinp, 0, s, 1, fuse ? &cl_src : nullptr));
   mark(e, s, "pw_wgrad_last", li);
   int gxi = 0, doi = 0;
   ENG_TRY(retarget_out(pl.dgrad[li], e.gx[gxi]));
@@ -407,8 +436,9 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       ENG_TRY(grad_join_stats_launch(g1, nullptr, cp.raw, nullptr, cp.sums_b, cp.coutp, rows_out, cp.coutp, s));
     }
     mark(e, s, "grad_join", b.cp);
-    ENG_TRY(bn_fin_b(e, cp, (float)rows_out, s));
-    ENG_TRY(affine_launch(dcur, cp.raw, cp.coef_b, 1, e.dp, rows_out, cp.coutp, s));
+    if (!fuse) ENG_TRY(bn_fin_b(e, cp, (float)rows_out, s));
+    const BnBwdSrc cp_src = src_b(e, cp, (float)rows_out);
+    ENG_TRY(affine_launch(dcur, cp.raw, cp.coef_b, 1, e.dp, rows_out, cp.coutp, s, fuse ? &cp_src : nullptr));
     mark(e, s, "bn_bwd_apply", b.cp);
     // ---- projection conv: weight gradient, then data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
     ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, e.dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
@@ -417,26 +447,30 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     mark(e, s, "pw_wgrad_project", b.cp);
     ENG_TRY(pw_gemm_launch(pl.dgrad[b.cp], s));
     mark(e, s, "pw_dgrad_project", b.cp);
-    ENG_TRY(bn_fin_b(e, cd, (float)rows_out, s));
+    if (!fuse) ENG_TRY(bn_fin_b(e, cd, (float)rows_out, s));
     // ---- depthwise conv backward (data + weight gradient, mask, statistics for the producer's BatchNorm)
     Conv& cin_raw = b.ce >= 0 ? e.convs[b.ce] : e.convs[0];
+    const BnBwdSrc cd_src = src_b(e, cd, (float)rows_out);
     if (e.dw_tiled && dw_tile_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
       ENG_TRY(dw_tile_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
                                  e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
-                                 cd.hin, cd.coutp, s));
+                                 cd.hin, cd.coutp, s, fuse ? &cd_src : nullptr));
     else
       ENG_TRY(dw_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
                             e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
-                            cd.hin, cd.coutp, cd.stride, s));
+                            cd.hin, cd.coutp, cd.stride, s, fuse ? &cd_src : nullptr));
     mark(e, s, "dw_bwd", b.cd);
     const long long rows_in = (long long)n * b.hin * b.hin;
-    ENG_TRY(bn_fin_b(e, cin_raw, (float)rows_in, s));
+    const bool in_fused = fuse && (b.ce >= 0 || e.stem_gemm);      // the CUDA-core stem weight gradient reads the array
+    if (!in_fused) ENG_TRY(bn_fin_b(e, cin_raw, (float)rows_in, s));
+    const BnBwdSrc in_src = src_b(e, cin_raw, (float)rows_in);
     if (b.ce >= 0) {
       Conv& ce = e.convs[b.ce];
       const __nv_bfloat16* xin = e.blocks[bi - 1].xout;
       ENG_TRY(pw_wgrad_launch(0, (int)rows_in, ce.coutp, ce.cinp, xin, ce.cinp, e.dze, ce.raw, ce.coutp, ce.coef_b,
                               e.blocks[bi - 1].xsum, e.grads + ce.off_w, ce.cinp, 0, s,
-                              e.pw_pack ? pw_wgrad_pick_pack(0, (int)rows_in, ce.coutp, ce.cinp) : 1));
+                              e.pw_pack ? pw_wgrad_pick_pack(0, (int)rows_in, ce.coutp, ce.cinp) : 1,
+                              in_fused ? &in_src : nullptr));
       mark(e, s, "pw_wgrad_expand", b.ce);
       gxi ^= 1;
       ENG_TRY(retarget_out(pl.dgrad[b.ce], e.gx[gxi]));
@@ -450,7 +484,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       if (e.stem_gemm) {
         const int M = n * st.hout * st.hout;
         ENG_TRY(pw_wgrad_launch(0, M, 32, 32, e.x0col, 32, e.dze, st.raw, 32, st.coef_b, e.stem_asum, e.stem_dw, 32, 0, s,
-                                pw_wgrad_pick_pack(0, M, 32, 32)));
+                                pw_wgrad_pick_pack(0, M, 32, 32), in_fused ? &in_src : nullptr));
         ENG_TRY(stem_dw_fold_launch(e.stem_dw, e.grads + st.off_w, s));
       } else {
         ENG_TRY(stem_wgrad_launch(e.x0, e.dze, st.raw, st.coef_b, e.grads + st.off_w, n, e.S, e.S, s));
@@ -510,6 +544,7 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   }
   build_spec(*e, offsets);
   e->pw_pack = !(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0);
+  e->bn_fuse = !(getenv("B200DP_BN_FUSE") != nullptr && atoi(getenv("B200DP_BN_FUSE")) == 0);
   {
     const char* st = getenv("B200DP_STEM");
     e->stem_gemm = !(st != nullptr && std::string(st) == "simt");

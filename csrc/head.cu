@@ -5,6 +5,7 @@
 // (cifar10_mpi_mobilenet_224.py:178-184) -- and softmax + topk at inference
 // (cifar10_128batch.py:170-172).  One warp per sample; loss sum / correct count / sample count are
 // accumulated on the device as doubles and read once per epoch.
+#include "bn_inline.cuh"
 #include "common.cuh"
 
 namespace b200dp {
@@ -130,13 +131,16 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
 
 __global__ void __launch_bounds__(256)
 head_pool_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ coef, float* __restrict__ pooled,
-                 float* __restrict__ drop, int B, int HW, int C, float p_drop, uint32_t seed, const int* step) {
+                 float* __restrict__ drop, int B, int HW, int C, float p_drop, uint32_t seed, const int* step,
+                 const BnFwdSrc bsrc) {
   pdl_trigger();
   pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const int b = blockIdx.y;
   if (c >= C) return;
-  const float sc = coef[c], sh = coef[C + c];
+  float sc, sh;
+  if (bsrc.sums != nullptr) bn_fwd_channel(bsrc, c, b == 0, sc, sh);
+  else { sc = coef[c]; sh = coef[C + c]; }
   const __nv_bfloat16* src = raw + (size_t)b * HW * C + c;
   float acc = 0.f;
   for (int p = 0; p < HW; ++p) acc += relu6f(fmaf(__bfloat162float(src[(size_t)p * C]), sc, sh));
@@ -264,10 +268,10 @@ head_bwd_mask_kernel(const __nv_bfloat16* __restrict__ raw, const float* __restr
 }  // namespace
 
 int head_pool_launch(const void* raw, const float* coef, float* pooled, float* drop, int B, int HW, int C,
-                     float p_drop, uint32_t seed, const int* step, cudaStream_t s) {
+                     float p_drop, uint32_t seed, const int* step, cudaStream_t s, const BnFwdSrc* src) {
   dim3 grid((C + 255) / 256, B);
   B200DP_CUDA(launch_k(head_pool_kernel, grid, dim3(256), 0, s, static_cast<const __nv_bfloat16*>(raw), coef, pooled, drop, B,
-                       HW, C, p_drop, seed, step));
+                       HW, C, p_drop, seed, step, src ? *src : BnFwdSrc{}));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

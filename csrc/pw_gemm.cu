@@ -89,7 +89,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ CUtensorMap tmAt, const __grid_constant__ CUtensorMap tmBt,
                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA2t,
                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmX,
-               const __grid_constant__ PwGemmParams P) {
+               const __grid_constant__ PwGemmParams P, const __grid_constant__ BnFwdSrc asrc) {
   using L = Layout<AMODE>;
   constexpr int NG = L::kEpiGroups;
   auto stamp = [&](int slot) {
@@ -164,9 +164,19 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   pdl_trigger();
   pdl_wait();
   // coefficient arrays have the unpacked lengths; packed column c belongs to channel c % true width
-  for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) {
-    const int j = i / P.K, c = i - j * P.K;
-    s_acoef[i] = P.acoef[j * P.k_true + c % P.k_true];
+  if (AMODE == A_BNRELU && asrc.sums != nullptr) {
+    // the A-side BatchNorm is finalised here (this GEMM is its first consumer); CTA 0 publishes the coefficients
+    for (int c = threadIdx.x; c < P.K; c += blockDim.x) {
+      float sc, sh;
+      bn_fwd_channel(asrc, c % P.k_true, blockIdx.x == 0 && c < P.k_true, sc, sh);
+      s_acoef[c] = sc;
+      s_acoef[P.K + c] = sh;
+    }
+  } else {
+    for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) {
+      const int j = i / P.K, c = i - j * P.K;
+      s_acoef[i] = P.acoef[j * P.k_true + c % P.k_true];
+    }
   }
   for (int i = threadIdx.x; i < n_ecoef; i += blockDim.x) {
     const int j = i / P.N, c = i - j * P.N;
@@ -483,7 +493,7 @@ int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
   // depend on which layer set it last
   B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   B200DP_CUDA(launch_k(kern, dim3(pl.grid), dim3(Layout<AMODE>::kThreads), pl.smem_bytes, s, pl.tmA, pl.tmB, pl.tmAt, pl.tmBt,
-                       pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p));
+                       pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p, pl.asrc));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -550,6 +560,7 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   B200DP_REQUIRE(amode >= 0 && amode <= 2 && emode >= 0 && emode <= 2, "pw_gemm: bad mode");
   PwGemmParams& p = pl->p;
   p = PwGemmParams{};
+  pl->asrc = BnFwdSrc{};
   p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldo = ldo;
   p.n_true = n_true; p.k_true = k_true;
   p.block_n = N < 128 ? N : 128;

@@ -6,6 +6,8 @@
 #include <cuda_runtime.h>
 #include <stddef.h>
 
+#include "bn_inline.cuh"
+
 namespace b200dp {
 
 enum { A_TMA = 0, A_BNRELU = 1, A_BNGRAD = 2 };
@@ -32,6 +34,7 @@ struct PwGemmParams {
 struct PwGemmPlan {
   CUtensorMap tmA, tmB, tmAt, tmBt, tmA2, tmA2t, tmO, tmX;   // At/Bt: maps for the (possibly narrower) last K chunk
   PwGemmParams p;
+  BnFwdSrc asrc;                // A_BNRELU: finalise the A-side BatchNorm from its producer's sums in the prologue
   int amode, emode, grid;
   size_t smem_bytes;
 };

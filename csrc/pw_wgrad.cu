@@ -26,6 +26,7 @@
 // Work items = (hidden chunk) x (narrow chunk) x (split of the m range); each item's fp32 tile is added to dW with
 // red.global.add (vectorised v4 when the narrow index is the contiguous one).
 // Reference behaviour replaced: cuDNN convolution-backward-filter for the 34 1x1 convs.
+#include "bn_inline.cuh"
 #include "common.cuh"
 #include "pw_gemm.h"
 #include "sm100.cuh"
@@ -87,7 +88,7 @@ __device__ __forceinline__ void cp_async_arrive(uint64_t* bar) {
 // or publish-only (MODE 0) | warps 12-15 = cp.async loaders | warps 1-3 idle.
 template <int MODE>
 __global__ void __launch_bounds__(512, 1)
-pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
+pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ BnBwdSrc bsrc) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int MK = P.mk;
@@ -135,9 +136,20 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P) {
   // on-chip set-up above overlaps the previous kernel's tail (PDL); global data from here on
   pdl_trigger();
   pdl_wait();
-  for (int i = threadIdx.x; i < ncoef; i += blockDim.x) {
-    const int j = i / P.hidden, c = i - j * P.hidden;
-    s_coef[i] = P.coef[j * P.hidden_true + c % P.hidden_true];
+  if (MODE == 0 && bsrc.sums != nullptr) {
+    // BatchNorm backward of the hidden side finalised here (first consumer); CTA 0 publishes ca, cb, cc, dgamma, dbeta
+    for (int c = threadIdx.x; c < P.hidden; c += blockDim.x) {
+      float ca, cb, cc;
+      bn_bwd_channel(bsrc, c % P.hidden_true, blockIdx.x == 0 && c < P.hidden_true, ca, cb, cc);
+      s_coef[c] = ca;
+      s_coef[P.hidden + c] = cb;
+      s_coef[2 * P.hidden + c] = cc;
+    }
+  } else {
+    for (int i = threadIdx.x; i < ncoef; i += blockDim.x) {
+      const int j = i / P.hidden, c = i - j * P.hidden;
+      s_coef[i] = P.coef[j * P.hidden_true + c % P.hidden_true];
+    }
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -381,7 +393,7 @@ int pw_wgrad_pick_pack(int mode, int M, int N, int K) {
 
 int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure, const void* t0, const void* t1,
                     int ld_t, const float* coef, const float* asum, float* dw, int ldw, int max_ctas, cudaStream_t s,
-                    int pack) {
+                    int pack, const BnBwdSrc* src) {
   B200DP_REQUIRE(mode == 0 || mode == 1, "pw_wgrad: bad mode");
   B200DP_REQUIRE(M > 0 && N % 16 == 0 && K % 16 == 0, "pw_wgrad: M=%d N=%d K=%d invalid", M, N, K);
   B200DP_REQUIRE(pure && t0 && coef && dw && (mode == 1 || (t1 && asum)), "pw_wgrad: missing pointers");
@@ -433,10 +445,10 @@ int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure
   const int grid = items < cap ? items : cap;
   if (mode == 0) {
     B200DP_CUDA(cudaFuncSetAttribute(pw_wgrad_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    B200DP_CUDA(launch_k(pw_wgrad_kernel<0>, dim3(grid), dim3(512), smem, s, p));
+    B200DP_CUDA(launch_k(pw_wgrad_kernel<0>, dim3(grid), dim3(512), smem, s, p, src ? *src : BnBwdSrc{}));
   } else {
     B200DP_CUDA(cudaFuncSetAttribute(pw_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    B200DP_CUDA(launch_k(pw_wgrad_kernel<1>, dim3(grid), dim3(512), smem, s, p));
+    B200DP_CUDA(launch_k(pw_wgrad_kernel<1>, dim3(grid), dim3(512), smem, s, p, BnBwdSrc{}));
   }
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
@@ -450,7 +462,7 @@ extern "C" int b200dp_pw_wgrad(int mode, int M, int N, int K, const void* pure, 
                                const void* t1, int ld_t, const float* coef, const float* asum, float* dw, int ldw,
                                int max_ctas, void* stream) {
   return pw_wgrad_launch(mode, M, N, K, pure, ld_pure, t0, t1, ld_t, coef, asum, dw, ldw, max_ctas,
-                         static_cast<cudaStream_t>(stream), 1);
+                         static_cast<cudaStream_t>(stream), 1, nullptr);
 }
 // Same with row packing (see pw_wgrad_pick_pack); pack = 0 lets the library choose.
 extern "C" int b200dp_pw_wgrad_packed(int mode, int M, int N, int K, const void* pure, const void* t0, const void* t1,
@@ -458,5 +470,5 @@ extern "C" int b200dp_pw_wgrad_packed(int mode, int M, int N, int K, const void*
                                       void* stream) {
   if (pack <= 0) pack = pw_wgrad_pick_pack(mode, M, N, K);
   return pw_wgrad_launch(mode, M, N, K, pure, mode == 0 ? K : N, t0, t1, mode == 0 ? N : K, coef, asum, dw, K, max_ctas,
-                         static_cast<cudaStream_t>(stream), pack);
+                         static_cast<cudaStream_t>(stream), pack, nullptr);
 }
