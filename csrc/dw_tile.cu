@@ -49,6 +49,8 @@ struct DwTileParams {
   float* stats;             // [2][stats_stride] or null
   int stats_stride;
   int B, H, W, C;
+  int S, Ho, Wo;            // stride (1 or 2; backward: 1 only) and output size; tiles are tiles of the OUTPUT
+  int nplanes, plane_stride;  // stride 2: four parity planes of the input (row parity, column parity), bytes apart
   int w, nchunks;           // channels OWNED by a chunk (multiple of 16, <= 64), C / w
   int wbox;                 // channels LOADED per chunk (>= w; equal to w in practice, see the launcher)
   int Ht, Wt, NI, Hp, Wp;   // output tile, images per tile, haloed box (Wp may carry one padding column)
@@ -161,6 +163,7 @@ __device__ __forceinline__ void decode_tile(const DwTileParams& P, int tile, int
   n0 = tn * P.NI;
 }
 
+template <int S>
 __global__ void __launch_bounds__(TILE_THREADS, 2)
 dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ DwTileParams P,
                    const __grid_constant__ BnFwdSrc bsrc) {
@@ -207,8 +210,17 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   auto issue = [&](int tile, int stage) {
     int n0, y0, x0;
     decode_tile(P, tile, n0, y0, x0);
-    mbar_arrive_expect_tx(&full[stage], box_bytes);
-    tma_load_4d(base + stage * STAGE_BYTES, &tmX, &full[stage], c0, x0 - 1, y0 - 1, n0);
+    mbar_arrive_expect_tx(&full[stage], box_bytes * (S == 1 ? 1 : 4));
+    if (S == 1) {
+      tma_load_4d(base + stage * STAGE_BYTES, &tmX, &full[stage], c0, x0 - 1, y0 - 1, n0);
+    } else {
+      // plane (pr, pc), entry (i, j) = input pixel (2 (y0-1+i) + pr, 2 (x0-1+j) + pc): the map samples every other
+      // row and column, so every tap of every output is a plain (row, column) offset inside ONE plane
+#pragma unroll
+      for (int pl = 0; pl < 4; ++pl)
+        tma_load_4d(base + stage * STAGE_BYTES + pl * P.plane_stride, &tmX, &full[stage], c0, 2 * (x0 - 1) + (pl & 1),
+                    2 * (y0 - 1) + (pl >> 1), n0);
+    }
   };
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmX);
@@ -253,7 +265,8 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     sh2[k] = f2_make(s_coef[64 + 8 * uj + 2 * k], s_coef[64 + 8 * uj + 2 * k + 1]);
   }
   const uint32_t xf_off = ur0 * rowbytes + (uj << 4), xf_step = urstep * rowbytes;
-  const uint32_t xf_end = P.NI * P.Hp * P.Wp * rowbytes;
+  // stride 2: the four planes are transformed as one range (the few alignment bytes between them hold nothing)
+  const uint32_t xf_end = S == 1 ? P.NI * P.Hp * P.Wp * rowbytes : 3 * P.plane_stride + P.NI * P.Hp * P.Wp * rowbytes;
 
   int it = 0;
 #pragma unroll 1
@@ -281,20 +294,11 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     named_bar_sync(1, CONSUMERS);
     // ---- pass 2: 3x3 stencil over my strip
     const int oy = y0 + st_yy, on = n0 + st_img;
-    const int xe = min(st_xe, P.W - x0);
-    if (active && oy < P.H && on < P.B && st_xs < xe) {
-      uint32_t a0 = sbase + st_off;
-      uint32_t a1 = a0 + rpitch, a2 = a1 + rpitch;
-      char* yp = reinterpret_cast<char*>(P.y + (((size_t)on * P.H + oy) * P.W + x0 + st_xs) * P.C + cq);
+    const int xe = min(st_xe, P.Wo - x0);
+    if (active && oy < P.Ho && on < P.B && st_xs < xe) {
+      char* yp = reinterpret_cast<char*>(P.y + (((size_t)on * P.Ho + oy) * P.Wo + x0 + st_xs) * P.C + cq);
       f2 win[3][3][2];                              // [column slot][row][channel pair]
-      auto load_col = [&](int slot) {
-        const uint2 v0 = lds8(a0), v1 = lds8(a1), v2 = lds8(a2);
-        a0 += rowbytes; a1 += rowbytes; a2 += rowbytes;
-        win[slot][0][0] = f2_from_bf16x2(v0.x); win[slot][0][1] = f2_from_bf16x2(v0.y);
-        win[slot][1][0] = f2_from_bf16x2(v1.x); win[slot][1][1] = f2_from_bf16x2(v1.y);
-        win[slot][2][0] = f2_from_bf16x2(v2.x); win[slot][2][1] = f2_from_bf16x2(v2.y);
-      };
-      auto emit = [&](int sl, int sm, int sr) {     // column slots holding x-1, x, x+1
+      auto emit = [&](int sl, int sm, int sr) {     // column slots holding taps kx = 0, 1, 2
         uint2 o;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -312,18 +316,65 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         *reinterpret_cast<uint2*>(yp) = o;
         yp += ystep;
       };
-      load_col(0);
-      load_col(1);
-      int x = st_xs;
-      // three outputs per trip so that the window rotates by renaming, not by moving registers
+      if (S == 1) {
+        uint32_t a0 = sbase + st_off;
+        uint32_t a1 = a0 + rpitch, a2 = a1 + rpitch;
+        auto load_col = [&](int slot) {
+          const uint2 v0 = lds8(a0), v1 = lds8(a1), v2 = lds8(a2);
+          a0 += rowbytes; a1 += rowbytes; a2 += rowbytes;
+          win[slot][0][0] = f2_from_bf16x2(v0.x); win[slot][0][1] = f2_from_bf16x2(v0.y);
+          win[slot][1][0] = f2_from_bf16x2(v1.x); win[slot][1][1] = f2_from_bf16x2(v1.y);
+          win[slot][2][0] = f2_from_bf16x2(v2.x); win[slot][2][1] = f2_from_bf16x2(v2.y);
+        };
+        load_col(0);
+        load_col(1);
+        int x = st_xs;
+        // three outputs per trip so that the window rotates by renaming, not by moving registers
 #pragma unroll 1
-      for (; x + 3 <= xe; x += 3) {
-        load_col(2); emit(0, 1, 2);
-        load_col(0); emit(1, 2, 0);
-        load_col(1); emit(2, 0, 1);
+        for (; x + 3 <= xe; x += 3) {
+          load_col(2); emit(0, 1, 2);
+          load_col(0); emit(1, 2, 0);
+          load_col(1); emit(2, 0, 1);
+        }
+        if (x < xe) { load_col(2); emit(0, 1, 2); ++x; }
+        if (x < xe) { load_col(0); emit(1, 2, 0); ++x; }
+      } else {
+        // stride 2.  Output (yy, x) reads, relative to the plane origin:
+        //   ky = 0: odd-row planes, row yy      ky = 1: even-row planes, row yy+1      ky = 2: odd-row planes, row yy+1
+        //   kx = 0: odd-col planes, col x       kx = 1: even-col planes, col x+1       kx = 2: odd-col planes, col x+1
+        // so the kx = 2 column of one output is the kx = 0 column of the next: two new columns per output.
+        const uint32_t pl_e = sbase + st_off;                          // (row, col) = (yy, xs) of plane 0 + my quad
+        const uint32_t ps = P.plane_stride;
+        // row r of the window: plane row-parity / row index as listed above
+        uint32_t ae0 = pl_e + 2 * ps + rowbytes;                       // ky=0: plane (1,0), row yy,   col xs+1
+        uint32_t ae1 = pl_e + rpitch + rowbytes;                       // ky=1: plane (0,0), row yy+1, col xs+1
+        uint32_t ae2 = pl_e + 2 * ps + rpitch + rowbytes;              // ky=2: plane (1,0), row yy+1, col xs+1
+        uint32_t ao0 = pl_e + 3 * ps;                                  // ky=0: plane (1,1), row yy,   col xs
+        uint32_t ao1 = pl_e + ps + rpitch;                             // ky=1: plane (0,1), row yy+1, col xs
+        uint32_t ao2 = pl_e + 3 * ps + rpitch;                         // ky=2: plane (1,1), row yy+1, col xs
+        auto load_odd = [&](int slot) {
+          const uint2 v0 = lds8(ao0), v1 = lds8(ao1), v2 = lds8(ao2);
+          ao0 += rowbytes; ao1 += rowbytes; ao2 += rowbytes;
+          win[slot][0][0] = f2_from_bf16x2(v0.x); win[slot][0][1] = f2_from_bf16x2(v0.y);
+          win[slot][1][0] = f2_from_bf16x2(v1.x); win[slot][1][1] = f2_from_bf16x2(v1.y);
+          win[slot][2][0] = f2_from_bf16x2(v2.x); win[slot][2][1] = f2_from_bf16x2(v2.y);
+        };
+        auto load_even = [&](int slot) {
+          const uint2 v0 = lds8(ae0), v1 = lds8(ae1), v2 = lds8(ae2);
+          ae0 += rowbytes; ae1 += rowbytes; ae2 += rowbytes;
+          win[slot][0][0] = f2_from_bf16x2(v0.x); win[slot][0][1] = f2_from_bf16x2(v0.y);
+          win[slot][1][0] = f2_from_bf16x2(v1.x); win[slot][1][1] = f2_from_bf16x2(v1.y);
+          win[slot][2][0] = f2_from_bf16x2(v2.x); win[slot][2][1] = f2_from_bf16x2(v2.y);
+        };
+        load_odd(0);
+        int x = st_xs;
+#pragma unroll 1
+        for (; x + 2 <= xe; x += 2) {
+          load_even(1); load_odd(2); emit(0, 1, 2);
+          load_even(1); load_odd(0); emit(2, 1, 0);
+        }
+        if (x < xe) { load_even(1); load_odd(2); emit(0, 1, 2); }
       }
-      if (x < xe) { load_col(2); emit(0, 1, 2); ++x; }
-      if (x < xe) { load_col(0); emit(1, 2, 0); ++x; }
     }
     fence_proxy_async_smem();          // my generic-proxy writes to the stage vs. the next TMA write into it
     __syncwarp();
@@ -602,7 +653,8 @@ dw_tile_bwd_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constan
 
 uint32_t magic(int d) { return (uint32_t)(((1ull << 32) + (uint64_t)d - 1) / (uint64_t)d); }
 
-int encode_nhwc(CUtensorMap* out, const void* base, int B, int H, int W, int C, int box_c, int box_w, int box_h, int box_n) {
+int encode_nhwc(CUtensorMap* out, const void* base, int B, int H, int W, int C, int box_c, int box_w, int box_h, int box_n,
+                int estride = 1) {
   typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -619,8 +671,9 @@ int encode_nhwc(CUtensorMap* out, const void* base, int B, int H, int W, int C, 
   }
   cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
   cuuint64_t gstride[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-  cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)box_w, (cuuint32_t)box_h, (cuuint32_t)box_n};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
+  // element stride e in x and y: the box spans e*box_w x e*box_h pixels and every e-th one is loaded
+  cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)(box_w * estride), (cuuint32_t)(box_h * estride), (cuuint32_t)box_n};
+  cuuint32_t estr[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
   CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr,
                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NAN_REQUEST_ZERO_FMA);   // halo outside the tensor = NaN (see pass 1)
@@ -641,80 +694,117 @@ int chunk_width(int C) {
   return 0;
 }
 
-// tile shape: maximise (thread utilisation) x (useful fraction of the haloed box) x (segment prologue) x (edge waste)
-void pick_tile(DwTileParams& P, int halo_limit = STAGE_BYTES, int plain_limit = 0) {
+// tile shape: maximise (thread utilisation) x (useful fraction of the haloed box) x (segment prologue) x (edge waste).
+// Tiles are tiles of the OUTPUT (P.Ho x P.Wo); stride 2 loads four parity planes of (Ht+1) x (Wt+1) input pixels.
+// Returns the score of the choice it leaves in P (so that a caller can compare chunk widths).
+double pick_tile(DwTileParams& P, int halo_limit = STAGE_BYTES, int plain_limit = 0) {
   const int Q = P.wbox / 4;
   P.par = CONSUMERS / Q;
-  const int max_px = halo_limit / (2 * P.wbox);
+  const int rowbytes = 2 * P.wbox;
+  const int hal = P.S == 1 ? 2 : 1, planes = P.S == 1 ? 1 : 4;
   double best = -1.0;
-  const int wcand[4] = {P.W < 28 ? P.W : 28, 21, 14, 7};
+  const int wcand[4] = {P.Wo < 28 ? P.Wo : 28, 21, 14, 7};
   for (int wi = 0; wi < 4; ++wi) {
     const int Wt = wcand[wi];
-    if (Wt > P.W || (wi > 0 && Wt >= wcand[0])) continue;
-    int Wp = Wt + 2;
+    if (Wt > P.Wo || (wi > 0 && Wt >= wcand[0])) continue;
+    int Wp = Wt + hal;
     if (P.wbox < 64 && (Wp % 2) == 0) ++Wp;     // odd pitch: rows of < 128 bytes then land in different banks
-    for (int Ht = 1; Ht <= P.H && Ht <= 32; ++Ht)
+    for (int Ht = 1; Ht <= P.Ho && Ht <= 32; ++Ht)
       for (int NI = 1; NI <= 4 && NI <= P.B; ++NI) {
-        const int Hp = Ht + 2;
-        if (NI * Hp * Wp > max_px) continue;
-        if (plain_limit > 0 && NI * Ht * (Wp - 2) * 2 * P.wbox > plain_limit) continue;
+        const int Hp = Ht + hal;
+        // planes start 128-byte aligned (TMA) AND on a row boundary (pass 1 walks all planes as one array of rows)
+        const int palign = (128 % rowbytes == 0 || rowbytes % 128 == 0) ? (rowbytes > 128 ? rowbytes : 128) : 3 * 128;
+        const int plane_bytes = (NI * Hp * Wp * rowbytes + palign - 1) / palign * palign;
+        if (planes * plane_bytes > halo_limit) continue;
+        if (plain_limit > 0 && NI * Ht * (Wp - 2) * rowbytes > plain_limit) continue;
         for (int NSEG = 1; NSEG <= 4; ++NSEG) {
           const int SL = (Wt + NSEG - 1) / NSEG;
-          if (SL < 5 && NSEG > 1) continue;
+          if (SL < (P.S == 1 ? 5 : 4) && NSEG > 1) continue;
           const int strips = NI * Ht * NSEG;
           if (strips > P.par) continue;             // one strip per thread: its geometry is hoisted out of the tile loop
           const double util = (double)strips / P.par * ((double)Wt / (NSEG * SL));
           const double halo = (double)(Ht * Wt) / (Hp * Wp);
-          const double prol = (double)SL / (SL + 2);
-          const int tx = (P.W + Wt - 1) / Wt, ty = (P.H + Ht - 1) / Ht, tn = (P.B + NI - 1) / NI;
-          const double edge = ((double)P.W / (tx * Wt)) * ((double)P.H / (ty * Ht)) * ((double)P.B / (tn * NI));
-          const double size = NI * Hp * Wp * 2.0 * P.wbox >= 16384 ? 1.0 : 0.9;   // small boxes: more barrier trips
+          const double prol = P.S == 1 ? (double)SL / (SL + 2) : (double)SL / (SL + 0.5);
+          const int tx = (P.Wo + Wt - 1) / Wt, ty = (P.Ho + Ht - 1) / Ht, tn = (P.B + NI - 1) / NI;
+          const double edge = ((double)P.Wo / (tx * Wt)) * ((double)P.Ho / (ty * Ht)) * ((double)P.B / (tn * NI));
+          const double size = planes * plane_bytes >= 16384 ? 1.0 : 0.9;          // small boxes: more barrier trips
           const double score = util * (0.5 + 0.5 * halo) * (0.7 + 0.3 * prol) * edge * size;
           if (score > best) {
             best = score;
             P.Wt = Wt; P.Ht = Ht; P.NI = NI; P.Hp = Hp; P.Wp = Wp; P.NSEG = NSEG; P.SL = SL;
+            P.plane_stride = plane_bytes;
           }
         }
       }
   }
-  P.Wq = P.Wp - 2;           // un-haloed box: same pitch parity as the haloed one
+  P.nplanes = planes;
+  P.Wq = P.Wp - 2;           // un-haloed box (backward): same pitch parity as the haloed one
   P.nstrips = P.NI * P.Ht * P.NSEG;
-  P.tiles_x = (P.W + P.Wt - 1) / P.Wt;
-  P.tiles_y = (P.H + P.Ht - 1) / P.Ht;
+  P.tiles_x = (P.Wo + P.Wt - 1) / P.Wt;
+  P.tiles_y = (P.Ho + P.Ht - 1) / P.Ht;
   P.ntiles = P.tiles_x * P.tiles_y * ((P.B + P.NI - 1) / P.NI);
+  return best;
 }
 
 }  // namespace
 
-bool dw_tile_supported(int B, int H, int W, int C, int stride) {
+bool dw_tile_supported(int B, int H, int W, int C, int stride) {      // forward AND backward
   return stride == 1 && chunk_width(C) > 0 && B >= 1 && H >= 1 && W >= 1 && H < 4096 && W < 4096;
+}
+bool dw_tile_fwd_supported(int B, int H, int W, int C, int stride) {  // the forward kernel also does stride 2
+  return (stride == 1 || stride == 2) && chunk_width(C) > 0 && B >= 1 && H >= 1 && W >= 1 && H < 4096 && W < 4096;
 }
 
 int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, const float* wts, void* y, float* stats,
-                       int stats_stride, int B, int H, int W, int C, cudaStream_t s, const BnFwdSrc* src) {
-  B200DP_REQUIRE(dw_tile_supported(B, H, W, C, 1), "dw_tile_fwd: B=%d H=%d W=%d C=%d unsupported", B, H, W, C);
+                       int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s, const BnFwdSrc* src) {
+  B200DP_REQUIRE(dw_tile_fwd_supported(B, H, W, C, stride), "dw_tile_fwd: B=%d H=%d W=%d C=%d stride=%d unsupported", B, H,
+                 W, C, stride);
   DwTileParams P{};
   P.scale = scale; P.shift = shift; P.wts = wts; P.y = static_cast<__nv_bfloat16*>(y);
   P.stats = stats; P.stats_stride = stats_stride;
   P.B = B; P.H = H; P.W = W; P.C = C;
-  P.w = chunk_width(C);
+  P.S = stride; P.Ho = (H - 1) / stride + 1; P.Wo = (W - 1) / stride + 1;
+  if (stride == 1) {
+    P.w = chunk_width(C);
+    P.wbox = P.w;   // measured: loading 64-wide (conflict-free 128-byte) rows for a 48-wide chunk idles a quarter of the
+                    // lanes and is slower than living with the bank conflicts of 96-byte rows (108 vs 90 us on 56x56x144)
+    pick_tile(P);
+  } else {
+    // stride 2 moves four input pixels per output: tiles hold few outputs, so a narrower chunk (more strips per
+    // tile for the same bytes) can keep more threads busy.  Try every equal split; narrow TMA rows cost a little.
+    DwTileParams best = P;
+    double best_score = -1.0;
+    for (int w = 64; w >= 16; w -= 16) {
+      if (C % w != 0) continue;
+      DwTileParams T = P;
+      T.w = T.wbox = w;
+      const double row_eff = w >= 64 ? 1.0 : (w >= 48 ? 0.97 : (w >= 32 ? 0.92 : 0.75));
+      const double sc = pick_tile(T) * row_eff;
+      if (sc > best_score) { best_score = sc; best = T; }
+    }
+    B200DP_REQUIRE(best_score > 0.0, "dw_tile_fwd: no tile fits (C=%d)", C);
+    P = best;
+  }
   P.nchunks = C / P.w;
-  P.wbox = P.w;   // measured: loading 64-wide (conflict-free 128-byte) rows for a 48-wide chunk idles a quarter of the lanes
-                  // and is slower than living with the bank conflicts of 96-byte rows (108 vs 90 us on 56x56x144)
-  pick_tile(P);
   P.magic_wp = magic(P.Wp); P.magic_hp = magic(P.Hp); P.magic_tx = magic(P.tiles_x); P.magic_ty = magic(P.tiles_y);
   P.magic_nseg = magic(P.NSEG); P.magic_ht = magic(P.Ht);
   CUtensorMap tm;
-  if (int rc = encode_nhwc(&tm, x, B, H, W, C, P.wbox, P.Wp, P.Hp, P.NI)) return rc;
+  if (int rc = encode_nhwc(&tm, x, B, H, W, C, P.wbox, P.Wp, P.Hp, P.NI, stride)) return rc;
   // CTA b owns chunk b % nchunks: the grid is a multiple of nchunks, at most two CTAs per SM
   int groups = 2 * num_sms() / P.nchunks;
   if (groups < 1) groups = 1;
   if (groups > P.ntiles) groups = P.ntiles;
   const int grid = groups * P.nchunks;
   const size_t smem = 128 + NST * STAGE_BYTES + 2 * NST * 8 + 256 * 4;
-  B200DP_CUDA(cudaFuncSetAttribute(dw_tile_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
-  B200DP_CUDA(launch_k(dw_tile_fwd_kernel, dim3((unsigned)grid), dim3(TILE_THREADS), smem, s, tm, P,
-                       src ? *src : BnFwdSrc{}));
+  if (stride == 1) {
+    B200DP_CUDA(cudaFuncSetAttribute(dw_tile_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
+    B200DP_CUDA(launch_k(dw_tile_fwd_kernel<1>, dim3((unsigned)grid), dim3(TILE_THREADS), smem, s, tm, P,
+                         src ? *src : BnFwdSrc{}));
+  } else {
+    B200DP_CUDA(cudaFuncSetAttribute(dw_tile_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
+    B200DP_CUDA(launch_k(dw_tile_fwd_kernel<2>, dim3((unsigned)grid), dim3(TILE_THREADS), smem, s, tm, P,
+                         src ? *src : BnFwdSrc{}));
+  }
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -728,6 +818,7 @@ int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshi
   P.scale = escale; P.shift = eshift; P.wts = wts; P.y = static_cast<__nv_bfloat16*>(dze);
   P.stats = stats; P.stats_stride = stats_stride; P.dcoef = dcoef; P.dwg = dw;
   P.B = B; P.H = H; P.W = W; P.C = C;
+  P.S = 1; P.Ho = H; P.Wo = W;
   P.w = chunk_width(C);
   P.nchunks = C / P.w;
   P.wbox = P.w;
@@ -756,9 +847,8 @@ using namespace b200dp;
 
 extern "C" int b200dp_dw_fwd_tile(const void* x, const float* scale, const float* shift, const float* w, void* y,
                                   float* stats, int stats_stride, int B, int H, int W, int C, int stride, void* stream) {
-  B200DP_REQUIRE(stride == 1, "dw_fwd_tile: stride 1 only");
-  return dw_tile_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, static_cast<cudaStream_t>(stream),
-                            nullptr);
+  return dw_tile_fwd_launch(x, scale, shift, w, y, stats, stats_stride, B, H, W, C, stride,
+                            static_cast<cudaStream_t>(stream), nullptr);
 }
 
 extern "C" int b200dp_dw_bwd_tile(const void* e_raw, const float* escale, const float* eshift, const void* dzd,

@@ -357,9 +357,9 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
       cin_raw = &ce;
     }
     const BnFwdSrc in_src = src_f(e, *cin_raw, (float)n * cin_raw->hout * cin_raw->hout);
-    if (e.dw_tiled && dw_tile_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
+    if (e.dw_tiled && dw_tile_fwd_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
       ENG_TRY(dw_tile_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w,
-                                 cd.raw, train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, s,
+                                 cd.raw, train ? cd.sums_f : nullptr, cd.coutp, n, cd.hin, cd.hin, cd.coutp, cd.stride, s,
                                  fuse ? &in_src : nullptr));
     else
       ENG_TRY(dw_fwd_launch(cin_raw->raw, cin_raw->coef_f, cin_raw->coef_f + cin_raw->coutp, e.params + cd.off_w, cd.raw,

@@ -21,8 +21,10 @@ int dw_tc_fwd_launch(const void* x, const float* scale, const float* shift, cons
                      int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s);
 // dw_tile.cu: stride-1 forward, TMA halo tiles in shared memory + register-window stencil on the CUDA cores
 bool dw_tile_supported(int B, int H, int W, int C, int stride);
+bool dw_tile_fwd_supported(int B, int H, int W, int C, int stride);    // the forward kernel also does stride 2
 int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
-                       int stats_stride, int B, int H, int W, int C, cudaStream_t s, const BnFwdSrc* src = nullptr);
+                       int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s,
+                       const BnFwdSrc* src = nullptr);
 int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
                        const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
                        int H, int W, int C, cudaStream_t s, const BnBwdSrc* src = nullptr);

@@ -28,8 +28,6 @@ def _relerr(a, b):
                                           (2, 112, 32, 1), (3, 15, 144, 2), (130, 14, 384, 1), (2, 28, 144, 2),
                                           (7, 7, 960, 1), (3, 14, 576, 2), (2, 112, 96, 2), (1, 56, 144, 1)])
 def test_dw_fwd(ops, B, H, C, stride, impl):
-    if impl == "tile" and stride != 1:
-        pytest.skip("the tiled kernel is stride 1 only")
     torch.manual_seed(C + H)
     x = _bf(torch.randn(B, H, H, C, device="cuda") * 2)
     coef = torch.stack([torch.rand(C, device="cuda") + 0.5, torch.randn(C, device="cuda")]).contiguous()
