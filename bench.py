@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200dp", choices=["b200dp", "reference"])
     ap.add_argument("--engine", default="auto", choices=["auto", "native", "torch"])
     ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--comm-algo", default="auto", choices=["auto", "one_shot", "two_shot"])
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -67,7 +68,7 @@ def run_b200dp(ns) -> dict:
             raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
         ns.gpus = info.world_size
     mode = "ddp" if info.world_size > 1 else "gpu"
-    cfg = TrainConfig(mode=mode, engine=ns.engine, comm=ns.comm, batch_size=ns.batch, dataset="synthetic")
+    cfg = TrainConfig(mode=mode, engine=ns.engine, comm=ns.comm, comm_algo=ns.comm_algo, batch_size=ns.batch, dataset="synthetic")
     ctx = setup_distributed(cfg.master_addr, cfg.master_port, "auto", info=info)
     if ctx.device.type != "cuda":
         raise SystemExit("bench.py needs a CUDA device")
@@ -138,7 +139,7 @@ def run_b200dp(ns) -> dict:
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": (value / BASELINE_IMAGES_PER_SEC[N]) if N in BASELINE_IMAGES_PER_SEC else None,
         "dtype": "bf16", "data": "synthetic CIFAR-10-shaped uint8 32x32x3, random-init weights",
-        "impl": "b200dp", "engine": engine.name, "comm": cfg.comm,
+        "impl": "b200dp", "engine": engine.name, "comm": cfg.comm + ("/" + getattr(engine, "comm_algo", "") if cfg.comm == "fused" and hasattr(engine, "comm_algo") else ""),
         "config": {"model": "MobileNetV2 (10-class head) @224", "global_batch": B * N, "per_rank_batch": B,
                    "seq_len": None, "image": "224x224x3", "parallelism": f"dp{N}",
                    "optimizer": "Adam lr=1e-4, fp32 master weights",

@@ -29,6 +29,8 @@ class TrainConfig:
     mode: str = "gpu"                 # cpu = serial CPU (mode 1), gpu = single GPU (mode 2), ddp = one rank per GPU (mode 3)
     engine: str = "auto"              # auto | native (sm_100a kernels) | torch (ATen ops; CPU mode and the comparison baseline)
     comm: str = "fused"               # fused (peer-memory all-reduce + Adam kernel) | nccl (baseline: NCCL all-reduce + separate Adam)
+    comm_algo: str = "auto"           # fused kernel: one_shot (every rank pulls all peers' gradients) | two_shot (reduce-scatter +
+                                      # all-gather over peer memory, 2(W-1)/W instead of W-1 gradient volumes per GPU) | auto = two_shot for W >= 4
     # ---- data --------------------------------------------------------------
     data_root: str = "./data"
     dataset: str = "auto"             # auto = real CIFAR-10 if present under data_root, else synthetic
@@ -88,6 +90,8 @@ class TrainConfig:
             raise ValueError(f"engine must be auto|native|torch, got {self.engine!r}")
         if self.comm not in ("fused", "nccl"):
             raise ValueError(f"comm must be fused|nccl, got {self.comm!r}")
+        if self.comm_algo not in ("auto", "one_shot", "two_shot"):
+            raise ValueError(f"comm_algo must be auto|one_shot|two_shot, got {self.comm_algo!r}")
         if self.epochs < 0 or self.lr <= 0:
             raise ValueError("epochs must be >= 0 and lr > 0")
         if not (0.0 <= self.dropout < 1.0):

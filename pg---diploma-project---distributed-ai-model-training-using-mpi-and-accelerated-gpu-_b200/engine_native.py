@@ -77,13 +77,15 @@ class NativeCore:
     """Owns the parameter / buffer arenas and the C++ executor; shared by training and inference."""
 
     def __init__(self, device: torch.device, batch: int, img_size: int, num_classes: int, dropout: float,
-                 seed: int, grads: Optional[torch.Tensor] = None, use_graphs: bool = True) -> None:
+                 seed: int, grads: Optional[torch.Tensor] = None, use_graphs: bool = True,
+                 params: Optional[torch.Tensor] = None) -> None:
         self.lib = _lib.require()
         self.device = device
         self.batch = batch
         self.layout = ArenaLayout(build_spec(img_size, num_classes))
         L = self.layout
-        self.params = torch.zeros(L.total, dtype=torch.float32, device=device)
+        # `params` / `grads` may live in a peer-mapped comm arena (two-shot optimiser: peers store the updated slices)
+        self.params = params if params is not None else torch.zeros(L.total, dtype=torch.float32, device=device)
         self.buffers = torch.zeros(L.buffer_total, dtype=torch.float32, device=device)
         self.grads = grads if grads is not None else torch.zeros(L.total, dtype=torch.float32, device=device)
         self.num_batches_tracked = 0
@@ -156,12 +158,21 @@ class NativeEngine:
         hyper = AdamHyper(cfg.lr, cfg.beta1, cfg.beta2, cfg.eps, cfg.weight_decay)
         self.nccl = cfg.comm == "nccl"
         # gradients live in the peer-mapped comm arena; the executor accumulates straight into it
-        self.fused = FusedAllReduceAdam(ctx, layout.total, hyper)
-        self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
-                               cfg.seed + 7919 * ctx.rank, grads=self.fused.grads)
-        # the fused kernel updates the executor's master weights in place
-        self.fused.params = self.core.params
-        self.fused.args.params[ctx.rank] = self.core.params.data_ptr()
+        algo = cfg.comm_algo
+        if algo == "auto":      # measured at W = 8: one-shot 128 us vs NCCL 72 us for the 9 MB gradient; two-shot moves 4x less
+            algo = "two_shot" if ctx.world_size >= 4 else "one_shot"
+        self.comm_algo = algo
+        self.fused = FusedAllReduceAdam(ctx, layout.total, hyper, algo=algo)
+        if algo == "two_shot":
+            # master weights live in the comm arena: each rank updates its slice and stores it into every peer's copy
+            self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
+                                   cfg.seed + 7919 * ctx.rank, grads=self.fused.grads, params=self.fused.params)
+        else:
+            self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
+                                   cfg.seed + 7919 * ctx.rank, grads=self.fused.grads)
+            # the fused kernel updates the executor's master weights in place
+            self.fused.params = self.core.params
+            self.fused.args.params[ctx.rank] = self.core.params.data_ptr()
         init = build_model(cfg.num_classes, cfg.dropout, cfg.img_size, cfg.pretrained)
         self.core.load_state_dict(init.state_dict())
         del init
