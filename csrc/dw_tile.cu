@@ -80,74 +80,6 @@ __device__ __forceinline__ uint2 lds8(uint32_t addr) {
   return v;
 }
 
-// ---- packed fp32 pairs (Blackwell FFMA2 / FADD2): one issue slot for two channels -------------------------------
-typedef unsigned long long f2;
-__device__ __forceinline__ f2 f2_make(float lo, float hi) {
-  f2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ f2 f2_from_bf16x2(uint32_t v) {
-  f2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(v << 16), "r"(v & 0xffff0000u));
-  return r;
-}
-__device__ __forceinline__ f2 f2_fma(f2 a, f2 b, f2 c) {
-  f2 d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-// the same on two scalar FFMAs (experiment: FFMA2 may issue on one of the two FMA pipes only)
-__device__ __forceinline__ f2 f2_fma_s(f2 a, f2 b, f2 c) {
-  float alo, ahi, blo, bhi, clo, chi;
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(alo), "=f"(ahi) : "l"(a));
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(blo), "=f"(bhi) : "l"(b));
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(clo), "=f"(chi) : "l"(c));
-  f2 d;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(fmaf(alo, blo, clo)), "f"(fmaf(ahi, bhi, chi)));
-  return d;
-}
-#ifdef B200DP_DW_SCALAR_FMA   // measured: forward equal, backward 8-10 % slower than FFMA2
-#define F2_STENCIL_FMA f2_fma_s
-#else
-#define F2_STENCIL_FMA f2_fma
-#endif
-__device__ __forceinline__ f2 f2_add(f2 a, f2 b) {
-  f2 d;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-__device__ __forceinline__ uint32_t f2_to_bf16x2(f2 a) {
-  uint32_t r;
-  asm("{\n\t.reg .b32 lo, hi;\n\tmov.b64 {lo, hi}, %1;\n\tcvt.rn.bf16x2.f32 %0, hi, lo;\n\t}" : "=r"(r) : "l"(a));
-  return r;
-}
-__device__ __forceinline__ uint32_t f2_to_bf16x2_relu(f2 a) {        // max(x, 0) folded into the conversion
-  uint32_t r;
-  asm("{\n\t.reg .b32 lo, hi;\n\tmov.b64 {lo, hi}, %1;\n\tcvt.rn.relu.bf16x2.f32 %0, hi, lo;\n\t}" : "=r"(r) : "l"(a));
-  return r;
-}
-// clamp to [0, 6] on the packed bf16 pair (both bounds are exact in bf16 and rounding is monotonic, so this equals
-// rounding the clamped fp32 value).  max / min return the non-NaN operand: a NaN input becomes 0.
-__device__ __forceinline__ uint32_t bf16x2_relu6(uint32_t v) {
-  uint32_t r;
-  asm("{\n\t.reg .b32 t;\n\tmax.bf16x2 t, %1, %2;\n\tmin.bf16x2 %0, t, %3;\n\t}" : "=r"(r) : "r"(v), "r"(0u), "r"(0x40C040C0u));
-  return r;
-}
-__device__ __forceinline__ f2 f2_pair(uint32_t lo_bits, uint32_t hi_bits) {
-  f2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo_bits), "r"(hi_bits));
-  return r;
-}
-__device__ __forceinline__ void f2_split(f2 v, float& lo, float& hi) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-// NaN -> 0, everything else unchanged: max / min return the non-NaN operand, and one of max(v,0), min(v,0) is zero
-__device__ __forceinline__ uint32_t bf16x2_nan0(uint32_t v) {
-  uint32_t r;
-  asm("{\n\t.reg .b32 p, q;\n\tmax.bf16x2 p, %1, %2;\n\tmin.bf16x2 q, %1, %2;\n\tor.b32 %0, p, q;\n\t}" : "=r"(r) : "r"(v), "r"(0u));
-  return r;
-}
 __device__ __forceinline__ void red_shared_f2(uint32_t addr, f2 v) {
   float lo, hi;
   asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
@@ -258,12 +190,8 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   const int U = w >> 3;                               // 16-byte units per pixel
   const int uj = t % U, ur0 = t / U, urstep = CONSUMERS / U;
   const bool xf_active = ur0 < urstep && 8 * uj >= lo && 8 * uj < hi;
-  f2 sc2[4], sh2[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    sc2[k] = f2_make(s_coef[8 * uj + 2 * k], s_coef[8 * uj + 2 * k + 1]);
-    sh2[k] = f2_make(s_coef[64 + 8 * uj + 2 * k], s_coef[64 + 8 * uj + 2 * k + 1]);
-  }
+  const uint32_t coef_u32 = smem_u32(s_coef) + 32 * uj;     // my unit's scale / shift: re-read per tile (4 loads) so that
+                                                            // they do not occupy 16 registers during the stencil
   const uint32_t xf_off = ur0 * rowbytes + (uj << 4), xf_step = urstep * rowbytes;
   // stride 2: the four planes are transformed as one range (the few alignment bytes between them hold nothing)
   const uint32_t xf_end = S == 1 ? P.NI * P.Hp * P.Wp * rowbytes : 3 * P.plane_stride + P.NI * P.Hp * P.Wp * rowbytes;
@@ -280,15 +208,29 @@ dw_tile_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     //      the copy engine; max(NaN, 0) = 0 (non-propagating max), which is exactly the post-activation zero padding,
     //      so no thread ever needs to know where in the image its pixel lies.
     if (xf_active) {
-#pragma unroll 2
-      for (uint32_t o = xf_off; o < xf_end; o += xf_step) {
-        const uint4 raw = lds16(sbase + o);
-        uint4 v;
-        v.x = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw.x), sc2[0], sh2[0])));
-        v.y = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw.y), sc2[1], sh2[1])));
-        v.z = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw.z), sc2[2], sh2[2])));
-        v.w = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw.w), sc2[3], sh2[3])));
-        sts16(sbase + o, v);
+      f2 sc2[4], sh2[4];
+      {
+        const uint4 a0 = lds16(coef_u32), a1 = lds16(coef_u32 + 16), b0 = lds16(coef_u32 + 256), b1 = lds16(coef_u32 + 272);
+        sc2[0] = f2_pair(a0.x, a0.y); sc2[1] = f2_pair(a0.z, a0.w); sc2[2] = f2_pair(a1.x, a1.y); sc2[3] = f2_pair(a1.z, a1.w);
+        sh2[0] = f2_pair(b0.x, b0.y); sh2[1] = f2_pair(b0.z, b0.w); sh2[2] = f2_pair(b1.x, b1.y); sh2[3] = f2_pair(b1.z, b1.w);
+      }
+      // four independent 16-byte loads in flight, then the math, then the stores (the asm accesses are volatile:
+      // load -> math -> store per unit would serialise on the shared-memory round trip)
+      for (uint32_t o = xf_off; o < xf_end; o += 4 * xf_step) {
+        uint4 raw[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (o + u * xf_step < xf_end) raw[u] = lds16(sbase + o + u * xf_step);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          raw[u].x = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw[u].x), sc2[0], sh2[0])));
+          raw[u].y = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw[u].y), sc2[1], sh2[1])));
+          raw[u].z = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw[u].z), sc2[2], sh2[2])));
+          raw[u].w = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(raw[u].w), sc2[3], sh2[3])));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (o + u * xf_step < xf_end) sts16(sbase + o + u * xf_step, raw[u]);
       }
     }
     named_bar_sync(1, CONSUMERS);
@@ -526,7 +468,7 @@ dw_tile_bwd_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constan
       const f2 cb[4] = {f2_pair(kb0.x, kb0.y), f2_pair(kb0.z, kb0.w), f2_pair(kb1.x, kb1.y), f2_pair(kb1.z, kb1.w)};
       const f2 cc[4] = {f2_pair(kc0.x, kc0.y), f2_pair(kc0.z, kc0.w), f2_pair(kc1.x, kc1.y), f2_pair(kc1.z, kc1.w)};
 #pragma unroll 2
-      for (uint32_t o = xf_off; o < halo_bytes; o += xf_step) {
+      for (uint32_t o = xf_off; o < halo_bytes; o += xf_step) {       // (batching two units here spills registers)
         const uint4 z = lds16(sbase + o), g = lds16(sbase + HALO_BYTES + o);
         uint4 v;
         v.x = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[0], f2_from_bf16x2(z.x), f2_fma(cb[0], f2_from_bf16x2(g.x), cc[0]))));

@@ -421,38 +421,60 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int wsh = w == 64 ? 0 : (w == 32 ? 1 : 2);
         const int col = kc * KCH + p * 8;
         const bool colok = p * 8 < w;
-        float c0[8], c1[8], c2[8];
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj) {
-          c0[jj] = colok ? s_acoef[col + jj] : 0.f;
-          c1[jj] = colok ? s_acoef[P.K + col + jj] : 0.f;
-          c2[jj] = (AMODE == A_BNGRAD && colok) ? s_acoef[2 * P.K + col + jj] : 0.f;
+        // my piece's coefficients as packed fp32 pairs (three 16-byte loads per array instead of 24 scalar ones)
+        f2 k0[4], k1[4], k2[4];
+        if (colok) {
+          const uint32_t ca = smem_u32(s_acoef + col);
+          const uint4 a0 = lds16(ca), a1 = lds16(ca + 16);
+          const uint4 b0 = lds16(ca + 4 * P.K), b1 = lds16(ca + 4 * P.K + 16);
+          k0[0] = f2_pair(a0.x, a0.y); k0[1] = f2_pair(a0.z, a0.w); k0[2] = f2_pair(a1.x, a1.y); k0[3] = f2_pair(a1.z, a1.w);
+          k1[0] = f2_pair(b0.x, b0.y); k1[1] = f2_pair(b0.z, b0.w); k1[2] = f2_pair(b1.x, b1.y); k1[3] = f2_pair(b1.z, b1.w);
+          if (AMODE == A_BNGRAD) {
+            const uint4 c0 = lds16(ca + 8 * P.K), c1 = lds16(ca + 8 * P.K + 16);
+            k2[0] = f2_pair(c0.x, c0.y); k2[1] = f2_pair(c0.z, c0.w); k2[2] = f2_pair(c1.x, c1.y); k2[3] = f2_pair(c1.z, c1.w);
+          }
         }
         mbar_wait(&raw_full[s], ph);
         const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
         const uint32_t sx = smem_u32(stage_a2 + (size_t)s * A_STAGE);
         if (colok) {
+          const bool full_tile = m0 + BM <= P.M;       // rows past M were zero-filled by TMA and must stay zero
+          // all loads of a batch first, then the math, then the stores: the shared-memory round trip (not the ~30
+          // instructions per piece) is what one piece costs, and the volatile asm accesses do not reorder themselves
+          constexpr int NB = AMODE == A_BNRELU ? 8 : 4;      // pieces per batch (A_BNGRAD holds two tiles' worth)
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = rb + 16 * i;
-            const uint32_t off = r * 2 * w + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
-            const bool ok = (m0 + r) < P.M;            // rows past M were zero-filled by TMA and must stay zero
-            float x[8], y[8];
-            unpack8(lds16(sa + off), x);
-            if (AMODE == A_BNRELU) {
+          for (int b0 = 0; b0 < 8; b0 += NB) {
+            uint4 xv[NB], gv[NB];
+            uint32_t off[NB];
 #pragma unroll
-              for (int jj = 0; jj < 8; ++jj) {
-                float z = fmaf(x[jj], c0[jj], c1[jj]);
-                if (P.a_relu6) z = relu6f(z);
-                y[jj] = ok ? z : 0.f;
-              }
-            } else {
-              float g[8];
-              unpack8(lds16(sx + off), g);             // sa = dz, sx = raw activation
-#pragma unroll
-              for (int jj = 0; jj < 8; ++jj) y[jj] = ok ? fmaf(c0[jj], x[jj], fmaf(c1[jj], g[jj], c2[jj])) : 0.f;
+            for (int i = 0; i < NB; ++i) {
+              const int r = rb + 16 * (b0 + i);
+              off[i] = r * 2 * w + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
+              xv[i] = lds16(sa + off[i]);
+              if (AMODE == A_BNGRAD) gv[i] = lds16(sx + off[i]);          // sa = dz, sx = raw activation
             }
-            sts16(sa + off, pack8(y));
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+              const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
+              uint32_t yw[4];
+              if (AMODE == A_BNRELU) {
+                // packed fp32 FMA, one rounding to bf16, clamp on the packed pair (0 and 6 are exact in bf16)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const uint32_t z = f2_to_bf16x2(f2_fma(f2_from_bf16x2(xw[q]), k0[q], k1[q]));
+                  yw[q] = P.a_relu6 ? bf16x2_relu6(z) : z;
+                }
+              } else {
+                const uint32_t gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  yw[q] = f2_to_bf16x2(f2_fma(k0[q], f2_from_bf16x2(xw[q]), f2_fma(k1[q], f2_from_bf16x2(gw[q]), k2[q])));
+              }
+              if (!full_tile && (m0 + rb + 16 * (b0 + i)) >= P.M) yw[0] = yw[1] = yw[2] = yw[3] = 0u;
+              xv[i] = make_uint4(yw[0], yw[1], yw[2], yw[3]);
+            }
+#pragma unroll
+            for (int i = 0; i < NB; ++i) sts16(sa + off[i], xv[i]);
           }
         }
         fence_proxy_async_smem();

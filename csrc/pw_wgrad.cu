@@ -281,12 +281,12 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
       int h0, hw, q0, c_lo, c_hi;
       decode(item, h0, hw, q0, c_lo, c_hi);
       const bool mine = pp * 8 < hw;
-      float sc[8], sh[8];
+      f2 sc[4], sh[4];                           // packed fp32 pairs: scale, shift of my 8 channels
       if (MODE == 1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          sc[j] = mine ? s_coef[h0 + pp * 8 + j] : 0.f;
-          sh[j] = mine ? s_coef[P.hidden + h0 + pp * 8 + j] : 0.f;
+        for (int j = 0; j < 4; ++j) {
+          sc[j] = mine ? f2_make(s_coef[h0 + pp * 8 + 2 * j], s_coef[h0 + pp * 8 + 2 * j + 1]) : 0ull;
+          sh[j] = mine ? f2_make(s_coef[P.hidden + h0 + pp * 8 + 2 * j], s_coef[P.hidden + h0 + pp * 8 + 2 * j + 1]) : 0ull;
         }
       }
       for (int c = c_lo; c < c_hi; ++c) {
@@ -298,12 +298,14 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
           for (int r = rb; r < MK; r += 8) {
             const uint32_t off = blk * MK * 128 + r * 128 + ((p ^ rb) << 4);
             const bool ok = (row0 + r) < P.M;      // rows past M were zero-filled and must stay zero
-            float x[8], y[8];
-            unpack8(lds16(st + off), x);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) y[j] = ok ? relu6f(fmaf(x[j], sc[j], sh[j])) : 0.f;
-            sts16(st + off, make_uint4(pack_bf16x2(y[0], y[1]), pack_bf16x2(y[2], y[3]), pack_bf16x2(y[4], y[5]),
-                                       pack_bf16x2(y[6], y[7])));
+            const uint4 xv = lds16(st + off);
+            uint4 yv;                               // packed fp32 FMA, one rounding, clamp on the packed bf16 pair
+            yv.x = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.x), sc[0], sh[0])));
+            yv.y = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.y), sc[1], sh[1])));
+            yv.z = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.z), sc[2], sh[2])));
+            yv.w = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.w), sc[3], sh[3])));
+            if (!ok) yv = make_uint4(0u, 0u, 0u, 0u);
+            sts16(st + off, yv);
           }
         }
         if (rezero && !mine) {

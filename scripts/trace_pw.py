@@ -34,6 +34,28 @@ for (B, h, cin, cout) in [(2, 7, 160, 960), (128, 7, 160, 960), (128, 14, 96, 57
         print(f"  {names[i]:48s} +{(t[i] - t[0]) / 1e3:7.2f} us")
 
 
+print("=== project conv forward (A = relu6(BN(raw)) rewritten in shared memory) ===")
+for (B, h, cin, cout) in [(128, 7, 960, 160), (128, 14, 576, 96), (128, 14, 384, 64)]:
+    M = B * h * h
+    raw = torch.randn(M, cin, device=dev).to(torch.bfloat16)
+    w = torch.randn(cout, cin, device=dev).to(torch.bfloat16)
+    coef = torch.rand(2, cin, device=dev)
+    stats = torch.zeros(2, cout, device=dev)
+    out = torch.empty(M, cout, dtype=torch.bfloat16, device=dev)
+    fn = lambda: ops.pw_gemm(w, a_raw=raw, acoef=coef, relu6=True, emode=ops.E_STATS, stats=stats, out=out)
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    trace.zero_()
+    lib.b200dp_debug_pw_trace(trace.data_ptr())
+    fn()
+    torch.cuda.synchronize()
+    lib.b200dp_debug_pw_trace(None)
+    t = trace.cpu().tolist()
+    print(f"--- M={M} K={cin} N={cout}")
+    for i in sorted([i for i in range(len(names)) if t[i]], key=lambda i: t[i]):
+        print(f"  {names[i]:48s} +{(t[i] - t[0]) / 1e3:7.2f} us")
+
 print("=== weight gradient (pw_wgrad) ===")
 wnames = ["entry", "setup done", "-", "first stage ready (MMA sees full)", "MMAs of item 0 committed",
           "epilogue sees tmem_full", "epilogue item 0 done (red.adds issued)", "epilogue loop done", "MMA loop done",
