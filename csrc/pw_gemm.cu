@@ -364,30 +364,49 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int col0 = n0 + c * 64 + p * 8;
             const bool colok = col0 < P.N && (c * 64 + p * 8) < P.block_n;
             if (!colok) continue;   // staging columns past the tile hold no data
+            if (EMODE == E_STATS) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int r = row0 + rr + 4 * i;
-              const uint32_t off = c * OUT_CHUNK + r * 128 + ((p ^ (r & 7)) << 4);
-              float x[8];
-              unpack8(lds16(ob_u32 + off), x);
-              if (EMODE == E_STATS) {
+              for (int i = 0; i < 8; ++i) {
+                const int r = row0 + rr + 4 * i;
+                const uint32_t off = c * OUT_CHUNK + r * 128 + ((p ^ (r & 7)) << 4);
+                float x[8];
+                unpack8(lds16(ob_u32 + off), x);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                   s0[c][j] += x[j];
                   s1[c][j] = fmaf(x[j], x[j], s1[c][j]);
                 }
-              } else {
-                float a[8];
-                unpack8(lds16(ax_u32 + off), a);     // rows past M were zero-filled by TMA -> masked to 0
+              }
+            } else {
+              // two rows per trip, loads before math before stores (volatile shared accesses keep their order)
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  const float z = fmaf(a[j], esc[c][j], esh[c][j]);
-                  const float o = (z > 0.f && z < 6.f) ? x[j] : 0.f;
-                  x[j] = o;
-                  s0[c][j] += o;
-                  s1[c][j] = fmaf(o, a[j], s1[c][j]);
+              for (int i = 0; i < 8; i += 2) {
+                uint32_t off[2];
+                uint4 xv[2], av[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                  const int r = row0 + rr + 4 * (i + u);
+                  off[u] = c * OUT_CHUNK + r * 128 + ((p ^ (r & 7)) << 4);
+                  xv[u] = lds16(ob_u32 + off[u]);
+                  av[u] = lds16(ax_u32 + off[u]);      // rows past M were zero-filled by TMA -> masked to 0
                 }
-                sts16(ob_u32 + off, pack8(x));
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                  float x[8], a[8];
+                  unpack8(xv[u], x);
+                  unpack8(av[u], a);
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) {
+                    const float z = fmaf(a[j], esc[c][j], esh[c][j]);
+                    const float o = (z > 0.f && z < 6.f) ? x[j] : 0.f;
+                    x[j] = o;
+                    s0[c][j] += o;
+                    s1[c][j] = fmaf(o, a[j], s1[c][j]);
+                  }
+                  xv[u] = pack8(x);
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) sts16(ob_u32 + off[u], xv[u]);
               }
             }
           }

@@ -295,17 +295,29 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
         const uint32_t st = smem_u32(base + (size_t)s * stage_bytes);
         const bool rezero = last_hw[s] > hw;
         if (MODE == 1 && mine) {
-          for (int r = rb; r < MK; r += 8) {
-            const uint32_t off = blk * MK * 128 + r * 128 + ((p ^ rb) << 4);
-            const bool ok = (row0 + r) < P.M;      // rows past M were zero-filled and must stay zero
-            const uint4 xv = lds16(st + off);
-            uint4 yv;                               // packed fp32 FMA, one rounding, clamp on the packed bf16 pair
-            yv.x = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.x), sc[0], sh[0])));
-            yv.y = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.y), sc[1], sh[1])));
-            yv.z = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.z), sc[2], sh[2])));
-            yv.w = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv.w), sc[3], sh[3])));
-            if (!ok) yv = make_uint4(0u, 0u, 0u, 0u);
-            sts16(st + off, yv);
+          // four rows per trip: loads, then math, then stores (the volatile shared accesses keep their order)
+          for (int r = rb; r < MK; r += 32) {
+            uint32_t off[4];
+            uint4 xv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int ru = r + 8 * u;
+              off[u] = blk * MK * 128 + ru * 128 + ((p ^ rb) << 4);
+              if (ru < MK) xv[u] = lds16(st + off[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const bool ok = (row0 + r + 8 * u) < P.M;      // rows past M were zero-filled and must stay zero
+              // packed fp32 FMA, one rounding, clamp on the packed bf16 pair
+              xv[u].x = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv[u].x), sc[0], sh[0])));
+              xv[u].y = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv[u].y), sc[1], sh[1])));
+              xv[u].z = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv[u].z), sc[2], sh[2])));
+              xv[u].w = bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(xv[u].w), sc[3], sh[3])));
+              if (!ok) xv[u] = make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (r + 8 * u < MK) sts16(st + off[u], xv[u]);
           }
         }
         if (rezero && !mine) {
