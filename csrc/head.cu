@@ -174,14 +174,20 @@ head_fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w, co
 
 constexpr int HEAD_MAX_CLASSES = 16;
 
+// grid (C / 128, B / HEAD_BROWS): a block takes 128 channels x HEAD_BROWS images (the earlier one-block-per-128-channels
+// version walked the whole batch serially, one dependent load after another: 84 us for 164k MACs)
+constexpr int HEAD_BROWS = 8;
+
 __global__ void __launch_bounds__(128)
 head_bwd_fc_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, const float* __restrict__ drop,
                    const float* __restrict__ w, float* __restrict__ dpool, float* __restrict__ dw,
                    float* __restrict__ dbias, int B, int HW, int C, int classes) {
   pdl_trigger();
   pdl_wait();
-  extern __shared__ float s_dl[];    // [B][classes]
-  for (int i = threadIdx.x; i < B * classes; i += blockDim.x) s_dl[i] = dlogits[i];
+  __shared__ float s_dl[HEAD_BROWS * HEAD_MAX_CLASSES];
+  const int b0 = blockIdx.y * HEAD_BROWS;
+  const int nb = min(HEAD_BROWS, B - b0);
+  for (int i = threadIdx.x; i < nb * classes; i += blockDim.x) s_dl[i] = dlogits[(size_t)b0 * classes + i];
   __syncthreads();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c < C) {
@@ -189,27 +195,36 @@ head_bwd_fc_kernel(const float* __restrict__ dlogits, const float* __restrict__ 
 #pragma unroll
     for (int j = 0; j < HEAD_MAX_CLASSES; ++j) { wc[j] = j < classes ? w[(size_t)j * C + c] : 0.f; gw[j] = 0.f; }
     const float inv = 1.f / (float)HW;
-    for (int b = 0; b < B; ++b) {
-      const float pv = pooled[(size_t)b * C + c];
-      float dp = 0.f;
+    float pv[HEAD_BROWS], dr[HEAD_BROWS];
 #pragma unroll
-      for (int j = 0; j < HEAD_MAX_CLASSES; ++j) {
-        if (j < classes) {
-          const float d = s_dl[b * classes + j];
-          dp = fmaf(d, wc[j], dp);
-          gw[j] = fmaf(d, pv, gw[j]);
+    for (int bb = 0; bb < HEAD_BROWS; ++bb) {
+      const bool ok = bb < nb;
+      pv[bb] = ok ? pooled[(size_t)(b0 + bb) * C + c] : 0.f;
+      dr[bb] = ok ? drop[(size_t)(b0 + bb) * C + c] : 0.f;
+    }
+#pragma unroll
+    for (int bb = 0; bb < HEAD_BROWS; ++bb) {
+      if (bb < nb) {
+        float dp = 0.f;
+#pragma unroll
+        for (int j = 0; j < HEAD_MAX_CLASSES; ++j) {
+          if (j < classes) {
+            const float d = s_dl[bb * classes + j];
+            dp = fmaf(d, wc[j], dp);
+            gw[j] = fmaf(d, pv[bb], gw[j]);
+          }
         }
+        dpool[(size_t)(b0 + bb) * C + c] = dp * dr[bb] * inv;
       }
-      dpool[(size_t)b * C + c] = dp * drop[(size_t)b * C + c] * inv;
     }
 #pragma unroll
     for (int j = 0; j < HEAD_MAX_CLASSES; ++j)
-      if (j < classes) dw[(size_t)j * C + c] += gw[j];
+      if (j < classes) atomicAdd(dw + (size_t)j * C + c, gw[j]);
   }
   if (blockIdx.x == 0 && threadIdx.x < classes) {
-    float s = 0.f;
-    for (int b = 0; b < B; ++b) s += s_dl[b * classes + threadIdx.x];
-    dbias[threadIdx.x] += s;
+    float sum = 0.f;
+    for (int bb = 0; bb < nb; ++bb) sum += s_dl[bb * classes + threadIdx.x];
+    atomicAdd(dbias + threadIdx.x, sum);
   }
 }
 
@@ -287,8 +302,7 @@ int head_bwd_launch(const float* dlogits, const float* pooled, const float* drop
                     float* dw, float* dbias, const void* raw, const float* coef, void* dz, float* sums, int stride,
                     int B, int HW, int C, int classes, cudaStream_t s) {
   B200DP_REQUIRE(classes <= HEAD_MAX_CLASSES, "head: at most %d classes", HEAD_MAX_CLASSES);
-  B200DP_REQUIRE((size_t)B * classes * 4 <= 48 * 1024, "head: batch too large for the shared dlogits tile");
-  B200DP_CUDA(launch_k(head_bwd_fc_kernel, dim3((C + 127) / 128), dim3(128), (size_t)B * classes * sizeof(float), s, dlogits,
+  B200DP_CUDA(launch_k(head_bwd_fc_kernel, dim3((C + 127) / 128, (B + HEAD_BROWS - 1) / HEAD_BROWS), dim3(128), 0, s, dlogits,
                        pooled, drop, w, dpool, dw, dbias, B, HW, C, classes));
   B200DP_CHECK_LAUNCH();
   const int CG = C / 8;
