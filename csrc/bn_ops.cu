@@ -288,15 +288,18 @@ weight_prep_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__
   pdl_wait();
   const WPrepEntry e = table[blockIdx.y];
   const int total = e.n * e.k;
+  // every destination is written in ITS OWN contiguous order (the strided side is the fp32 read, which hits L2)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int n = i / e.k, k = i - n * e.k;
+    const int n = i / e.k, k = i - n * e.k;               // (n, k) order: W and its block-diagonal copy
     const __nv_bfloat16 v = __float2bfloat16(master[e.off + i]);
     if (w != nullptr) w[e.off + i] = v;
-    wt[e.off + (long long)k * e.n + n] = v;
     for (int p = 0; p < e.rf && e.rf > 1; ++p)
       wpack[e.off_pf + (long long)(p * e.n + n) * (e.rf * e.k) + p * e.k + k] = v;
+    const int k2 = i / e.n, n2 = i - k2 * e.n;            // (k, n) order: W^T and its block-diagonal copy
+    const __nv_bfloat16 vt = __float2bfloat16(master[e.off + (long long)n2 * e.k + k2]);
+    wt[e.off + i] = vt;
     for (int p = 0; p < e.rd && e.rd > 1; ++p)
-      wpack[e.off_pd + (long long)(p * e.k + k) * (e.rd * e.n) + p * e.n + n] = v;
+      wpack[e.off_pd + (long long)(p * e.k + k2) * (e.rd * e.n) + p * e.n + n2] = vt;
   }
 }
 
