@@ -176,3 +176,34 @@ def test_loader_batches_survive_host_running_ahead(env):
     want = torch.stack([ds.labels[i * 64:(i + 1) * 64].double().sum() + ds.images[i * 64:(i + 1) * 64].double().sum()
                         for i in range(40)])
     assert torch.equal(got, want)
+
+
+@pytest.mark.parametrize("batch,n,img", [(1, 1, 224), (3, 3, 64), (5, 5, 32), (7, 6, 96), (16, 9, 128), (33, 33, 64)])
+def test_engine_odd_shapes(env, batch, n, img):
+    """Every kernel family picks its tiling from the shape (depthwise tiles, row packing of narrow GEMMs, im2col stem):
+    evaluation logits against the fp32 PyTorch model, then a training step, at awkward batch sizes / resolutions."""
+    ops, en = env
+    ref, core = _make(en, batch, img=img, graphs=False)
+    with torch.no_grad():
+        for m in ref.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.uniform_(-0.3, 0.3)
+                m.running_var.uniform_(0.5, 1.5)
+    core.load_state_dict(ref.state_dict())
+    images, labels = _data(n)
+    x = ops.preprocess(images, None, size=img, channels=3).permute(0, 3, 1, 2).float()
+    ref.eval()
+    with torch.no_grad():
+        want = ref(x)
+    core.eval_step(images, labels, n)
+    torch.cuda.synchronize()
+    got = core.logits[:n]
+    assert (got - want).abs().max().item() < 0.05 * want.abs().max().item() + 0.05, (got - want).abs().max().item()
+    core.grads.zero_()
+    core.metrics_train.zero_()
+    core.train_step(images, labels, None, n)
+    torch.cuda.synchronize()
+    m = core.metrics_train.tolist()
+    assert all(v == v for v in m) and m[2] == n
+    assert torch.isfinite(core.grads).all() and float(core.grads.abs().sum()) > 0
+    core.close()
