@@ -147,7 +147,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full[s], AMODE == A_TMA ? 1 : 1 + PROD_THREADS);
+      mbar_init(&full[s], AMODE == A_TMA ? 1 : 1 + PROD_THREADS / 32);   // TMA (weights) + one arrival per transform warp
       mbar_init(&empty[s], 1);
       mbar_init(&raw_full[s], 1);
     }
@@ -243,6 +243,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_wait(&full[s], ph);
           tc_fence_after();
           if (it == 0 && kc == 0) stamp(3);
+          if (it == 0 && kc == 4) stamp(14);      // steady-state pace of the K loop: (stamp 15 - stamp 14) / 8 chunks
+          if (it == 0 && kc == 12) stamp(15);
           const int w = kc == P.kc - 1 ? P.tail_w : KCH;
           const uint64_t da = umma_desc_kmajor(smem_u32(stage_a + (size_t)s * A_STAGE), w);
           const uint64_t db = umma_desc_kmajor(smem_u32(stage_b + (size_t)s * b_stage), w);
@@ -454,6 +456,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         mbar_wait(&raw_full[s], ph);
+        if (pt == 0 && mt == mt0 && kc == 4) stamp(16);     // transform warps: raw chunk 4 / 12 available
+        if (pt == 0 && mt == mt0 && kc == 12) stamp(17);
         const uint32_t sa = smem_u32(stage_a + (size_t)s * A_STAGE);
         const uint32_t sx = smem_u32(stage_a2 + (size_t)s * A_STAGE);
         if (colok) {
@@ -496,8 +500,10 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int i = 0; i < NB; ++i) sts16(sa + off[i], xv[i]);
           }
         }
+        // one arrival per warp: 128 per-thread arrivals on one mbarrier serialise in shared memory, once per K chunk
         fence_proxy_async_smem();
-        mbar_arrive(&full[s]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
         if (++s == stages) { s = 0; ph ^= 1; }
       }
     }

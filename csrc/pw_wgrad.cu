@@ -120,7 +120,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full[s], XF_THREADS);
+      mbar_init(&full[s], XF_THREADS / 32);      // one arrival per transform warp
       mbar_init(&empty[s], 1);
       mbar_init(&raw_full[s], LD_THREADS);
     }
@@ -329,7 +329,8 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
         }
         last_hw[s] = hw;
         fence_proxy_async_smem();
-        mbar_arrive(&full[s]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
         if (++s == stages) { s = 0; ph ^= 1; }
       }
     }

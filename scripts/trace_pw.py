@@ -9,11 +9,12 @@ lib = _lib.require()
 lib.b200dp_debug_pw_trace.argtypes = [ctypes.c_void_p]
 lib.b200dp_debug_pw_trace.restype = None
 dev = torch.device("cuda", 0)
-trace = torch.zeros(16, dtype=torch.int64, device=dev)
+trace = torch.zeros(32, dtype=torch.int64, device=dev)
 names = ["entry", "setup done", "first TMA issued", "first tile landed (MMA sees full)", "MMAs of tile 0 committed",
          "epilogue sees tmem_full", "epilogue tile 0 stored (TMA store issued)", "roles done (thread 0)",
          "teardown barrier passed", "TMEM released", "epilogue warp: tile loop done", "epilogue warp: sums flushed to smem",
-         "epilogue warp: TMA stores complete", "warp 2: after stats atomics, before dealloc"]
+         "epilogue warp: TMA stores complete", "warp 2: after stats atomics, before dealloc",
+         "MMA thread: chunk 4 ready", "MMA thread: chunk 12 ready", "transform: raw chunk 4 landed", "transform: raw chunk 12 landed"]
 for (B, h, cin, cout) in [(2, 7, 160, 960), (128, 7, 160, 960), (128, 14, 96, 576), (128, 28, 32, 192)]:
     M = B * h * h
     a = torch.randn(M, cin, device=dev).to(torch.bfloat16)
