@@ -26,6 +26,8 @@
 // Work items = (hidden chunk) x (narrow chunk) x (split of the m range); each item's fp32 tile is added to dW with
 // red.global.add (vectorised v4 when the narrow index is the contiguous one).
 // Reference behaviour replaced: cuDNN convolution-backward-filter for the 34 1x1 convs.
+#include <cstdlib>
+
 #include "bn_inline.cuh"
 #include "common.cuh"
 #include "pw_gemm.h"
@@ -56,6 +58,8 @@ struct WgradParams {
   const __nv_bfloat16* t1;     // hidden raw tensor 1 (MODE 0: y_raw)
   const __nv_bfloat16* qsrc;   // narrow tensor
   const float* asum;           // MODE 0: [narrow] column sums of the narrow tensor over all M rows
+  int fuse_g;                  // MODE 0: 1 = form G = ca*dz + cb*y + cc in shared memory (transform warps) and issue ONE
+                               // MMA per 16 rows instead of the factored two (these layers are MMA-issue bound)
   unsigned long long* trace;   // debugging: CTA 0 writes %globaltimer at its pipeline milestones (null = off)
 };
 
@@ -198,7 +202,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
           // between two accumulators costs about twice as much per instruction (measured in dw_tc.cu).
           for (int k = 0; k < (MK >> 4); ++k)
             umma_bf16(d_tmem, dh + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, (c > c_lo) | (k > 0));
-          if (MODE == 0)
+          if (MODE == 0 && !P.fuse_g)
             for (int k = 0; k < (MK >> 4); ++k)
               umma_bf16(d_tmem + 128, dh2 + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, (c > c_lo) | (k > 0));
           umma_commit(&empty[s]);
@@ -236,7 +240,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
         tmem_ld_x16(taddr + c16 * 16, r);
         tmem_ld_wait();
         uint32_t r2[16];
-        if (MODE == 0) {
+        if (MODE == 0 && !P.fuse_g) {
           tmem_ld_x16(taddr + 128 + c16 * 16, r2);
           tmem_ld_wait();
         }
@@ -248,8 +252,9 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
             float v[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j)     // each of the `pack` diagonal blocks adds its share of cc * sum_m A
-              v[j] = fmaf(ka, __uint_as_float(r[j]),
-                          fmaf(kb, __uint_as_float(r2[j]), kc * inv_pack * __ldg(P.asum + qt + j)));
+              v[j] = P.fuse_g ? __uint_as_float(r[j])
+                              : fmaf(ka, __uint_as_float(r[j]),
+                                     fmaf(kb, __uint_as_float(r2[j]), kc * inv_pack * __ldg(P.asum + qt + j)));
 #pragma unroll
             for (int j = 0; j < 16; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
           } else {                   // dW[n = narrow][k = hidden]: consecutive lanes -> consecutive k
@@ -318,6 +323,38 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
 #pragma unroll
             for (int u = 0; u < 4; ++u)
               if (r + 8 * u < MK) sts16(st + off[u], xv[u]);
+          }
+        }
+        if (MODE == 0 && P.fuse_g && mine) {
+          // G = ca*dz + cb*y + cc into the dz tile (packed fp32, one rounding to bf16); rows past M stay zero
+          f2 ka[4], kb[4], kc[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int hc = h0 + pp * 8 + 2 * j;
+            ka[j] = f2_make(s_coef[hc], s_coef[hc + 1]);
+            kb[j] = f2_make(s_coef[P.hidden + hc], s_coef[P.hidden + hc + 1]);
+            kc[j] = f2_make(s_coef[2 * P.hidden + hc], s_coef[2 * P.hidden + hc + 1]);
+          }
+          for (int r = rb; r < MK; r += 16) {
+            uint32_t off[2];
+            uint4 zv[2], yv[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              off[u] = blk * MK * 128 + (r + 8 * u) * 128 + ((p ^ rb) << 4);
+              zv[u] = lds16(st + off[u]);
+              yv[u] = lds16(st + h_bytes + off[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const bool ok = (row0 + r + 8 * u) < P.M;
+              zv[u].x = f2_to_bf16x2(f2_fma(ka[0], f2_from_bf16x2(zv[u].x), f2_fma(kb[0], f2_from_bf16x2(yv[u].x), kc[0])));
+              zv[u].y = f2_to_bf16x2(f2_fma(ka[1], f2_from_bf16x2(zv[u].y), f2_fma(kb[1], f2_from_bf16x2(yv[u].y), kc[1])));
+              zv[u].z = f2_to_bf16x2(f2_fma(ka[2], f2_from_bf16x2(zv[u].z), f2_fma(kb[2], f2_from_bf16x2(yv[u].z), kc[2])));
+              zv[u].w = f2_to_bf16x2(f2_fma(ka[3], f2_from_bf16x2(zv[u].w), f2_fma(kb[3], f2_from_bf16x2(yv[u].w), kc[3])));
+              if (!ok) zv[u] = make_uint4(0u, 0u, 0u, 0u);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) sts16(st + off[u], zv[u]);
           }
         }
         if (rezero && !mine) {
@@ -427,7 +464,14 @@ int pw_wgrad_launch(int mode, int M, int N, int K, const void* pure, int ld_pure
   p.ldh = ld_t; p.ldq = ld_pure; p.ldw = ldw;
   p.coef = coef; p.dw = dw;
   p.hchunks = (p.hidden + 127) / 128;
-  const int qmax = mode == 0 ? 128 : 256;                // MODE 0 keeps two accumulators per stage
+  {
+    // measured per layer (profile_step, B200DP_WGRAD_FUSEG=0/1): the transform warps are slower than the second MMA
+    // everywhere except where the wider accumulator saves passes over the hidden tensors (last conv: 47 -> 36 us)
+    const char* fg = getenv("B200DP_WGRAD_FUSEG");
+    const bool want = fg != nullptr ? atoi(fg) != 0 : p.narrow > 160;
+    p.fuse_g = (mode == 0 && want) ? 1 : 0;
+  }
+  const int qmax = (mode == 0 && !p.fuse_g) ? 128 : 256;   // the factored MODE 0 keeps two accumulators per stage
   p.qchunks = (p.narrow + qmax - 1) / qmax;
   while (p.narrow % p.qchunks != 0 || (p.narrow / p.qchunks) % 16 != 0) ++p.qchunks;
   p.nq = p.narrow / p.qchunks;
