@@ -45,7 +45,8 @@ constexpr int OUT_CHUNK = BM * 128;     // one 64-column block of the output til
 constexpr int ACC_COLS = 128;           // TMEM columns per accumulator stage
 constexpr int TMEM_COLS = 256;
 constexpr int EPI_THREADS = 128;
-constexpr int PROD_THREADS = 128;
+constexpr int PROD_THREADS = 256;        // transform warps: 8 (one warp per scheduler cannot hide its own ALU latency)
+constexpr int XROWS = PROD_THREADS / 8;  // rows covered by one sweep of the transform threads
 constexpr int MAX_STAGES = 8;
 
 struct Smem {
@@ -80,7 +81,7 @@ template <int AMODE>
 struct Layout {
   static constexpr int kEpiGroups = 2;
   static constexpr int kProdWarp0 = 4 + 4 * kEpiGroups;
-  static constexpr int kThreads = AMODE == A_TMA ? 384 : 512;
+  static constexpr int kThreads = AMODE == A_TMA ? 384 : 384 + PROD_THREADS;
 };
 
 template <int AMODE, int EMODE>
@@ -432,7 +433,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (AMODE != A_TMA && warp >= L::kProdWarp0) {
     // =========================== transform warps: raw tile -> operand tile, in place ===========================
     const int pt = threadIdx.x - L::kProdWarp0 * 32;   // 0..127
-    const int p = pt & 7, rb = pt >> 3;                // 16-byte piece p of rows rb + 16 i
+    const int p = pt & 7, rb = pt >> 3;                // 16-byte piece p of rows rb + XROWS i
     int s = 0;
     uint32_t ph = 0;
     for (int mt = mt0; mt < P.m_tiles; mt += mt_step) {
@@ -464,14 +465,15 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const bool full_tile = m0 + BM <= P.M;       // rows past M were zero-filled by TMA and must stay zero
           // all loads of a batch first, then the math, then the stores: the shared-memory round trip (not the ~30
           // instructions per piece) is what one piece costs, and the volatile asm accesses do not reorder themselves
-          constexpr int NB = AMODE == A_BNRELU ? 8 : 4;      // pieces per batch (A_BNGRAD holds two tiles' worth)
+          constexpr int NPIECE = BM / XROWS;                 // pieces per thread per chunk
+          constexpr int NB = NPIECE;                         // all of them in one batch
 #pragma unroll
-          for (int b0 = 0; b0 < 8; b0 += NB) {
+          for (int b0 = 0; b0 < NPIECE; b0 += NB) {
             uint4 xv[NB], gv[NB];
             uint32_t off[NB];
 #pragma unroll
             for (int i = 0; i < NB; ++i) {
-              const int r = rb + 16 * (b0 + i);
+              const int r = rb + XROWS * (b0 + i);
               off[i] = r * 2 * w + ((p ^ ((r >> wsh) & ((8 >> wsh) - 1))) << 4);
               xv[i] = lds16(sa + off[i]);
               if (AMODE == A_BNGRAD) gv[i] = lds16(sx + off[i]);          // sa = dz, sx = raw activation
@@ -493,7 +495,7 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int q = 0; q < 4; ++q)
                   yw[q] = f2_to_bf16x2(f2_fma(k0[q], f2_from_bf16x2(xw[q]), f2_fma(k1[q], f2_from_bf16x2(gw[q]), k2[q])));
               }
-              if (!full_tile && (m0 + rb + 16 * (b0 + i)) >= P.M) yw[0] = yw[1] = yw[2] = yw[3] = 0u;
+              if (!full_tile && (m0 + rb + XROWS * (b0 + i)) >= P.M) yw[0] = yw[1] = yw[2] = yw[3] = 0u;
               xv[i] = make_uint4(yw[0], yw[1], yw[2], yw[3]);
             }
 #pragma unroll
@@ -611,8 +613,11 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldo = ldo;
   p.n_true = n_true; p.k_true = k_true;
   p.block_n = N < 128 ? N : 128;
-  p.n_tiles = (N + p.block_n - 1) / p.block_n;
   p.m_tiles = (M + BM - 1) / BM;
+  // few row tiles (7x7 layers): 128-wide column blocks leave SMs idle and make every CTA stream a 128-column weight
+  // tile per K chunk through its own ~27 B/clk of L2 bandwidth; 64-wide blocks use more SMs and halve that tile
+  if (N > 64 && p.m_tiles * ((N + 127) / 128) < num_sms()) p.block_n = 64;
+  p.n_tiles = (N + p.block_n - 1) / p.block_n;
   p.kc = (K + KCH - 1) / KCH;
   p.a0 = static_cast<const __nv_bfloat16*>(a0);
   p.a1 = static_cast<const __nv_bfloat16*>(a1);
