@@ -1,4 +1,7 @@
-// Depthwise 3x3 convolution on the 5th-generation tensor cores (K2, K4, K5).
+// Depthwise 3x3 convolution on the 5th-generation tensor cores (K2, K4, K5) -- EXPERIMENT, not on the
+// training path (opt-in through b200dp_dw_fwd_tc / ops.dw_fwd(impl="tc")): correct, tested, and slower than the
+// CUDA-core tile kernel of dw_tile.cu, because every tcgen05.mma costs 100-200 cycles however small it is (measured
+// with the B200DP_DWTC_DBG switches below) and this formulation needs 36 tiny ones per 128 pixels x 64 channels.
 //
 // A depthwise conv has no reduction over channels, so it is not a GEMM -- but it IS nine GEMMs with diagonal
 // weight matrices:   y[p, c] = sum_t  a[p + shift_t, c] * w_t[c]  =  sum_t ( A_t * diag(w_t) )[p, c].

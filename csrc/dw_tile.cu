@@ -1,27 +1,32 @@
-// Depthwise 3x3 convolution, stride 1, shared-memory tiled and TMA-fed (K2, K4, K5).
+// Depthwise 3x3 convolution, shared-memory tiled and TMA-fed (K2, K4, K5): forward for stride 1 and 2,
+// backward for stride 1.
 //
-// Same contract as dw_fwd_kernel in dwconv.cu:  y_raw = dwconv3x3( relu6(scale * x_raw + shift) ) + sum(y), sum(y^2).
+// Same contract as the kernels in dwconv.cu:  y_raw = dwconv3x3( relu6(scale * x_raw + shift) ) + sum(y), sum(y^2).
 // What is different is where the latency goes.  dwconv.cu keeps a sliding window AND a register prefetch of raw
 // global words per thread (126 registers, 21 % of the warps resident, ~55 instructions per output: address
 // arithmetic, per-row masks, unpacking every input three times).  Here
 //
-//   producer warp   one TMA box {w channels, Wt+2, Ht+2, NI images} of the RAW producer output per tile, halo
-//                   zero-filled, NST boxes in flight per CTA and two CTAs per SM -- global latency is covered by
-//                   bytes in flight in shared memory, not by registers;
-//   8 compute warps pass 1: rewrite the tile in place, relu6(scale*x+shift) -> bf16, and 0 where the halo lies
-//                   outside the image (padding is post-activation); each input element is transformed ONCE;
-//                   pass 2: a thread owns 4 channels and walks one output row segment with a 3x3 window of fp32
-//                   registers (3 LDS.64 + 12 unpacks + 36 FMA per 4 outputs), stores 8 bytes per output pixel
-//                   (a half-warp writes one contiguous 128-byte pixel) and keeps the BatchNorm sums in registers.
+//   thread 0        keeps NST TMA boxes {w channels, Wt+2, Ht+2, NI images} of the RAW producer output in flight per
+//                   CTA (two CTAs per SM): global latency is covered by bytes in flight in shared memory, not by
+//                   registers.  The halo outside the image is filled with NaN by the copy engine.
+//   8 compute warps pass 1: rewrite the tile in place, min(max(bf16(scale*x+shift), 0), 6) on packed bf16 pairs; max /
+//                   min return the non-NaN operand, so the NaN halo becomes 0 = the post-activation zero padding and
+//                   no thread ever computes where in the image its pixel lies; each input is transformed ONCE;
+//                   pass 2: a thread owns 4 channels and one output row segment (its geometry is a per-thread constant
+//                   of the whole kernel), a 3x3 window of packed fp32 pairs: 3 LDS.64 + 12 unpacks + 18 FFMA2 per
+//                   4-channel output, 8-byte stores (a half-warp writes one contiguous pixel), BatchNorm sums in
+//                   registers for the whole kernel.
 //
 // Channels are split into equal chunks of w <= 64 (144 -> 3 x 48, 960 -> 15 x 64); CTA b owns chunk b % nchunks for
-// its whole life (weights, scale/shift and sums stay in registers) and neighbouring CTAs work on the chunks of
-// the SAME tile at the same time, so the 128-byte lines of a pixel are fetched from HBM once (measured with
-// scripts/exp_tma_bw.cu: streaming one 64-channel chunk of a 144-channel tensor costs as much DRAM time as
-// streaming all of it).
+// its whole life (weights and sums stay in registers) and neighbouring CTAs work on the chunks of the SAME tile at the
+// same time, so the 128-byte lines of a pixel are fetched from HBM once (measured with scripts/exp_tma_bw.cu:
+// streaming one 64-channel chunk of a 144-channel tensor costs as much DRAM time as streaming all of it).
+// Stride 2: four parity planes of the input per tile (TMA element strides {1, 2, 2, 1}); every tap of every output
+// is then a plain (row, column) offset inside one plane; the chunk width is chosen per layer.
+// The BatchNorm of the producer can be finalised in the prologue (bn_inline.cuh): this kernel is its first consumer.
 //
 // The tensor-core formulation of the same conv (dw_tc.cu) is kept as an experiment: ~100-200 cycles per
-// tcgen05.mma make nine tap-shifted N=16 MMAs per 128 pixels slower than 36 FMAs per thread.
+// tcgen05.mma make nine tap-shifted N=16 MMAs per 128 pixels slower than 18 packed FMAs per thread.
 //
 // Reference behaviour replaced: cuDNN/ATen depthwise conv + cuDNN batch-norm + hardtanh as separate passes
 // (torchvision mobilenetv2.py ConvBNReLU; cifar10_mpi_mobilenet_224.py:177-179).
