@@ -598,6 +598,260 @@ dw_tile_bwd_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constan
 }
 
 
+// ---------------------------------------------------------------------------------------------------------------
+// Backward, stride 2.  A tile is Ht x Wt positions of the conv OUTPUT; it owns the 2Ht x 2Wt input pixels under it.
+// Boxes per tile: dz and d_raw {w, Wt+1, Ht+1, NI} at (x0, y0) -- the extra row / column is what odd input rows /
+// columns of the tile's last line reach -- and e_raw {w, 2Wt, 2Ht, NI} at (2x0, 2y0).
+// Input pixel (h, v) gets, with a = h/2, b = v/2:
+//   h even: ky = 1 from dd row a                      h odd: ky = 0 from dd row a+1, ky = 2 from dd row a
+//   v even: kx = 1 from dd col b                      v odd: kx = 0 from dd col b+1, kx = 2 from dd col b
+// A thread owns 4 channels and ONE input row (so the row parity, i.e. which taps exist, is a per-thread constant of the
+// whole kernel) and walks column PAIRS (2b, 2b+1) with a two-column window of dd.  "Row A" = dd row a with
+// ky = 1 (even rows) or 2 (odd rows); "row B" = dd row a+1 with ky = 0, weights zero on even rows.
+// Warps 0-7: data gradient + mask + sums; warps 8-15: weight gradient (12 accumulator pairs per thread).
+constexpr int DD_BYTES = 18 * 1024, E2_BYTES = 64 * 1024;
+static_assert(2 * DD_BYTES + E2_BYTES == BW_STAGE, "stride-2 backward uses the same stage size");
+
+__global__ void __launch_bounds__(BW_THREADS, 1)
+dw_tile_bwd2_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ CUtensorMap tmG,
+                    const __grid_constant__ CUtensorMap tmE, const __grid_constant__ DwTileParams P,
+                    const __grid_constant__ BnBwdSrc bsrc) {
+  pdl_trigger();
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + BW_NST * BW_STAGE);
+  uint64_t* empty = full + BW_NST;
+  float* s_stats = reinterpret_cast<float*>(empty + BW_NST);     // [2][64]
+  float* s_ecoef = s_stats + 128;                                 // [2][64]
+  float* s_dcoef = s_ecoef + 128;                                 // [3][64]
+  float* s_dw = s_dcoef + 192;                                    // [9][64]
+
+  const int lane = threadIdx.x & 31;
+  const int w = P.w, rowbytes = 2 * w;
+  const int chunk = (int)blockIdx.x % P.nchunks, c0 = chunk * w;
+  const int tile0 = (int)blockIdx.x / P.nchunks, tstep = (int)gridDim.x / P.nchunks;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < BW_NST; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], BW_THREADS / 32);
+    }
+    fence_barrier_init();
+  }
+  for (int i = threadIdx.x; i < 128 + 9 * 64; i += BW_THREADS) (i < 128 ? s_stats[i] : s_dw[i - 128]) = 0.f;
+  pdl_wait();
+  if (threadIdx.x < w) {
+    s_ecoef[threadIdx.x] = P.scale[c0 + threadIdx.x];
+    s_ecoef[64 + threadIdx.x] = P.shift[c0 + threadIdx.x];
+    float ca, cb, cc;
+    if (bsrc.sums != nullptr) {
+      bn_bwd_channel(bsrc, c0 + threadIdx.x, tile0 == 0, ca, cb, cc);
+    } else {
+      ca = P.dcoef[c0 + threadIdx.x];
+      cb = P.dcoef[P.C + c0 + threadIdx.x];
+      cc = P.dcoef[2 * P.C + c0 + threadIdx.x];
+    }
+    s_dcoef[threadIdx.x] = ca;
+    s_dcoef[64 + threadIdx.x] = cb;
+    s_dcoef[128 + threadIdx.x] = cc;
+  }
+  __syncthreads();
+
+  const uint32_t dd_bytes = (uint32_t)(P.NI * P.Hp * P.Wp * rowbytes);          // Hp = Ht + 1, Wp = Wt + 1 (+ pad)
+  const uint32_t e_bytes = (uint32_t)(P.NI * 2 * P.Ht * P.Wq * rowbytes);        // Wq = 2 Wt (+ pad)
+  auto issue = [&](int tile, int stage) {
+    int n0, y0, x0;
+    decode_tile(P, tile, n0, y0, x0);
+    uint8_t* st = base + stage * BW_STAGE;
+    mbar_arrive_expect_tx(&full[stage], 2 * dd_bytes + e_bytes);
+    tma_load_4d(st, &tmZ, &full[stage], c0, x0, y0, n0);
+    tma_load_4d(st + DD_BYTES, &tmG, &full[stage], c0, x0, y0, n0);
+    tma_load_4d(st + 2 * DD_BYTES, &tmE, &full[stage], c0, 2 * x0, 2 * y0, n0);
+  };
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmZ); prefetch_tmap(&tmG); prefetch_tmap(&tmE);
+    for (int k = 0; k < BW_NST; ++k)
+      if (tile0 + k * tstep < P.ntiles) issue(tile0 + k * tstep, k);
+  }
+
+  const bool grp_b = threadIdx.x >= BW_GROUP;
+  const int t = threadIdx.x - (grp_b ? BW_GROUP : 0);
+  const int Q = w >> 2;
+  const int j = t % Q, sidx = t / Q;
+  const int cq = c0 + 4 * j;
+  // my strip: image, INPUT row hh of the tile (0 .. 2Ht-1), first column pair
+  int st_img, st_hh, st_bs;
+  {
+    const int q1 = fastdiv(sidx, P.magic_nseg, P.NSEG);
+    st_bs = (sidx - q1 * P.NSEG) * P.SL;
+    st_img = fastdiv(q1, P.magic_ht, 2 * P.Ht);                  // magic_ht is the magic of 2*Ht here
+    st_hh = q1 - st_img * 2 * P.Ht;
+  }
+  const bool active = sidx < P.nstrips;
+  const int st_be = min(st_bs + P.SL, P.Wt);
+  const int ph = st_hh & 1, ra = st_hh >> 1;                      // row parity, dd row "A"
+  const int kyA = ph ? 2 : 1;                                     // tap row served by dd row A; row B serves ky = 0
+  const uint32_t dd_off = ((st_img * P.Hp + ra) * P.Wp + st_bs) * rowbytes + (j << 3);
+  const uint32_t e_off = 2 * DD_BYTES + ((st_img * 2 * P.Ht + st_hh) * P.Wq + 2 * st_bs) * rowbytes + (j << 3);
+  const uint32_t rpitch = P.Wp * rowbytes;
+  const size_t ystep = (size_t)P.C * 2;
+  // group A: weights of rows A / B by kx; group B: the matching weight-gradient accumulators
+  f2 wA[3][2], wB[3][2];
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx) {
+    float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
+    if (!grp_b && active) {
+      va = *reinterpret_cast<const float4*>(P.wts + (kyA * 3 + kx) * P.C + cq);
+      if (ph) vb = *reinterpret_cast<const float4*>(P.wts + kx * P.C + cq);
+    }
+    wA[kx][0] = f2_make(va.x, va.y); wA[kx][1] = f2_make(va.z, va.w);
+    wB[kx][0] = f2_make(vb.x, vb.y); wB[kx][1] = f2_make(vb.z, vb.w);
+  }
+  f2 s0[2], s1[2];
+  s0[0] = s0[1] = s1[0] = s1[1] = 0ull;
+  const f2 esc[2] = {f2_make(s_ecoef[4 * j], s_ecoef[4 * j + 1]), f2_make(s_ecoef[4 * j + 2], s_ecoef[4 * j + 3])};
+  const f2 esh[2] = {f2_make(s_ecoef[64 + 4 * j], s_ecoef[64 + 4 * j + 1]),
+                     f2_make(s_ecoef[64 + 4 * j + 2], s_ecoef[64 + 4 * j + 3])};
+  const int U = w >> 3;
+  const int uj = threadIdx.x % U, ur0 = threadIdx.x / U, urstep = BW_THREADS / U;
+  const bool xf_active = ur0 < urstep;
+  const uint32_t xf_off = ur0 * rowbytes + (uj << 4), xf_step = urstep * rowbytes;
+  const uint32_t dc_addr = smem_u32(s_dcoef) + 32 * uj;
+
+  int it = 0;
+#pragma unroll 1
+  for (int tile = tile0; tile < P.ntiles; tile += tstep, ++it) {
+    const int stage = it % BW_NST, par = (it / BW_NST) & 1;
+    int n0, y0, x0;
+    decode_tile(P, tile, n0, y0, x0);
+    const uint32_t sbase = smem_u32(base + stage * BW_STAGE);
+    mbar_wait(&full[stage], par);
+    // ---- pass 1: dd = ca*dz + cb*d_raw + cc, in place of dz; NaN (outside the image) -> 0
+    if (xf_active) {
+      const uint4 ka0 = lds16(dc_addr), ka1 = lds16(dc_addr + 16);
+      const uint4 kb0 = lds16(dc_addr + 256), kb1 = lds16(dc_addr + 272);
+      const uint4 kc0 = lds16(dc_addr + 512), kc1 = lds16(dc_addr + 528);
+      const f2 ca[4] = {f2_pair(ka0.x, ka0.y), f2_pair(ka0.z, ka0.w), f2_pair(ka1.x, ka1.y), f2_pair(ka1.z, ka1.w)};
+      const f2 cb[4] = {f2_pair(kb0.x, kb0.y), f2_pair(kb0.z, kb0.w), f2_pair(kb1.x, kb1.y), f2_pair(kb1.z, kb1.w)};
+      const f2 cc[4] = {f2_pair(kc0.x, kc0.y), f2_pair(kc0.z, kc0.w), f2_pair(kc1.x, kc1.y), f2_pair(kc1.z, kc1.w)};
+#pragma unroll 2
+      for (uint32_t o = xf_off; o < dd_bytes; o += xf_step) {
+        const uint4 z = lds16(sbase + o), g = lds16(sbase + DD_BYTES + o);
+        uint4 v;
+        v.x = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[0], f2_from_bf16x2(z.x), f2_fma(cb[0], f2_from_bf16x2(g.x), cc[0]))));
+        v.y = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[1], f2_from_bf16x2(z.y), f2_fma(cb[1], f2_from_bf16x2(g.y), cc[1]))));
+        v.z = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[2], f2_from_bf16x2(z.z), f2_fma(cb[2], f2_from_bf16x2(g.z), cc[2]))));
+        v.w = bf16x2_nan0(f2_to_bf16x2(f2_fma(ca[3], f2_from_bf16x2(z.w), f2_fma(cb[3], f2_from_bf16x2(g.w), cc[3]))));
+        sts16(sbase + o, v);
+      }
+    }
+    named_bar_sync(1, BW_THREADS);
+    // ---- pass 2: my input row, column pairs [st_bs, be)
+    const int h = 2 * y0 + st_hh, on = n0 + st_img;
+    const int vcol0 = 2 * (x0 + st_bs);                             // first input column of my strip
+    const int be = min(st_be, (P.W - 2 * x0 + 1) >> 1);
+    if (active && h < P.H && on < P.B && st_bs < be) {
+      uint32_t aA = sbase + dd_off, aB = aA + rpitch, ae = sbase + e_off;
+      f2 cA[2], cB[2], nA[2], nB[2];
+      auto load_dd = [&](f2 (&xa)[2], f2 (&xb)[2]) {
+        const uint2 va = lds8(aA), vb = lds8(aB);
+        aA += rowbytes; aB += rowbytes;
+        xa[0] = f2_from_bf16x2(va.x); xa[1] = f2_from_bf16x2(va.y);
+        xb[0] = f2_from_bf16x2(vb.x); xb[1] = f2_from_bf16x2(vb.y);
+      };
+      load_dd(cA, cB);
+      int v = vcol0;
+      if (!grp_b) {
+        char* yp = reinterpret_cast<char*>(P.y + (((size_t)on * P.H + h) * P.W + vcol0) * P.C + cq);
+        // mask with ReLU6' of the input activation, accumulate the sums, store one pixel
+        auto finish = [&](const uint2 ev, const f2 (&acc)[2], char* dst) {
+          uint2 o;
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            const f2 e = f2_from_bf16x2(hf == 0 ? ev.x : ev.y);
+            const f2 z = f2_fma(e, esc[hf], esh[hf]);
+            float alo, ahi, zlo, zhi;
+            f2_split(acc[hf], alo, ahi);
+            f2_split(z, zlo, zhi);
+            alo = (zlo > 0.f && zlo < 6.f) ? alo : 0.f;
+            ahi = (zhi > 0.f && zhi < 6.f) ? ahi : 0.f;
+            const f2 m = f2_make(alo, ahi);
+            s0[hf] = f2_add(s0[hf], m);
+            s1[hf] = f2_fma(m, e, s1[hf]);
+            (hf == 0 ? o.x : o.y) = f2_to_bf16x2(m);
+          }
+          *reinterpret_cast<uint2*>(dst) = o;
+        };
+#pragma unroll 1
+        for (int b = st_bs; b < be; ++b, v += 2) {
+          load_dd(nA, nB);
+          const uint2 e0 = lds8(ae), e1 = lds8(ae + rowbytes);
+          ae += 2 * rowbytes;
+          f2 d0[2], d1[2];
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            d0[hf] = f2_fma(wB[1][hf], cB[hf], f2_fma(wA[1][hf], cA[hf], 0ull));
+            d1[hf] = f2_fma(wA[0][hf], nA[hf], f2_fma(wA[2][hf], cA[hf], 0ull));
+            d1[hf] = f2_fma(wB[0][hf], nB[hf], f2_fma(wB[2][hf], cB[hf], d1[hf]));
+          }
+          finish(e0, d0, yp);
+          if (v + 1 < P.W) finish(e1, d1, yp + ystep);
+          yp += 2 * ystep;
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) { cA[hf] = nA[hf]; cB[hf] = nB[hf]; }
+        }
+      } else {
+        // wA / wB are the weight-gradient accumulators of rows A / B here
+#pragma unroll 1
+        for (int b = st_bs; b < be; ++b, v += 2) {
+          load_dd(nA, nB);
+          const uint2 e0 = lds8(ae), e1 = lds8(ae + rowbytes);   // a pixel outside the image is NaN -> activation 0
+          ae += 2 * rowbytes;
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            const f2 a0 = f2_from_bf16x2(bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(hf == 0 ? e0.x : e0.y), esc[hf], esh[hf]))));
+            const f2 a1 = f2_from_bf16x2(bf16x2_relu6(f2_to_bf16x2(f2_fma(f2_from_bf16x2(hf == 0 ? e1.x : e1.y), esc[hf], esh[hf]))));
+            wA[1][hf] = f2_fma(a0, cA[hf], wA[1][hf]);
+            wA[0][hf] = f2_fma(a1, nA[hf], wA[0][hf]);
+            wA[2][hf] = f2_fma(a1, cA[hf], wA[2][hf]);
+            wB[1][hf] = f2_fma(a0, cB[hf], wB[1][hf]);
+            wB[0][hf] = f2_fma(a1, nB[hf], wB[0][hf]);
+            wB[2][hf] = f2_fma(a1, cB[hf], wB[2][hf]);
+            cA[hf] = nA[hf]; cB[hf] = nB[hf];
+          }
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[stage]);
+    if (threadIdx.x == 0 && tile + BW_NST * tstep < P.ntiles) {
+      mbar_wait(&empty[stage], par);
+      issue(tile + BW_NST * tstep, stage);
+    }
+  }
+  if (active) {
+    if (!grp_b) {
+      const uint32_t sa = smem_u32(s_stats) + 16 * j;
+      red_shared_f2(sa, s0[0]); red_shared_f2(sa + 8, s0[1]);
+      red_shared_f2(sa + 256, s1[0]); red_shared_f2(sa + 264, s1[1]);
+    } else {
+      const uint32_t sa = smem_u32(s_dw) + 16 * j;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        red_shared_f2(sa + 256 * (kyA * 3 + kx), wA[kx][0]); red_shared_f2(sa + 256 * (kyA * 3 + kx) + 8, wA[kx][1]);
+        if (ph) { red_shared_f2(sa + 256 * kx, wB[kx][0]); red_shared_f2(sa + 256 * kx + 8, wB[kx][1]); }
+      }
+    }
+  }
+  named_bar_sync(1, BW_THREADS);
+  for (int i = threadIdx.x; i < 11 * w; i += BW_THREADS) {
+    const int hh = i / w, c = i - hh * w;
+    if (hh < 2) atomicAdd(P.stats + hh * P.stats_stride + c0 + c, s_stats[hh * 64 + c]);
+    else atomicAdd(P.dwg + (hh - 2) * P.C + c0 + c, s_dw[(hh - 2) * 64 + c]);
+  }
+}
+
 uint32_t magic(int d) { return (uint32_t)(((1ull << 32) + (uint64_t)d - 1) / (uint64_t)d); }
 
 int encode_nhwc(CUtensorMap* out, const void* base, int B, int H, int W, int C, int box_c, int box_w, int box_h, int box_n,
@@ -788,6 +1042,92 @@ int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshi
   return B200DP_OK;
 }
 
+// stride-2 backward: tile of the conv output, strips = input rows x column-pair segments
+static double pick_tile_bwd2(DwTileParams& P) {
+  const int Q = P.w / 4, rowbytes = 2 * P.w;
+  P.par = BW_GROUP / Q;
+  double best = -1.0;
+  const int wcand[4] = {P.Wo < 28 ? P.Wo : 28, 21, 14, 7};
+  for (int wi = 0; wi < 4; ++wi) {
+    const int Wt = wcand[wi];
+    if (Wt > P.Wo || (wi > 0 && Wt >= wcand[0])) continue;
+    int Wp = Wt + 1, Wq = 2 * Wt;
+    if (P.w < 64) { if (Wp % 2 == 0) ++Wp; ++Wq; }          // odd pitches for rows narrower than 128 bytes
+    for (int Ht = 1; Ht <= P.Ho && Ht <= 16; ++Ht)
+      for (int NI = 1; NI <= 4 && NI <= P.B; ++NI) {
+        const int Hp = Ht + 1;
+        if (NI * Hp * Wp * rowbytes > DD_BYTES || NI * 2 * Ht * Wq * rowbytes > E2_BYTES) continue;
+        for (int NSEG = 1; NSEG <= 4; ++NSEG) {
+          const int SL = (Wt + NSEG - 1) / NSEG;
+          if (SL < 3 && NSEG > 1) continue;
+          const int strips = NI * 2 * Ht * NSEG;
+          if (strips > P.par) continue;
+          const double util = (double)strips / P.par * ((double)Wt / (NSEG * SL));
+          const double halo = (double)(Ht * Wt) / (Hp * Wp);
+          const double prol = (double)SL / (SL + 0.5);
+          const int tx = (P.Wo + Wt - 1) / Wt, ty = (P.Ho + Ht - 1) / Ht, tn = (P.B + NI - 1) / NI;
+          const double edge = ((double)P.Wo / (tx * Wt)) * ((double)P.Ho / (ty * Ht)) * ((double)P.B / (tn * NI));
+          const double size = NI * 2 * Ht * Wq * rowbytes >= 16384 ? 1.0 : 0.9;
+          const double score = util * (0.7 + 0.3 * halo) * (0.8 + 0.2 * prol) * edge * size;
+          if (score > best) {
+            best = score;
+            P.Wt = Wt; P.Ht = Ht; P.NI = NI; P.Hp = Hp; P.Wp = Wp; P.Wq = Wq; P.NSEG = NSEG; P.SL = SL;
+          }
+        }
+      }
+  }
+  P.nstrips = P.NI * 2 * P.Ht * P.NSEG;
+  P.tiles_x = (P.Wo + P.Wt - 1) / P.Wt;
+  P.tiles_y = (P.Ho + P.Ht - 1) / P.Ht;
+  P.ntiles = P.tiles_x * P.tiles_y * ((P.B + P.NI - 1) / P.NI);
+  return best;
+}
+
+bool dw_tile_bwd_supported(int B, int H, int W, int C, int stride) {
+  return (stride == 1 || stride == 2) && chunk_width(C) > 0 && B >= 1 && H >= 1 && W >= 1 && H < 4096 && W < 4096;
+}
+
+int dw_tile_bwd2_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
+                        const float* dcoef, const float* wts, void* dze, float* stats, int stats_stride, float* dw, int B,
+                        int H, int W, int C, cudaStream_t s, const BnBwdSrc* src) {
+  B200DP_REQUIRE(dw_tile_bwd_supported(B, H, W, C, 2), "dw_tile_bwd2: B=%d H=%d W=%d C=%d unsupported", B, H, W, C);
+  B200DP_REQUIRE(stats != nullptr && dw != nullptr, "dw_tile_bwd2: stats / dw missing");
+  DwTileParams P{};
+  P.scale = escale; P.shift = eshift; P.wts = wts; P.y = static_cast<__nv_bfloat16*>(dze);
+  P.stats = stats; P.stats_stride = stats_stride; P.dcoef = dcoef; P.dwg = dw;
+  P.B = B; P.H = H; P.W = W; P.C = C;
+  P.S = 2; P.Ho = (H - 1) / 2 + 1; P.Wo = (W - 1) / 2 + 1;
+  DwTileParams best = P;
+  double best_score = -1.0;
+  for (int w = 64; w >= 16; w -= 16) {
+    if (C % w != 0) continue;
+    DwTileParams T = P;
+    T.w = T.wbox = w;
+    const double row_eff = w >= 64 ? 1.0 : (w >= 48 ? 0.97 : (w >= 32 ? 0.92 : 0.75));
+    const double sc = pick_tile_bwd2(T) * row_eff;
+    if (sc > best_score) { best_score = sc; best = T; }
+  }
+  B200DP_REQUIRE(best_score > 0.0, "dw_tile_bwd2: no tile fits (C=%d)", C);
+  P = best;
+  P.nchunks = C / P.w;
+  P.magic_wp = magic(P.Wp); P.magic_hp = magic(P.Hp); P.magic_tx = magic(P.tiles_x); P.magic_ty = magic(P.tiles_y);
+  P.magic_nseg = magic(P.NSEG); P.magic_ht = magic(2 * P.Ht);
+  CUtensorMap tmZ, tmG, tmE;
+  if (int rc = encode_nhwc(&tmZ, dzd, B, P.Ho, P.Wo, C, P.w, P.Wp, P.Hp, P.NI)) return rc;
+  if (int rc = encode_nhwc(&tmG, d_raw, B, P.Ho, P.Wo, C, P.w, P.Wp, P.Hp, P.NI)) return rc;
+  if (int rc = encode_nhwc(&tmE, e_raw, B, H, W, C, P.w, P.Wq, 2 * P.Ht, P.NI)) return rc;
+  int groups = num_sms() / P.nchunks;
+  if (groups < 1) groups = 1;
+  if (groups > P.ntiles) groups = P.ntiles;
+  const int grid = groups * P.nchunks;
+  const size_t smem = 128 + BW_NST * BW_STAGE + 2 * BW_NST * 8 + (128 + 128 + 192 + 576) * 4;
+  B200DP_CUDA(cudaFuncSetAttribute(dw_tile_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  B200DP_CUDA(launch_k(dw_tile_bwd2_kernel, dim3((unsigned)grid), dim3(BW_THREADS), smem, s, tmZ, tmG, tmE, P,
+                       src ? *src : BnBwdSrc{}));
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
 }  // namespace b200dp
 
 using namespace b200dp;
@@ -801,7 +1141,9 @@ extern "C" int b200dp_dw_fwd_tile(const void* x, const float* scale, const float
 extern "C" int b200dp_dw_bwd_tile(const void* e_raw, const float* escale, const float* eshift, const void* dzd,
                                   const void* d_raw, const float* dcoef, const float* w, void* dze, float* stats,
                                   int stats_stride, float* dw, int B, int H, int W, int C, int stride, void* stream) {
-  B200DP_REQUIRE(stride == 1, "dw_bwd_tile: stride 1 only");
+  if (stride == 2)
+    return dw_tile_bwd2_launch(e_raw, escale, eshift, dzd, d_raw, dcoef, w, dze, stats, stats_stride, dw, B, H, W, C,
+                               static_cast<cudaStream_t>(stream), nullptr);
   return dw_tile_bwd_launch(e_raw, escale, eshift, dzd, d_raw, dcoef, w, dze, stats, stats_stride, dw, B, H, W, C,
                             static_cast<cudaStream_t>(stream), nullptr);
 }

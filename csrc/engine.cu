@@ -455,6 +455,10 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       ENG_TRY(dw_tile_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
                                  e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
                                  cd.hin, cd.coutp, s, fuse ? &cd_src : nullptr));
+    else if (e.dw_tiled && cd.stride == 2 && dw_tile_bwd_supported(n, cd.hin, cd.hin, cd.coutp, 2))
+      ENG_TRY(dw_tile_bwd2_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
+                                  e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                                  cd.hin, cd.coutp, s, fuse ? &cd_src : nullptr));
     else
       ENG_TRY(dw_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
                             e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,

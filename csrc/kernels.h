@@ -28,6 +28,10 @@ int dw_tile_fwd_launch(const void* x, const float* scale, const float* shift, co
 int dw_tile_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
                        const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
                        int H, int W, int C, cudaStream_t s, const BnBwdSrc* src = nullptr);
+bool dw_tile_bwd_supported(int B, int H, int W, int C, int stride);
+int dw_tile_bwd2_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
+                        const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
+                        int H, int W, int C, cudaStream_t s, const BnBwdSrc* src = nullptr);
 // stem.cu
 int stem_fwd_launch(const void* x, const float* w, void* y, float* stats, int stats_stride, int B, int H, int W,
                     cudaStream_t s);

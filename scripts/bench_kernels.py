@@ -156,6 +156,14 @@ cases = {
     "dw_fwd_s2_tile_56_144": lambda: dw_fwd(56, 144, 2, "tile"),
     "dw_fwd_s2_tile_28_192": lambda: dw_fwd(28, 192, 2, "tile"),
     "dw_fwd_s2_tile_14_576": lambda: dw_fwd(14, 576, 2, "tile"),
+    "dw_bwd_s2_simt_112_96": lambda: dw_bwd(112, 96, 2, "simt"),
+    "dw_bwd_s2_simt_56_144": lambda: dw_bwd(56, 144, 2, "simt"),
+    "dw_bwd_s2_simt_28_192": lambda: dw_bwd(28, 192, 2, "simt"),
+    "dw_bwd_s2_simt_14_576": lambda: dw_bwd(14, 576, 2, "simt"),
+    "dw_bwd_s2_tile_112_96": lambda: dw_bwd(112, 96, 2, "tile"),
+    "dw_bwd_s2_tile_56_144": lambda: dw_bwd(56, 144, 2, "tile"),
+    "dw_bwd_s2_tile_28_192": lambda: dw_bwd(28, 192, 2, "tile"),
+    "dw_bwd_s2_tile_14_576": lambda: dw_bwd(14, 576, 2, "tile"),
     "dw_bwd_56_144_s1": lambda: dw_bwd(56, 144, 1),
     "dw_bwd_112_96_s2": lambda: dw_bwd(112, 96, 2),
     "dw_bwd_14_384_s1": lambda: dw_bwd(14, 384, 1),

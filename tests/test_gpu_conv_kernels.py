@@ -45,10 +45,8 @@ def test_dw_fwd(ops, B, H, C, stride, impl):
 @pytest.mark.parametrize("impl", ["simt", "tile"])
 @pytest.mark.parametrize("B,H,C,stride", [(4, 28, 192, 1), (3, 56, 96, 2), (2, 14, 576, 1), (3, 7, 960, 1),
                                           (2, 112, 32, 1), (3, 15, 144, 2), (70, 14, 384, 1), (2, 56, 144, 1),
-                                          (5, 7, 960, 1)])
+                                          (5, 7, 960, 1), (2, 112, 96, 2), (3, 28, 192, 2), (4, 14, 576, 2), (2, 56, 144, 2)])
 def test_dw_bwd(ops, B, H, C, stride, impl):
-    if impl == "tile" and stride != 1:
-        pytest.skip("the tiled kernel is stride 1 only")
     torch.manual_seed(C + H + 1)
     Ho = (H - 1) // stride + 1
     e_raw = _bf(torch.randn(B, H, H, C, device="cuda") * 2)
