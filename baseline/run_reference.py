@@ -32,9 +32,19 @@ class _Done(BaseException):
 
 
 def main(ns) -> dict:
-    script = os.path.join(REF, "cifar10_128batch.py" if ns.gpus == 1 else "cifar10_mpi_mobilenet_224.py")
-    if not os.path.isfile(script):
-        return {"impl": "reference", "unavailable": "baseline/_ref is empty (run baseline/install_reference.py where /root/reference exists)"}
+    # baseline/_ref is git-ignored; on a box where build() has not run, materialise the same bytes from the
+    # mount or the bundled archive into a private directory (one per process: ranks must not race on files).
+    sys.path.insert(0, HERE)
+    import install_reference
+    ref = REF
+    if not install_reference.installed(ref):
+        ref = tempfile.mkdtemp(prefix="b200dp_refsrc_")
+        try:
+            if install_reference.main(ref, quiet=True) != 0:
+                return {"impl": "reference", "unavailable": "no reference scripts: baseline/_ref, /root/reference and baseline/reference_scripts.tar.gz all absent"}
+        except Exception as e:
+            return {"impl": "reference", "unavailable": f"reference install failed: {e}"}
+    script = os.path.join(ref, "cifar10_128batch.py" if ns.gpus == 1 else "cifar10_mpi_mobilenet_224.py")
     try:
         import torch
         import torchvision
