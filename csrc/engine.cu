@@ -83,7 +83,10 @@ struct Engine {
   int stem_pack = 1;
   __nv_bfloat16 *x0col = nullptr, *stem_w = nullptr;
   float *stem_asum = nullptr, *stem_dw = nullptr;
-  __nv_bfloat16 *dzd = nullptr, *dze = nullptr, *dp = nullptr, *gx[2] = {nullptr, nullptr}, *dout[2] = {nullptr, nullptr};
+  // dze / dp are double-buffered: the weight-gradient kernels that read them run on side branches of the step graph
+  // and may still be busy when the main chain produces the next block's tensors
+  __nv_bfloat16 *dzd = nullptr, *dze[2] = {nullptr, nullptr}, *dp[2] = {nullptr, nullptr}, *gx[2] = {nullptr, nullptr},
+                *dout[2] = {nullptr, nullptr};
   float *sums_all = nullptr;
   size_t sums_bytes = 0;
   float *pooled = nullptr, *drop = nullptr, *logits = nullptr, *dlogits = nullptr, *dpool = nullptr;
@@ -96,6 +99,19 @@ struct Engine {
   bool pw_pack = true;      // row packing of narrow pointwise layers (B200DP_PW_PACK=0: off)
   bool dw_tiled = true;     // stride-1 depthwise convs on the TMA-tiled kernels (B200DP_DW_IMPL=simt: sliding-window kernels)
   cudaStream_t cap_stream = nullptr;   // graphs are captured here (the caller's stream may be the legacy default stream)
+  // fork / join inside a step (B200DP_FORK=0: one linear chain).  side[0]: project-conv weight gradients,
+  // side[1]: expand-conv / last-conv / stem weight gradients, side[2]: gradient all-reduce + Adam per bucket
+  // Measured (1x B200, batch 128): forking the weight gradients is SLOWER at every threshold -- 5.09 ms/step with none,
+  // 5.10 / 5.14 / 5.18 with the blocks up to 7 / 14 / 28 rows tall forked, 5.19 with all.  Every kernel here is sized to
+  // fill the machine on its own, so a concurrent branch only takes SMs, TMEM columns and L2 away from the critical
+  // path.  The weight-gradient fork is therefore opt-in (B200DP_FORK_WGRAD=1, B200DP_FORK_MAXH=<rows>); the forward
+  // weight-preparation fork and the communication branch, which do not compete with anything, are always on.
+  bool fork = true;
+  bool fork_wgrad = false;
+  int fork_max_h = 14;       // only blocks whose input is at most this tall fork their weight gradients
+  cudaStream_t side[3] = {nullptr, nullptr, nullptr};
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_next = 0;
   bool eval_coef_valid = false;
   std::map<int, Plans> plans;
   // profiling
@@ -199,9 +215,9 @@ size_t layout_workspace(Engine& e, char* base) {
     max_x = ein > max_x ? ein : max_x;
   }
   e.dzd = carve<__nv_bfloat16>(p, max_d);
-  e.dze = carve<__nv_bfloat16>(p, max_e);
-  e.dp = carve<__nv_bfloat16>(p, max_x);
   for (int i = 0; i < 2; ++i) {
+    e.dze[i] = carve<__nv_bfloat16>(p, max_e);
+    e.dp[i] = carve<__nv_bfloat16>(p, max_x);
     e.gx[i] = carve<__nv_bfloat16>(p, max_x);
     e.dout[i] = carve<__nv_bfloat16>(p, max_x);
   }
@@ -247,6 +263,10 @@ BnBwdSrc src_b(const Engine& e, const Conv& c, float count) {
   return b;
 }
 
+// Which copy of dze / dp a block uses: consecutive blocks alternate, the head (index = number of blocks) writes dze[0].
+inline int dze_idx(const Engine& e, int bi) { return ((int)e.blocks.size() - bi) & 1; }
+inline int dp_idx(int bi) { return bi & 1; }
+
 int build_plans(Engine& e, Plans& pl, int n) {
   pl.n = n;
   const int nc = (int)e.convs.size();
@@ -278,8 +298,10 @@ int build_plans(Engine& e, Plans& pl, int n) {
                              ce.cinp, xin, ce.cinp, nullptr, nullptr, nullptr, 0, wf(ce), ce.raw, ce.coutp,
                              nullptr, nullptr, ce.sums_f, ce.coutp, 0, ce.pack_f));
       // dgrad: dx[M, cin] = BNgrad(dze, e_raw)[M, hidden] * W[hidden, cin]   (weights transposed: [cin][hidden])
-      ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp, e.dze, ce.raw,
-                           ce.coef_b, 0, wd(ce), e.gx[0], ce.cinp, nullptr, nullptr, nullptr, 0, 0, ce.pack_d));
+      ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp,
+                           e.dze[dze_idx(e, b.index - 1)], ce.raw, ce.coef_b, 0, wd(ce), e.gx[0], ce.cinp, nullptr, nullptr,
+                           nullptr, 0, 0, ce.pack_d));
+      if (e.fork && e.fork_wgrad && e.bn_fuse) pl.dgrad[b.ce].gsrc = src_b(e, ce, (float)Min);
     }
     for (int ev = 0; ev < 2; ++ev)
       ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[b.cp] : &pl.fwd[b.cp], A_BNRELU, ev ? E_PLAIN : E_STATS, Mout, cp.coutp,
@@ -287,7 +309,7 @@ int build_plans(Engine& e, Plans& pl, int n) {
                            cp.coutp, nullptr, nullptr, cp.sums_f, cp.coutp, 0, cp.pack_f));
     if (e.bn_fuse) pl.fwd[b.cp].asrc = src_f(e, cd, (float)Mout);     // training plan only: eval reads running-stat coefficients
     // project dgrad: dzd[M, hidden] = mask(dp[M, cout] * W[cout, hidden])   (weights transposed: [hidden][cout])
-    ENG_TRY(pw_gemm_plan(&pl.dgrad[b.cp], A_TMA, E_MASKSTATS, Mout, cp.cinp, cp.coutp, e.dp, cp.coutp, nullptr, nullptr,
+    ENG_TRY(pw_gemm_plan(&pl.dgrad[b.cp], A_TMA, E_MASKSTATS, Mout, cp.cinp, cp.coutp, e.dp[dp_idx(b.index - 1)], cp.coutp, nullptr, nullptr,
                          nullptr, 0, wd(cp), e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, 0, cp.pack_d));
   }
   {
@@ -299,8 +321,9 @@ int build_plans(Engine& e, Plans& pl, int n) {
       ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[li] : &pl.fwd[li], A_TMA, ev ? E_PLAIN : E_STATS, M, cl.coutp, cl.cinp,
                            lb.xout, cl.cinp, nullptr, nullptr, nullptr, 0, e.w_bf16 + cl.off_w, cl.raw, cl.coutp, nullptr,
                            nullptr, cl.sums_f, cl.coutp, 0));
-    ENG_TRY(pw_gemm_plan(&pl.dgrad[li], A_BNGRAD, E_PLAIN, M, cl.cinp, cl.coutp, nullptr, cl.coutp, e.dze, cl.raw,
+    ENG_TRY(pw_gemm_plan(&pl.dgrad[li], A_BNGRAD, E_PLAIN, M, cl.cinp, cl.coutp, nullptr, cl.coutp, e.dze[0], cl.raw,
                          cl.coef_b, 0, e.wt_bf16 + cl.off_w, e.gx[0], cl.cinp, nullptr, nullptr, nullptr, 0, 0));
+    if (e.fork && e.fork_wgrad && e.bn_fuse) pl.dgrad[li].gsrc = src_b(e, cl, (float)M);
   }
   return B200DP_OK;
 }
@@ -320,9 +343,32 @@ int bn_fin_b(Engine& e, Conv& c, float count, cudaStream_t s) {
                                 e.grads + c.off_b, c.coutp, s);
 }
 
+// Fork / join helpers.  They work the same on real streams and under stream capture (where they become graph edges).
+cudaEvent_t next_event(Engine& e) {
+  if (e.ev_next == e.ev_pool.size()) {
+    cudaEvent_t ev;
+    cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    e.ev_pool.push_back(ev);
+  }
+  return e.ev_pool[e.ev_next++];
+}
+// everything enqueued on `from` so far happens before whatever is enqueued on `to` from now on
+int order_after(Engine& e, cudaStream_t from, cudaStream_t to) {
+  if (from == to) return B200DP_OK;
+  cudaEvent_t ev = next_event(e);
+  B200DP_CUDA(cudaEventRecord(ev, from));
+  B200DP_CUDA(cudaStreamWaitEvent(to, ev, 0));
+  return B200DP_OK;
+}
+
 int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t s) {
-  ENG_TRY(weight_prep_launch(e.params, e.w_bf16, e.wt_bf16, e.w_pack, e.wprep_dev, e.n_pw, s));
+  // the bf16 weight copies do not depend on the input, the preprocessing does not depend on the weights: two branches
+  e.ev_next = 0;
+  cudaStream_t sw = (e.fork && !e.profiling) ? e.side[0] : s;
+  ENG_TRY(order_after(e, s, sw));
+  ENG_TRY(weight_prep_launch(e.params, e.w_bf16, e.wt_bf16, e.w_pack, e.wprep_dev, e.n_pw, sw));
   mark(e, s, "weight_prep");
+  if (e.stem_gemm) ENG_TRY(stem_weight_prep_launch(e.params + e.convs[0].off_w, e.stem_w, e.stem_pack, sw));
   if (train) {
     B200DP_CUDA(cudaMemsetAsync(e.sums_all, 0, e.sums_bytes, s));
   } else if (!e.eval_coef_valid) {
@@ -335,11 +381,12 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
   mark(e, s, "preprocess");
   Conv& st = e.convs[0];
   if (e.stem_gemm) {
-    ENG_TRY(stem_weight_prep_launch(e.params + st.off_w, e.stem_w, e.stem_pack, s));
     ENG_TRY(stem_im2col_launch(e.x0, e.x0col, train ? e.stem_asum : nullptr, n, e.S, e.S, s));
     mark(e, s, "stem_im2col", 0);
+    ENG_TRY(order_after(e, sw, s));
     ENG_TRY(pw_gemm_launch(train ? pl.fwd[0] : pl.fwd_eval[0], s));
   } else {
+    ENG_TRY(order_after(e, sw, s));
     ENG_TRY(stem_fwd_launch(e.x0, e.params + st.off_w, st.raw, train ? st.sums_f : nullptr, st.coutp, n, e.S, e.S, s));
   }
   mark(e, s, "stem_fwd", 0);
@@ -398,12 +445,33 @@ __global__ void bump_step_kernel(int* step) {
   *step += 1;
 }
 
+// Backward pass.  The main chain is the data-gradient path (grad_join -> affine -> project dgrad -> depthwise backward
+// -> expand dgrad); the pointwise weight gradients only READ what that chain produces, so each is forked onto a side
+// branch right after its inputs exist and joined again when its input buffer is about to be overwritten (two blocks
+// later: dze / dp are double-buffered) or at the end of the step.
 int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
+  const bool forked = e.fork && e.fork_wgrad && !e.profiling;
+  cudaStream_t sp = forked ? e.side[0] : s;      // project-conv weight gradients
+  cudaStream_t se = forked ? e.side[1] : s;      // expand / last / stem weight gradients
+  cudaStream_t const sp_side = sp, se_side = se;
+  bool sp_used = false, se_used = false;
+  cudaEvent_t dze_free[2] = {nullptr, nullptr}, dp_free[2] = {nullptr, nullptr};   // last side-branch reader done
+  auto wait_free = [&](cudaEvent_t& ev) -> int {
+    if (ev != nullptr) B200DP_CUDA(cudaStreamWaitEvent(s, ev, 0));
+    ev = nullptr;
+    return B200DP_OK;
+  };
+  auto mark_free = [&](cudaEvent_t& ev, cudaStream_t side) -> int {
+    if (side == s) return B200DP_OK;
+    ev = next_event(e);
+    B200DP_CUDA(cudaEventRecord(ev, side));
+    return B200DP_OK;
+  };
   const int li = (int)e.convs.size() - 1;
   Conv& cl = e.convs[li];
   const int HW = cl.hout * cl.hout;
   ENG_TRY(head_bwd_launch(e.dlogits, e.pooled, e.drop, e.params + e.off_fcw, e.dpool, e.grads + e.off_fcw,
-                          e.grads + e.off_fcb, cl.raw, cl.coef_f, e.dze, cl.sums_b, cl.coutp, n, HW, cl.coutp,
+                          e.grads + e.off_fcb, cl.raw, cl.coef_f, e.dze[0], cl.sums_b, cl.coutp, n, HW, cl.coutp,
                           e.classes, s));
   mark(e, s, "head_bwd");
   const bool fuse = e.bn_fuse;
@@ -411,9 +479,12 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
   Block& lb = e.blocks.back();
   const int Ml = n * HW;
   const BnBwdSrc cl_src = src_b(e, cl, (float)n * HW);
-  ENG_TRY(pw_wgrad_launch(0, Ml, cl.coutp, cl.cinp, lb.xout, cl.cinp, e.dze, cl.raw, cl.coutp, cl.coef_b, lb.xsum,
-                          e.grads + cl.off_w, cl.cinp, 0, s, 1, fuse ? &cl_src : nullptr));
+  ENG_TRY(order_after(e, s, se));
+  se_used |= se != s;
+  ENG_TRY(pw_wgrad_launch(0, Ml, cl.coutp, cl.cinp, lb.xout, cl.cinp, e.dze[0], cl.raw, cl.coutp, cl.coef_b, lb.xsum,
+                          e.grads + cl.off_w, cl.cinp, 0, se, 1, fuse ? &cl_src : nullptr));
   mark(e, s, "pw_wgrad_last", li);
+  ENG_TRY(mark_free(dze_free[0], se));
   int gxi = 0, doi = 0;
   ENG_TRY(retarget_out(pl.dgrad[li], e.gx[gxi]));
   ENG_TRY(pw_gemm_launch(pl.dgrad[li], s));
@@ -425,6 +496,12 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     Block& b = e.blocks[bi];
     Conv& cd = e.convs[b.cd];
     Conv& cp = e.convs[b.cp];
+    // the big early layers fill the machine on their own: a concurrent weight gradient only takes SMs and L2 away
+    // from the critical path there (measured), so they stay on the main chain
+    sp = b.hout <= e.fork_max_h ? sp_side : s;
+    se = b.hin <= e.fork_max_h ? se_side : s;
+    __nv_bfloat16* dp = e.dp[dp_idx(bi)];
+    __nv_bfloat16* dze = e.dze[dze_idx(e, bi)];
     const long long rows_out = (long long)n * b.hout * b.hout;
     // ---- gradient w.r.t. this block's output: consumer dgrad (+ residual path of the next block)
     const __nv_bfloat16* dcur = g1;
@@ -438,44 +515,52 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     mark(e, s, "grad_join", b.cp);
     if (!fuse) ENG_TRY(bn_fin_b(e, cp, (float)rows_out, s));
     const BnBwdSrc cp_src = src_b(e, cp, (float)rows_out);
-    ENG_TRY(affine_launch(dcur, cp.raw, cp.coef_b, 1, e.dp, rows_out, cp.coutp, s, fuse ? &cp_src : nullptr));
+    ENG_TRY(wait_free(dp_free[dp_idx(bi)]));
+    ENG_TRY(affine_launch(dcur, cp.raw, cp.coef_b, 1, dp, rows_out, cp.coutp, s, fuse ? &cp_src : nullptr));
     mark(e, s, "bn_bwd_apply", b.cp);
-    // ---- projection conv: weight gradient, then data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
-    ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, e.dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
-                            nullptr, e.grads + cp.off_w, cp.cinp, 0, s,
+    // ---- projection conv: weight gradient (side branch), data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
+    ENG_TRY(order_after(e, s, sp));
+    sp_used |= sp != s;
+    ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
+                            nullptr, e.grads + cp.off_w, cp.cinp, 0, sp,
                             e.pw_pack ? pw_wgrad_pick_pack(1, (int)rows_out, cp.coutp, cp.cinp) : 1));
     mark(e, s, "pw_wgrad_project", b.cp);
+    ENG_TRY(mark_free(dp_free[dp_idx(bi)], sp));
     ENG_TRY(pw_gemm_launch(pl.dgrad[b.cp], s));
     mark(e, s, "pw_dgrad_project", b.cp);
     if (!fuse) ENG_TRY(bn_fin_b(e, cd, (float)rows_out, s));
     // ---- depthwise conv backward (data + weight gradient, mask, statistics for the producer's BatchNorm)
     Conv& cin_raw = b.ce >= 0 ? e.convs[b.ce] : e.convs[0];
     const BnBwdSrc cd_src = src_b(e, cd, (float)rows_out);
+    ENG_TRY(wait_free(dze_free[dze_idx(e, bi)]));
     if (e.dw_tiled && dw_tile_supported(n, cd.hin, cd.hin, cd.coutp, cd.stride))
       ENG_TRY(dw_tile_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
-                                 e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                                 e.params + cd.off_w, dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
                                  cd.hin, cd.coutp, s, fuse ? &cd_src : nullptr));
     else if (e.dw_tiled && cd.stride == 2 && dw_tile_bwd_supported(n, cd.hin, cd.hin, cd.coutp, 2))
       ENG_TRY(dw_tile_bwd2_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
-                                  e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                                  e.params + cd.off_w, dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
                                   cd.hin, cd.coutp, s, fuse ? &cd_src : nullptr));
     else
       ENG_TRY(dw_bwd_launch(cin_raw.raw, cin_raw.coef_f, cin_raw.coef_f + cin_raw.coutp, e.dzd, cd.raw, cd.coef_b,
-                            e.params + cd.off_w, e.dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
+                            e.params + cd.off_w, dze, cin_raw.sums_b, cin_raw.coutp, e.grads + cd.off_w, n, cd.hin,
                             cd.hin, cd.coutp, cd.stride, s, fuse ? &cd_src : nullptr));
     mark(e, s, "dw_bwd", b.cd);
     const long long rows_in = (long long)n * b.hin * b.hin;
     const bool in_fused = fuse && (b.ce >= 0 || e.stem_gemm);      // the CUDA-core stem weight gradient reads the array
     if (!in_fused) ENG_TRY(bn_fin_b(e, cin_raw, (float)rows_in, s));
     const BnBwdSrc in_src = src_b(e, cin_raw, (float)rows_in);
+    ENG_TRY(order_after(e, s, se));
+    se_used |= se != s;
     if (b.ce >= 0) {
       Conv& ce = e.convs[b.ce];
       const __nv_bfloat16* xin = e.blocks[bi - 1].xout;
-      ENG_TRY(pw_wgrad_launch(0, (int)rows_in, ce.coutp, ce.cinp, xin, ce.cinp, e.dze, ce.raw, ce.coutp, ce.coef_b,
-                              e.blocks[bi - 1].xsum, e.grads + ce.off_w, ce.cinp, 0, s,
+      ENG_TRY(pw_wgrad_launch(0, (int)rows_in, ce.coutp, ce.cinp, xin, ce.cinp, dze, ce.raw, ce.coutp, ce.coef_b,
+                              e.blocks[bi - 1].xsum, e.grads + ce.off_w, ce.cinp, 0, se,
                               e.pw_pack ? pw_wgrad_pick_pack(0, (int)rows_in, ce.coutp, ce.cinp) : 1,
                               in_fused ? &in_src : nullptr));
       mark(e, s, "pw_wgrad_expand", b.ce);
+      ENG_TRY(mark_free(dze_free[dze_idx(e, bi)], se));
       gxi ^= 1;
       ENG_TRY(retarget_out(pl.dgrad[b.ce], e.gx[gxi]));
       ENG_TRY(pw_gemm_launch(pl.dgrad[b.ce], s));
@@ -487,15 +572,18 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       Conv& st = e.convs[0];
       if (e.stem_gemm) {
         const int M = n * st.hout * st.hout;
-        ENG_TRY(pw_wgrad_launch(0, M, 32, 32, e.x0col, 32, e.dze, st.raw, 32, st.coef_b, e.stem_asum, e.stem_dw, 32, 0, s,
+        ENG_TRY(pw_wgrad_launch(0, M, 32, 32, e.x0col, 32, dze, st.raw, 32, st.coef_b, e.stem_asum, e.stem_dw, 32, 0, se,
                                 pw_wgrad_pick_pack(0, M, 32, 32), in_fused ? &in_src : nullptr));
-        ENG_TRY(stem_dw_fold_launch(e.stem_dw, e.grads + st.off_w, s));
+        ENG_TRY(stem_dw_fold_launch(e.stem_dw, e.grads + st.off_w, se));
       } else {
-        ENG_TRY(stem_wgrad_launch(e.x0, e.dze, st.raw, st.coef_b, e.grads + st.off_w, n, e.S, e.S, s));
+        ENG_TRY(stem_wgrad_launch(e.x0, dze, st.raw, st.coef_b, e.grads + st.off_w, n, e.S, e.S, se));
       }
       mark(e, s, "stem_wgrad", 0);
     }
   }
+  // join the side branches: the step (and the capture) ends on the main stream
+  if (sp_used) ENG_TRY(order_after(e, sp_side, s));
+  if (se_used) ENG_TRY(order_after(e, se_side, s));
   B200DP_CUDA(launch_k(bump_step_kernel, dim3(1), dim3(1), 0, s, e.step_dev));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
@@ -549,6 +637,9 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   build_spec(*e, offsets);
   e->pw_pack = !(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0);
   e->bn_fuse = !(getenv("B200DP_BN_FUSE") != nullptr && atoi(getenv("B200DP_BN_FUSE")) == 0);
+  e->fork = !(getenv("B200DP_FORK") != nullptr && atoi(getenv("B200DP_FORK")) == 0);
+  e->fork_wgrad = getenv("B200DP_FORK_WGRAD") != nullptr && atoi(getenv("B200DP_FORK_WGRAD")) != 0;
+  if (getenv("B200DP_FORK_MAXH") != nullptr) e->fork_max_h = atoi(getenv("B200DP_FORK_MAXH"));
   {
     const char* st = getenv("B200DP_STEM");
     e->stem_gemm = !(st != nullptr && std::string(st) == "simt");
@@ -579,6 +670,7 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   e->n_pw = (int)table.size();
   B200DP_CUDA(cudaMemcpy(e->wprep_dev, table.data(), table.size() * sizeof(WPrepEntry), cudaMemcpyHostToDevice));
   B200DP_CUDA(cudaStreamCreateWithFlags(&e->cap_stream, cudaStreamNonBlocking));
+  for (auto& st : e->side) B200DP_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   B200DP_CUDA(cudaDeviceSynchronize());
   *out = e;
   return B200DP_OK;
@@ -593,6 +685,8 @@ int b200dp_engine_destroy(void* h) {
     if (kv.second.eval_graph) cudaGraphExecDestroy(kv.second.eval_graph);
   }
   if (e->cap_stream) cudaStreamDestroy(e->cap_stream);
+  for (auto& st : e->side) if (st) cudaStreamDestroy(st);
+  for (auto ev : e->ev_pool) cudaEventDestroy(ev);
   if (e->ws) cudaFree(e->ws);
   delete e;
   return B200DP_OK;

@@ -90,7 +90,8 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ CUtensorMap tmAt, const __grid_constant__ CUtensorMap tmBt,
                const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmA2t,
                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmX,
-               const __grid_constant__ PwGemmParams P, const __grid_constant__ BnFwdSrc asrc) {
+               const __grid_constant__ PwGemmParams P, const __grid_constant__ BnFwdSrc asrc,
+               const __grid_constant__ BnBwdSrc gsrc) {
   using L = Layout<AMODE>;
   constexpr int NG = L::kEpiGroups;
   auto stamp = [&](int slot) {
@@ -172,6 +173,16 @@ pw_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       bn_fwd_channel(asrc, c % P.k_true, blockIdx.x == 0 && c < P.k_true, sc, sh);
       s_acoef[c] = sc;
       s_acoef[P.K + c] = sh;
+    }
+  } else if (AMODE == A_BNGRAD && gsrc.sums != nullptr) {
+    // BatchNorm-backward coefficients straight from the producer's sums, with NO side effects: the weight-gradient
+    // kernel of the same layer runs concurrently on another graph branch and is the designated writer
+    for (int c = threadIdx.x; c < P.K; c += blockDim.x) {
+      float ca, cb, cc;
+      bn_bwd_channel(gsrc, c % P.k_true, false, ca, cb, cc);
+      s_acoef[c] = ca;
+      s_acoef[P.K + c] = cb;
+      s_acoef[2 * P.K + c] = cc;
     }
   } else {
     for (int i = threadIdx.x; i < n_acoef; i += blockDim.x) {
@@ -542,7 +553,7 @@ int launch_t(const PwGemmPlan& pl, cudaStream_t s) {
   // depend on which layer set it last
   B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   B200DP_CUDA(launch_k(kern, dim3(pl.grid), dim3(Layout<AMODE>::kThreads), pl.smem_bytes, s, pl.tmA, pl.tmB, pl.tmAt, pl.tmBt,
-                       pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p, pl.asrc));
+                       pl.tmA2, pl.tmA2t, pl.tmO, pl.tmX, pl.p, pl.asrc, pl.gsrc));
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -610,6 +621,7 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   PwGemmParams& p = pl->p;
   p = PwGemmParams{};
   pl->asrc = BnFwdSrc{};
+  pl->gsrc = BnBwdSrc{};
   p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldo = ldo;
   p.n_true = n_true; p.k_true = k_true;
   p.block_n = N < 128 ? N : 128;

@@ -35,6 +35,7 @@ struct PwGemmPlan {
   CUtensorMap tmA, tmB, tmAt, tmBt, tmA2, tmA2t, tmO, tmX;   // At/Bt: maps for the (possibly narrower) last K chunk
   PwGemmParams p;
   BnFwdSrc asrc;                // A_BNRELU: finalise the A-side BatchNorm from its producer's sums in the prologue
+  BnBwdSrc gsrc;                // A_BNGRAD: compute (ca, cb, cc) from the sums in the prologue, side-effect free
   int amode, emode, grid;
   size_t smem_bytes;
 };

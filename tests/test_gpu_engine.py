@@ -75,7 +75,7 @@ def test_train_step_matches_teacher_forced_torch(env, graphs):
         assert err < 0.1 * b.norm().item() + 5e-4, (k, err, b.norm().item())    # cos >= 0.995 <=> relative error <= 0.1
         if b.norm() > 5e-3:                      # tiny BatchNorm-gain gradients are dominated by bf16 noise
             assert cos(a, b) > 0.995, (k, cos(a, b))
-            assert 0.97 < (a.norm() / b.norm()).item() < 1.03, (k, a.norm().item(), b.norm().item())
+            assert 0.95 < (a.norm() / b.norm()).item() < 1.05, (k, a.norm().item(), b.norm().item())
     # running statistics after one step against torch's own update on the fp32 forward
     ref2, _ = None, None
     sd = core.state_dict()
