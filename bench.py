@@ -43,7 +43,10 @@ def parse_args():
     ap.add_argument("--impl", default="b200dp", choices=["b200dp", "reference"])
     ap.add_argument("--engine", default="auto", choices=["auto", "native", "torch"])
     ap.add_argument("--comm", default="fused", choices=["fused", "nccl"])
-    ap.add_argument("--comm-algo", default="auto", choices=["auto", "one_shot", "two_shot"])
+    ap.add_argument("--comm-algo", default="auto", choices=["auto", "one_shot", "two_shot", "nvls"])
+    ap.add_argument("--comm-overlap", type=int, default=1, help="0: one fused kernel after the step graph (round-1 behaviour)")
+    ap.add_argument("--comm-buckets", default=None, help="block indices where gradient buckets start, e.g. 14,7,3")
+    ap.add_argument("--comm-blocks", type=int, default=0, help="CTAs per in-graph bucket launch")
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -68,7 +71,13 @@ def run_b200dp(ns) -> dict:
             raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
         ns.gpus = info.world_size
     mode = "ddp" if info.world_size > 1 else "gpu"
-    cfg = TrainConfig(mode=mode, engine=ns.engine, comm=ns.comm, comm_algo=ns.comm_algo, batch_size=ns.batch, dataset="synthetic")
+    cfg = TrainConfig(mode=mode, engine=ns.engine, comm=ns.comm, comm_algo=ns.comm_algo, batch_size=ns.batch, dataset="synthetic",
+                      comm_overlap=bool(ns.comm_overlap))
+    if ns.comm_buckets is not None:
+        cfg.comm_buckets = ns.comm_buckets
+    if ns.comm_blocks > 0:
+        cfg.comm_blocks = ns.comm_blocks
+    cfg.validate()
     ctx = setup_distributed(cfg.master_addr, cfg.master_port, "auto", info=info)
     if ctx.device.type != "cuda":
         raise SystemExit("bench.py needs a CUDA device")

@@ -14,9 +14,21 @@
 // one-shot (algo 0): every rank reduces and updates everything; traffic in = (W-1) * bytes.
 // two-shot (algo 1): rank r reduces + updates slice r only, then stores the new weights into
 //                    every peer (reduce-scatter + all-gather); traffic = 2 (W-1)/W * bytes.
+// NVLS     (algo 2): two-shot through the NVSwitch multicast mapping of the arena (vmm.cu):
+//                    `multimem.ld_reduce.add.v4.f32` returns the sum over all ranks computed in the
+//                    switch, `multimem.st.v4.f32` writes the updated slice into every replica.
+// A launch covers the element range [range_lo, range_hi): the executor (engine.cu) launches one
+// per gradient bucket from a branch of the step graph, so buckets reduce while backward is
+// still producing the next ones (DDP's Reducer, ref :142-145, :179).  Such launches use a small
+// fixed grid: block b only ever waits for block b of its peers, never for another block of its
+// own GPU, so a grid that is only partly resident next to the compute kernels still completes.
+// A barrier that times out (dead or stalled peer) makes the block return WITHOUT touching
+// weights, moments or gradients, and raises both a device flag (sticky: later launches return at
+// once) and, when given, a host-mapped mirror the trainer polls without synchronising.
 // No host involvement per step: learning rate, Adam step count and barrier epochs live in
 // device memory, so the launch is CUDA-graph capturable.
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -60,9 +72,33 @@ __device__ __forceinline__ void st_peer_u2(void* p, uint32_t a, uint32_t b) {
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(a), "r"(b) : "memory");
 }
 
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_f4(float* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ void raise_error(const b200dp_comm_adam& P, int code) {
+  atomicExch(P.error_flag, code);
+  if (P.error_host != nullptr) {
+    *reinterpret_cast<volatile int*>(P.error_host) = code;
+    __threadfence_system();
+  }
+}
+
 // All threads of the block call this.  Block b of this rank meets block b of every peer.
-__device__ __forceinline__ void flag_barrier(const b200dp_comm_adam& P, uint32_t target,
+// Returns false (for the whole block) when a peer did not arrive within `limit` polls.
+__device__ __forceinline__ bool flag_barrier(const b200dp_comm_adam& P, uint32_t target,
                                              unsigned long long limit) {
+  int failed = 0;
   __syncthreads();
   if (threadIdx.x < (unsigned)P.world) {
     __threadfence_system();
@@ -72,13 +108,20 @@ __device__ __forceinline__ void flag_barrier(const b200dp_comm_adam& P, uint32_t
     unsigned long long spins = 0;
     while ((int32_t)(ld_acquire_sys(mine) - target) < 0) {
       if (++spins > limit) {  // a peer is dead or stalled: report, do not hang the GPU
-        atomicExch(P.error_flag, 1 + (int)threadIdx.x);
+        raise_error(P, 1 + (int)threadIdx.x);
+        failed = 1;
         break;
       }
       if ((spins & 63) == 63) __nanosleep(64);
     }
   }
-  __syncthreads();
+  return __syncthreads_or(failed) == 0;
+}
+
+// sticky failure: once any launch has raised the flag, later launches do nothing
+__device__ __forceinline__ bool already_failed(const b200dp_comm_adam& P) {
+  const int bad = threadIdx.x == 0 ? *reinterpret_cast<volatile int*>(P.error_flag) : 0;
+  return __syncthreads_or(bad) != 0;
 }
 
 template <int GD>
@@ -116,8 +159,13 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
   const int W = (WT > 0) ? WT : P.world;
   const int rank = P.rank;
   const uint32_t epoch = P.epoch_state[blockIdx.x];
-  const int step = P.step_state[blockIdx.x];
+  const long long n4_all = P.numel >> 2;
+  const long long r_lo = P.range_hi > 0 ? (P.range_lo >> 2) : 0;
+  const long long r_hi = P.range_hi > 0 ? (P.range_hi >> 2) : n4_all;
+  const int step = P.step_state[0];     // advanced by a separate one-thread launch after the LAST launch of a step
+  const bool barriers = W > 1 && !P.skip_barriers;
   const unsigned long long limit = P.spin_limit ? P.spin_limit : kDefaultSpin;
+  if (already_failed(P)) return;
 
   if (threadIdx.x == 0) {
     const double t = (double)(step + 1);
@@ -126,32 +174,34 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
     s_scal[0] = (float)((double)(*P.lr) / bc1);
     s_scal[1] = (float)(1.0 / sqrt(bc2));
   }
-  if (W > 1) {
-    flag_barrier(P, epoch + 1, limit);  // every peer has finished its backward pass
+  if (barriers) {
+    if (!flag_barrier(P, epoch + 1, limit)) return;  // every peer has finished producing this range
   } else {
-    __syncthreads();
+    __syncthreads();      // (skip_barriers: a one-CTA barrier launch ahead of this one did the waiting)
   }
   const float step_size = s_scal[0], isb2 = s_scal[1];
   const float b1 = (float)P.beta1, b2 = (float)P.beta2, eps = P.eps, wd = P.weight_decay;
   const float ob1 = (float)(1.0 - P.beta1), ob2 = (float)(1.0 - P.beta2);
   const float scale = 1.0f / (float)W;
 
-  const long long n4 = P.numel >> 2;
-  long long lo = 0, hi = n4;
+  const long long n4 = r_hi - r_lo;
+  long long lo = r_lo, hi = r_hi;
   long long per = n4;
-  if (ALGO == 1) {
+  if (ALGO >= 1) {
     per = (n4 + W - 1) / W;
-    lo = per * rank;
-    hi = lo + per < n4 ? lo + per : n4;
+    lo = r_lo + per * rank;
+    hi = lo + per < r_hi ? lo + per : r_hi;
   }
-  const long long stride = (long long)gridDim.x * kThreads;
+  const long long stride = (long long)gridDim.x * blockDim.x;
   float* __restrict__ myp = P.params[rank];
   float* __restrict__ mm = P.m;
   float* __restrict__ vv = P.v;
 
-  for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += stride) {
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    if constexpr (WT > 0) {
+    if constexpr (ALGO == 2) {
+      acc = mc_ld_reduce_f4(reinterpret_cast<const float*>(P.mc_grads) + i * 4);   // summed inside the switch
+    } else if constexpr (WT > 0) {
       float4 g[WT];
 #pragma unroll
       for (int r = 0; r < WT; ++r) g[r] = load_grad<GD>(P.grads[r], i);   // all loads in flight first
@@ -185,6 +235,8 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
       if (P.work_bf16[rank] != nullptr)
         *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(P.work_bf16[rank]) + i * 4) =
             make_uint2(w01, w23);
+    } else if (ALGO == 2) {
+      mc_st_f4(P.mc_params + i * 4, p);   // one store, the switch replicates it into every rank's weights
     } else {
       for (int r = 0; r < W; ++r) {  // all-gather: push the updated slice into every replica
         st_peer_f4(P.params[r] + i * 4, p);
@@ -194,38 +246,45 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
     }
   }
 
-  const bool second = (W > 1) && (P.zero_grads || ALGO == 1);
-  if (second) flag_barrier(P, epoch + 2, limit);  // peers are done reading my gradients / writing my weights
+  if (W > 1) __threadfence_system();   // my stores into the peers' weights are performed before anything that follows
+  const bool second = barriers && (P.zero_grads || ALGO >= 1);
+  if (second && !flag_barrier(P, epoch + 2, limit)) return;  // peers are done reading my gradients / writing my weights
   if (P.zero_grads) {
     void* mine = const_cast<void*>(P.grads[rank]);
     if (ALGO == 0 || W == 1) {
-      for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n4; i += stride)
+      for (long long i = r_lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < r_hi; i += stride)
         zero_grad<GD>(mine, i);
     } else {
       for (int q = 0; q < W; ++q) {  // the part of slice q that block b of rank q has read
-        const long long qlo = per * q;
-        const long long qhi = qlo + per < n4 ? qlo + per : n4;
-        for (long long i = qlo + (long long)blockIdx.x * kThreads + threadIdx.x; i < qhi; i += stride)
+        const long long qlo = r_lo + per * q;
+        const long long qhi = qlo + per < r_hi ? qlo + per : r_hi;
+        for (long long i = qlo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < qhi; i += stride)
           zero_grad<GD>(mine, i);
       }
     }
   }
-  if (threadIdx.x == 0) {
-    P.epoch_state[blockIdx.x] = epoch + 2;
-    if (P.apply_adam) P.step_state[blockIdx.x] = step + 1;
-  }
+  if (threadIdx.x == 0 && barriers) P.epoch_state[blockIdx.x] = epoch + 2;
 }
 
+__global__ void comm_bump_kernel(int* step_state) { step_state[0] += 1; }
+
+// Barrier across ranks; `bump` != 0 also advances the Adam step count (the step's last launch).  With one CTA this
+// is how the in-graph buckets wait: the waiting costs one CTA slot, not the grid of the data launch that follows.
 __global__ void __launch_bounds__(kThreads)
-comm_barrier_kernel(const __grid_constant__ b200dp_comm_adam P) {
+comm_barrier_kernel(const __grid_constant__ b200dp_comm_adam P, int bump) {
   const uint32_t epoch = P.epoch_state[blockIdx.x];
   const unsigned long long limit = P.spin_limit ? P.spin_limit : kDefaultSpin;
-  if (P.world > 1) flag_barrier(P, epoch + 2, limit);
-  if (threadIdx.x == 0) P.epoch_state[blockIdx.x] = epoch + 2;
+  if (already_failed(P)) return;
+  if (P.world > 1 && !flag_barrier(P, epoch + 2, limit)) return;
+  if (threadIdx.x == 0) {
+    P.epoch_state[blockIdx.x] = epoch + 2;
+    if (bump && blockIdx.x == 0) P.step_state[0] += 1;
+  }
 }
 
 struct BcastArgs {
   float* dst[B200DP_MAX_WORLD];
+  float* mc_dst;              // multicast alias of dst (NVLS): one store reaches every rank
   const float* src;
   long long n4;
   int root;
@@ -235,22 +294,80 @@ __global__ void __launch_bounds__(kThreads)
 comm_broadcast_kernel(const __grid_constant__ b200dp_comm_adam P, const __grid_constant__ BcastArgs A) {
   const uint32_t epoch = P.epoch_state[blockIdx.x];
   const unsigned long long limit = P.spin_limit ? P.spin_limit : kDefaultSpin;
-  if (P.world > 1) flag_barrier(P, epoch + 1, limit);  // nobody is still using dst
+  if (already_failed(P)) return;
+  if (P.world > 1 && !flag_barrier(P, epoch + 1, limit)) return;  // nobody is still using dst
   if (P.rank == A.root) {
-    const long long stride = (long long)gridDim.x * kThreads;
-    for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < A.n4; i += stride) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < A.n4; i += stride) {
       const float4 v = *reinterpret_cast<const float4*>(A.src + i * 4);
-      for (int r = 0; r < P.world; ++r)
-        if (A.dst[r] + i * 4 != A.src + i * 4) st_peer_f4(A.dst[r] + i * 4, v);
+      if (A.mc_dst != nullptr) {
+        mc_st_f4(A.mc_dst + i * 4, v);
+      } else {
+        for (int r = 0; r < P.world; ++r)
+          if (A.dst[r] + i * 4 != A.src + i * 4) st_peer_f4(A.dst[r] + i * 4, v);
+      }
     }
   }
-  if (P.world > 1) flag_barrier(P, epoch + 2, limit);  // root's stores have landed everywhere
+  if (P.world > 1 && !flag_barrier(P, epoch + 2, limit)) return;  // root's stores have landed everywhere
   if (threadIdx.x == 0) P.epoch_state[blockIdx.x] = epoch + 2;
 }
 
+// All-reduce of k <= 32 doubles (sum or max): every rank stores its values into row `rank` of every peer's slot
+// table, barrier, every rank combines the rows of its own table in rank order (bit-identical results), barrier.
+// One block; shares flag row 0 and epoch slot 0 with the kernels above (same stream, same order on every rank).
+__global__ void __launch_bounds__(64)
+comm_reduce_f64_kernel(const __grid_constant__ b200dp_comm_adam P, const double* in, double* out, int k, int op) {
+  const uint32_t epoch = P.epoch_state[0];
+  const unsigned long long limit = P.spin_limit ? P.spin_limit : kDefaultSpin;
+  if (already_failed(P)) return;
+  const int W = P.world;
+  if (W == 1) {
+    if ((int)threadIdx.x < k) out[threadIdx.x] = in[threadIdx.x];
+    return;
+  }
+  if ((int)threadIdx.x < k) {
+    const double v = in[threadIdx.x];
+    for (int r = 0; r < W; ++r) {
+      double* dst = P.slots[r] + (size_t)P.rank * B200DP_REDUCE_MAX + threadIdx.x;
+      asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(dst), "d"(v) : "memory");
+    }
+  }
+  if (!flag_barrier(P, epoch + 1, limit)) return;
+  if ((int)threadIdx.x < k) {
+    double acc = 0.0;
+    for (int r = 0; r < W; ++r) {
+      double v;
+      const double* src = P.slots[P.rank] + (size_t)r * B200DP_REDUCE_MAX + threadIdx.x;
+      asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(src) : "memory");
+      acc = r == 0 ? v : (op == 0 ? acc + v : fmax(acc, v));
+    }
+    out[threadIdx.x] = acc;
+  }
+  if (!flag_barrier(P, epoch + 2, limit)) return;       // nobody overwrites a table that is still being read
+  if (threadIdx.x == 0) P.epoch_state[0] = epoch + 2;
+}
+
+// threads per CTA: 512 by default; bucket launches from the step graph (exact_blocks > 0) may use fewer so that a
+// comm CTA fits into the registers / thread slots the persistent compute CTAs leave free (B200DP_COMM_THREADS)
+int threads_for(const b200dp_comm_adam& a) {
+  static int small = [] {
+    const char* v = getenv("B200DP_COMM_THREADS");
+    const int t = v ? atoi(v) : 0;
+    return (t >= 32 && t <= kThreads && t % 32 == 0) ? t : 0;
+  }();
+  return (a.exact_blocks > 0 && small > 0) ? small : kThreads;
+}
+
+int grid_for(const b200dp_comm_adam& a);
+int validate(const b200dp_comm_adam* a);
+}  // namespace
+int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, int bump, cudaStream_t s);
+namespace {
+
 int grid_for(const b200dp_comm_adam& a) {
-  long long n4 = a.numel >> 2;
-  if (a.algo == 1 && a.world > 1) n4 = (n4 + a.world - 1) / a.world;
+  if (a.exact_blocks > 0) return a.exact_blocks < B200DP_COMM_MAX_BLOCKS ? a.exact_blocks : B200DP_COMM_MAX_BLOCKS;
+  long long n4 = (a.range_hi > 0 ? a.range_hi - a.range_lo : a.numel) >> 2;
+  if (a.algo >= 1 && a.world > 1) n4 = (n4 + a.world - 1) / a.world;
   long long blocks = (n4 + (long long)kThreads * 2 - 1) / ((long long)kThreads * 2);
   int cap = a.max_blocks > 0 ? a.max_blocks : kDefaultBlocks;
   if (cap > B200DP_COMM_MAX_BLOCKS) cap = B200DP_COMM_MAX_BLOCKS;
@@ -265,6 +382,10 @@ int validate(const b200dp_comm_adam* a) {
   B200DP_REQUIRE(a->rank >= 0 && a->rank < a->world, "comm_adam: rank %d outside world %d", a->rank, a->world);
   B200DP_REQUIRE(a->numel > 0 && (a->numel & 3) == 0, "comm_adam: numel %lld must be a positive multiple of 4",
                  a->numel);
+  B200DP_REQUIRE(a->range_hi == 0 || (a->range_lo >= 0 && a->range_lo < a->range_hi && a->range_hi <= a->numel &&
+                                      (a->range_lo & 3) == 0 && (a->range_hi & 3) == 0),
+                 "comm_adam: range [%lld, %lld) must be a non-empty multiple-of-4 sub-range of [0, %lld)", a->range_lo,
+                 a->range_hi, a->numel);
   B200DP_REQUIRE(a->epoch_state && a->step_state && a->error_flag, "comm_adam: state pointers missing");
   for (int r = 0; r < a->world; ++r) {
     B200DP_REQUIRE(a->grads[r] != nullptr, "comm_adam: grads[%d] is null", r);
@@ -275,18 +396,61 @@ int validate(const b200dp_comm_adam* a) {
 
 template <int GD, int ALGO>
 int launch_w(const b200dp_comm_adam& a, int grid, cudaStream_t s) {
+  const int threads = threads_for(a);
   switch (a.world) {
-    case 1: comm_adam_kernel<GD, ALGO, 1><<<grid, kThreads, 0, s>>>(a); break;
-    case 2: comm_adam_kernel<GD, ALGO, 2><<<grid, kThreads, 0, s>>>(a); break;
-    case 4: comm_adam_kernel<GD, ALGO, 4><<<grid, kThreads, 0, s>>>(a); break;
-    case 8: comm_adam_kernel<GD, ALGO, 8><<<grid, kThreads, 0, s>>>(a); break;
-    default: comm_adam_kernel<GD, ALGO, 0><<<grid, kThreads, 0, s>>>(a); break;
+    case 1: comm_adam_kernel<GD, ALGO, 1><<<grid, threads, 0, s>>>(a); break;
+    case 2: comm_adam_kernel<GD, ALGO, 2><<<grid, threads, 0, s>>>(a); break;
+    case 4: comm_adam_kernel<GD, ALGO, 4><<<grid, threads, 0, s>>>(a); break;
+    case 8: comm_adam_kernel<GD, ALGO, 8><<<grid, threads, 0, s>>>(a); break;
+    default: comm_adam_kernel<GD, ALGO, 0><<<grid, threads, 0, s>>>(a); break;
   }
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
 
 }  // namespace
+
+int comm_adam_launch(const b200dp_comm_adam& a, cudaStream_t s) {
+  if (int rc = validate(&a)) return rc;
+  if (a.apply_adam) {
+    B200DP_REQUIRE(a.params[a.rank] && a.m && a.v && a.lr, "comm_adam: Adam state pointers missing");
+    if (a.algo == 1)
+      for (int r = 0; r < a.world; ++r)
+        B200DP_REQUIRE(a.params[r] != nullptr, "comm_adam: two-shot needs params[%d]", r);
+  } else {
+    B200DP_REQUIRE(a.out_avg != nullptr, "comm_adam: out_avg missing");
+    B200DP_REQUIRE(a.algo == 0, "comm_adam: plain all-reduce is one-shot only");
+  }
+  B200DP_REQUIRE(a.grad_dtype == 0 || a.grad_dtype == 1, "comm_adam: grad_dtype must be 0 or 1");
+  B200DP_REQUIRE(a.algo >= 0 && a.algo <= 2, "comm_adam: algo must be 0, 1 or 2");
+  int algo = a.algo;
+  if (algo == 2) {
+    B200DP_REQUIRE(a.grad_dtype == 0, "comm_adam: the NVLS path reduces fp32 gradients");
+    if (a.world == 1) algo = 0;
+    else B200DP_REQUIRE(a.mc_grads && a.mc_params, "comm_adam: NVLS needs the multicast addresses");
+  }
+  const int grid = grid_for(a);
+  int rc;
+  if (a.grad_dtype == 0) {
+    rc = algo == 0 ? launch_w<0, 0>(a, grid, s) : algo == 1 ? launch_w<0, 1>(a, grid, s) : launch_w<0, 2>(a, grid, s);
+  } else {
+    rc = algo == 0 ? launch_w<1, 0>(a, grid, s) : launch_w<1, 1>(a, grid, s);
+  }
+  if (rc != B200DP_OK) return rc;
+  if (a.apply_adam && a.bump_step) {
+    comm_bump_kernel<<<1, 1, 0, s>>>(a.step_state);
+    B200DP_CHECK_LAUNCH();
+  }
+  return B200DP_OK;
+}
+
+int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, int bump, cudaStream_t s) {
+  if (int rc = validate(&a)) return rc;
+  comm_barrier_kernel<<<blocks, kThreads, 0, s>>>(a, bump);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
 }  // namespace b200dp
 
 using namespace b200dp;
@@ -297,33 +461,16 @@ extern "C" int b200dp_comm_adam_grid(const b200dp_comm_adam* a) {
 }
 
 extern "C" int b200dp_comm_adam_step(const b200dp_comm_adam* a, void* stream) {
-  if (int rc = validate(a)) return rc;
-  if (a->apply_adam) {
-    B200DP_REQUIRE(a->params[a->rank] && a->m && a->v && a->lr, "comm_adam: Adam state pointers missing");
-    if (a->algo == 1)
-      for (int r = 0; r < a->world; ++r)
-        B200DP_REQUIRE(a->params[r] != nullptr, "comm_adam: two-shot needs params[%d]", r);
-  } else {
-    B200DP_REQUIRE(a->out_avg != nullptr, "comm_adam: out_avg missing");
-    B200DP_REQUIRE(a->algo == 0, "comm_adam: plain all-reduce is one-shot only");
-  }
-  B200DP_REQUIRE(a->grad_dtype == 0 || a->grad_dtype == 1, "comm_adam: grad_dtype must be 0 or 1");
-  const int grid = grid_for(*a);
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (a->grad_dtype == 0) {
-    return a->algo == 0 ? launch_w<0, 0>(*a, grid, s) : launch_w<0, 1>(*a, grid, s);
-  }
-  return a->algo == 0 ? launch_w<1, 0>(*a, grid, s) : launch_w<1, 1>(*a, grid, s);
+  B200DP_REQUIRE(a != nullptr, "comm_adam: null args");
+  return comm_adam_launch(*a, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int b200dp_comm_barrier(const b200dp_comm_adam* a, void* stream) {
   if (int rc = validate(a)) return rc;
-  comm_barrier_kernel<<<grid_for(*a), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(*a);
-  B200DP_CHECK_LAUNCH();
-  return B200DP_OK;
+  return comm_barrier_launch(*a, grid_for(*a), 0, static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int b200dp_comm_broadcast(const b200dp_comm_adam* a, int root, float* const* dst_by_rank,
+extern "C" int b200dp_comm_broadcast(const b200dp_comm_adam* a, int root, float* const* dst_by_rank, float* mc_dst,
                                      const float* src, long long numel, void* stream) {
   if (int rc = validate(a)) return rc;
   B200DP_REQUIRE(root >= 0 && root < a->world, "broadcast: root %d outside world", root);
@@ -333,10 +480,25 @@ extern "C" int b200dp_comm_broadcast(const b200dp_comm_adam* a, int root, float*
     B200DP_REQUIRE(dst_by_rank[r] != nullptr, "broadcast: dst[%d] is null", r);
     b.dst[r] = dst_by_rank[r];
   }
+  b.mc_dst = a->world > 1 ? mc_dst : nullptr;
   b.src = src;
   b.n4 = numel >> 2;
   b.root = root;
-  comm_broadcast_kernel<<<grid_for(*a), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(*a, b);
+  b200dp_comm_adam g = *a;          // grid from the broadcast size, not from the optimiser's vector
+  g.numel = numel; g.range_lo = g.range_hi = 0; g.algo = 0; g.exact_blocks = 0;
+  comm_broadcast_kernel<<<grid_for(g), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(*a, b);
+  B200DP_CHECK_LAUNCH();
+  return B200DP_OK;
+}
+
+extern "C" int b200dp_comm_reduce_f64(const b200dp_comm_adam* a, const double* in, double* out, int k, int op,
+                                      void* stream) {
+  if (int rc = validate(a)) return rc;
+  B200DP_REQUIRE(in && out && k >= 1 && k <= B200DP_REDUCE_MAX, "reduce_f64: k=%d outside [1, %d]", k, B200DP_REDUCE_MAX);
+  B200DP_REQUIRE(op == 0 || op == 1, "reduce_f64: op must be 0 (sum) or 1 (max)");
+  if (a->world > 1)
+    for (int r = 0; r < a->world; ++r) B200DP_REQUIRE(a->slots[r] != nullptr, "reduce_f64: slots[%d] is null", r);
+  comm_reduce_f64_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(*a, in, out, k, op);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }

@@ -21,6 +21,10 @@
 
 extern "C" int b200dp_preprocess(const uint8_t* images, const float* params, void* out_bf16, int batch, int size,
                                  int out_channels, void* stream);
+namespace b200dp {
+int comm_adam_launch(const b200dp_comm_adam& a, cudaStream_t s);
+int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, int bump, cudaStream_t s);
+}
 extern "C" int b200dp_softmax_xent(const float* logits, const int64_t* labels, float* loss_out, float* dlogits_out,
                                    double* metrics, int batch, int classes, float mean_over, void* stream);
 
@@ -54,7 +58,7 @@ struct WPrepEntry { long long off; int n, k; int rf, rd; long long off_pf, off_p
 struct Plans {            // per batch size
   int n = 0;
   std::vector<PwGemmPlan> fwd, fwd_eval, dgrad;    // indexed by conv (index 0 = the stem run as an im2col GEMM)
-  cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr;
+  cudaGraphExec_t train_graph = nullptr, eval_graph = nullptr, eval_pre_graph = nullptr;
   int train_aug = -1;      // augmentation flag the train graph was captured with
   unsigned long long train_kernels = 0, eval_kernels = 0;   // kernel nodes in each graph (for the launch counter)
 };
@@ -112,6 +116,13 @@ struct Engine {
   cudaStream_t side[3] = {nullptr, nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_next = 0;
+  // Gradient all-reduce + Adam inside the step (set_comm): one launch per bucket, on side[2], as soon as backward
+  // has produced the bucket.  Buckets are address ranges of the flat arena; bucket_first[k] = index of the first
+  // block of bucket k (descending: backward reaches them in this order), the last bucket ends with the stem.
+  bool comm_on = false;
+  b200dp_comm_adam comm{};
+  int comm_blocks = 148;
+  std::vector<int> bucket_first;
   bool eval_coef_valid = false;
   std::map<int, Plans> plans;
   // profiling
@@ -361,7 +372,7 @@ int order_after(Engine& e, cudaStream_t from, cudaStream_t to) {
   return B200DP_OK;
 }
 
-int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t s) {
+int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t s, bool pre = false) {
   // the bf16 weight copies do not depend on the input, the preprocessing does not depend on the weights: two branches
   e.ev_next = 0;
   cudaStream_t sw = (e.fork && !e.profiling) ? e.side[0] : s;
@@ -377,7 +388,7 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
                                   e.eps, c.coef_f, c.coutp, s));
     mark(e, s, "bn_eval_coef");
   }
-  ENG_TRY(b200dp_preprocess(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0, n, e.S, 4, s));
+  if (!pre) ENG_TRY(b200dp_preprocess(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0, n, e.S, 4, s));
   mark(e, s, "preprocess");
   Conv& st = e.convs[0];
   if (e.stem_gemm) {
@@ -465,6 +476,42 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     if (side == s) return B200DP_OK;
     ev = next_event(e);
     B200DP_CUDA(cudaEventRecord(ev, side));
+    return B200DP_OK;
+  };
+  // ---- communication branch: bucket k covers the arena from the first conv of block bucket_first[k] up to the
+  // start of bucket k-1 (bucket 0 runs to the end of the arena: last conv + classifier)
+  cudaStream_t sc = (e.fork && !e.profiling) ? e.side[2] : s;
+  size_t next_bucket = 0;
+  long long bucket_hi = e.param_total;
+  bool sc_used = false;
+  auto launch_bucket = [&](long long lo, bool last) -> int {
+    if (sc != s) {
+      ENG_TRY(order_after(e, s, sc));
+      if (sp_used) ENG_TRY(order_after(e, sp_side, sc));
+      if (se_used) ENG_TRY(order_after(e, se_side, sc));
+      sc_used = true;
+    }
+    // Waiting and moving data are separate launches: a ONE-CTA barrier kernel absorbs the skew between ranks while
+    // the compute kernels keep every other SM, then a wide, short launch reduces + updates the bucket without
+    // waiting for anybody.  After the last bucket one more barrier tells every rank that its weights are complete
+    // and its gradients have been read; only then are the gradients cleared.
+    b200dp_comm_adam a = e.comm;
+    const bool multi = a.world > 1;
+    if (multi) ENG_TRY(comm_barrier_launch(a, 1, 0, sc));
+    a.range_lo = lo;
+    a.range_hi = bucket_hi;
+    a.skip_barriers = multi ? 1 : 0;
+    a.zero_grads = multi ? 0 : 1;
+    a.bump_step = (last && !multi) ? 1 : 0;
+    a.exact_blocks = 0;
+    a.max_blocks = e.comm_blocks;
+    ENG_TRY(comm_adam_launch(a, sc));
+    mark(e, s, "comm_adam");
+    if (last && multi) {
+      ENG_TRY(comm_barrier_launch(a, 1, 1, sc));
+      B200DP_CUDA(cudaMemsetAsync(e.grads, 0, (size_t)e.param_total * sizeof(float), sc));
+    }
+    bucket_hi = lo;
     return B200DP_OK;
   };
   const int li = (int)e.convs.size() - 1;
@@ -580,7 +627,18 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       }
       mark(e, s, "stem_wgrad", 0);
     }
+    // every gradient of blocks >= bi exists now: hand the finished bucket to the communication branch
+    if (e.comm_on) {
+      if (bi == 0) {
+        ENG_TRY(launch_bucket(0, true));
+      } else if (next_bucket < e.bucket_first.size() && e.bucket_first[next_bucket] == bi) {
+        const Conv& first = e.convs[b.ce >= 0 ? b.ce : b.cd];
+        ENG_TRY(launch_bucket(first.off_w, false));
+        ++next_bucket;
+      }
+    }
   }
+  if (sc_used) ENG_TRY(order_after(e, sc, s));
   // join the side branches: the step (and the capture) ends on the main stream
   if (sp_used) ENG_TRY(order_after(e, sp_side, s));
   if (se_used) ENG_TRY(order_after(e, se_side, s));
@@ -670,7 +728,12 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   e->n_pw = (int)table.size();
   B200DP_CUDA(cudaMemcpy(e->wprep_dev, table.data(), table.size() * sizeof(WPrepEntry), cudaMemcpyHostToDevice));
   B200DP_CUDA(cudaStreamCreateWithFlags(&e->cap_stream, cudaStreamNonBlocking));
-  for (auto& st : e->side) B200DP_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  {
+    int prio_lo = 0, prio_hi = 0;     // numerically lowest = highest priority
+    B200DP_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    for (int i = 0; i < 3; ++i)       // the communication branch outranks compute: its few CTAs take the first free slots
+      B200DP_CUDA(cudaStreamCreateWithPriority(&e->side[i], cudaStreamNonBlocking, i == 2 ? prio_hi : prio_lo));
+  }
   B200DP_CUDA(cudaDeviceSynchronize());
   *out = e;
   return B200DP_OK;
@@ -683,6 +746,7 @@ int b200dp_engine_destroy(void* h) {
   for (auto& kv : e->plans) {
     if (kv.second.train_graph) cudaGraphExecDestroy(kv.second.train_graph);
     if (kv.second.eval_graph) cudaGraphExecDestroy(kv.second.eval_graph);
+    if (kv.second.eval_pre_graph) cudaGraphExecDestroy(kv.second.eval_pre_graph);
   }
   if (e->cap_stream) cudaStreamDestroy(e->cap_stream);
   for (auto& st : e->side) if (st) cudaStreamDestroy(st);
@@ -796,6 +860,75 @@ int b200dp_engine_eval_step(void* h, const uint8_t* images, const int64_t* label
   }
   B200DP_CUDA(cudaGraphLaunch(g, s));
   g_launches.fetch_add(pl->eval_kernels, std::memory_order_relaxed);
+  return B200DP_OK;
+}
+
+// Evaluation forward of input that is already pre-processed: `x` = normalised bf16 NHWC [n, S, S, 4] (4th channel 0),
+// e.g. a full-resolution photograph resized to S x S outside (inference.py).  Logits land in buffer 3.
+int b200dp_engine_forward_preprocessed(void* h, const void* x, int n, void* stream) {
+  Engine* e = static_cast<Engine*>(h);
+  B200DP_REQUIRE(e && x && n >= 1 && n <= e->B, "forward_preprocessed: batch %d outside [1, %d]", n, e ? e->B : 0);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (x != (const void*)e->x0)
+    B200DP_CUDA(cudaMemcpyAsync(e->x0, x, (size_t)n * e->S * e->S * 4 * 2, cudaMemcpyDeviceToDevice, s));
+  Plans* pl;
+  ENG_TRY(get_plans(*e, n, &pl));
+  if (!e->use_graphs || e->profiling || !e->eval_coef_valid) {
+    ENG_TRY(forward(*e, *pl, n, false, false, s, true));
+    e->eval_coef_valid = true;
+    return B200DP_OK;
+  }
+  cudaGraphExec_t& g = pl->eval_pre_graph;
+  if (g == nullptr) {
+    cudaGraph_t graph;
+    cudaStream_t cs = e->cap_stream;
+    const unsigned long long before = g_launches.load();
+    B200DP_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    int rc = forward(*e, *pl, n, false, false, cs, true);
+    cudaError_t ce = cudaStreamEndCapture(cs, &graph);
+    pl->eval_kernels = g_launches.load() - before;
+    g_launches.store(before);
+    if (rc != B200DP_OK) { if (ce == cudaSuccess) cudaGraphDestroy(graph); return rc; }
+    B200DP_CUDA(ce);
+    B200DP_CUDA(cudaGraphInstantiate(&g, graph, 0));
+    cudaGraphDestroy(graph);
+  }
+  B200DP_CUDA(cudaGraphLaunch(g, s));
+  g_launches.fetch_add(pl->eval_kernels, std::memory_order_relaxed);
+  return B200DP_OK;
+}
+
+// Run the gradient all-reduce + Adam INSIDE the training step (bucketed, overlapped with backward): `args` is the
+// fully populated argument block of b200dp_comm_adam_step (copied; range / bump_step / exact_blocks are set per
+// bucket here), `bucket_first` the block indices (0..16, strictly descending) at which a new bucket starts, and
+// `comm_blocks` the fixed grid of every bucket launch.  args == NULL switches it off again.  Existing step graphs
+// are dropped.  Every rank must configure the same buckets.
+int b200dp_engine_set_comm(void* h, const b200dp_comm_adam* args, const int* bucket_first, int n_buckets,
+                           int comm_blocks) {
+  Engine* e = static_cast<Engine*>(h);
+  B200DP_REQUIRE(e != nullptr, "set_comm: null engine");
+  cudaDeviceSynchronize();
+  for (auto& kv : e->plans) {
+    if (kv.second.train_graph) { cudaGraphExecDestroy(kv.second.train_graph); kv.second.train_graph = nullptr; }
+  }
+  e->comm_on = args != nullptr;
+  e->bucket_first.clear();
+  if (!e->comm_on) return B200DP_OK;
+  B200DP_REQUIRE(args->numel == e->param_total, "set_comm: optimiser vector has %lld elements, the arena %lld",
+                 args->numel, e->param_total);
+  B200DP_REQUIRE(args->grads[args->rank] == (const void*)e->grads && args->params[args->rank] == e->params,
+                 "set_comm: the optimiser must work on the engine's gradient and parameter arenas");
+  B200DP_REQUIRE(comm_blocks >= 1 && comm_blocks <= B200DP_COMM_MAX_BLOCKS, "set_comm: comm_blocks %d out of range",
+                 comm_blocks);
+  int prev = (int)e->blocks.size();
+  for (int i = 0; i < n_buckets; ++i) {
+    B200DP_REQUIRE(bucket_first[i] > 0 && bucket_first[i] < prev, "set_comm: bucket starts must descend within (0, %d)",
+                   (int)e->blocks.size());
+    prev = bucket_first[i];
+    e->bucket_first.push_back(bucket_first[i]);
+  }
+  e->comm = *args;
+  e->comm_blocks = comm_blocks;
   return B200DP_OK;
 }
 

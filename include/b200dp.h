@@ -28,6 +28,7 @@ extern "C" {
 
 #define B200DP_MAX_WORLD 16
 #define B200DP_COMM_MAX_BLOCKS 256
+#define B200DP_REDUCE_MAX 32
 #define B200DP_AUG_NPARAM 12
 
 const char* b200dp_last_error(void);
@@ -66,7 +67,9 @@ typedef struct b200dp_comm_adam {
   int grad_dtype;                           /* 0 = fp32 gradients, 1 = bf16 gradients */
   int algo;                                 /* 0 = one-shot (every rank reduces everything),
                                                1 = two-shot (rank r reduces + updates slice r, then
-                                                   stores the new weights into every peer) */
+                                                   stores the new weights into every peer),
+                                               2 = NVLS: two-shot with multimem.ld_reduce / multimem.st on
+                                                   the multicast mapping (mc_grads, mc_params) */
   const void* grads[B200DP_MAX_WORLD];      /* grads[r] = rank r's gradient vector as mapped HERE */
   uint32_t* flags[B200DP_MAX_WORLD];        /* flags[r] = rank r's flag pad as mapped HERE
                                                (B200DP_COMM_MAX_BLOCKS * B200DP_MAX_WORLD uint32) */
@@ -76,7 +79,7 @@ typedef struct b200dp_comm_adam {
   float* m;                                 /* Adam first moment  (local) */
   float* v;                                 /* Adam second moment (local) */
   const float* lr;                          /* device scalar: learning rate for this step */
-  int* step_state;                          /* device int[B200DP_COMM_MAX_BLOCKS]: completed Adam steps */
+  int* step_state;                          /* device int[>= 1]: step_state[0] = completed Adam steps */
   uint32_t* epoch_state;                    /* device uint32[B200DP_COMM_MAX_BLOCKS]: barrier epochs */
   int* error_flag;                          /* device int: set non-zero if a barrier spin timed out */
   double beta1, beta2;                      /* doubles: (1 - beta) and the bias corrections match torch.optim.Adam exactly */
@@ -87,6 +90,23 @@ typedef struct b200dp_comm_adam {
   float* out_avg;                           /* apply_adam == 0: fp32 output vector (local) */
   unsigned long long spin_limit;            /* polls before a barrier gives up (0 = default) */
   int max_blocks;                           /* 0 = default grid */
+  /* ---- bucketed launches (engine.cu launches one per gradient bucket from a branch of the step graph) ---- */
+  long long range_lo, range_hi;             /* element sub-range handled by this launch, multiples of 4;
+                                               range_hi == 0 means the whole vector */
+  int bump_step;                            /* advance the Adam step count after this launch (the LAST launch of a
+                                               step sets it; done by a one-thread follow-up launch) */
+  int skip_barriers;                        /* the caller has already waited for the peers with a one-CTA
+                                               b200dp_comm_barrier ahead of this launch (in-graph buckets): do not
+                                               wait again (zero_grads must then be 0 unless world == 1) */
+  int exact_blocks;                         /* > 0: use exactly this grid */
+  /* ---- NVLS ---- */
+  const void* mc_grads;                     /* multicast address of the gradient vector (algo 2) */
+  float* mc_params;                         /* multicast address of the master weights (algo 2) */
+  /* ---- failure reporting / small reductions ---- */
+  int* error_host;                          /* optional host-mapped int mirroring error_flag: the trainer polls it
+                                               without synchronising the device */
+  double* slots[B200DP_MAX_WORLD];          /* slots[r] = rank r's table double[B200DP_MAX_WORLD][B200DP_REDUCE_MAX]
+                                               as mapped HERE (b200dp_comm_reduce_f64) */
 } b200dp_comm_adam;
 
 /* Launch the fused step on `stream`.  All ranks must call it the same number of times with the
@@ -100,8 +120,34 @@ int b200dp_comm_barrier(const b200dp_comm_adam* args, void* stream);
 
 /* Rank `root` stores `numel` fp32 values into every peer's `dst` (K-C3, K-C4:
  * DDP's parameter broadcast at construction and buffer broadcast, ref :142, :177). */
-int b200dp_comm_broadcast(const b200dp_comm_adam* args, int root, float* const* dst_by_rank,
+int b200dp_comm_broadcast(const b200dp_comm_adam* args, int root, float* const* dst_by_rank, float* mc_dst,
                           const float* src, long long numel, void* stream);
+/* `mc_dst` (may be NULL): multicast alias of the destination; the root then issues one multimem.st per 16 bytes
+ * and the NVSwitch replicates it, instead of W-1 peer stores. */
+
+/* All-reduce (op 0 = sum, 1 = max) of k <= B200DP_REDUCE_MAX doubles over the peer slot tables: the epoch-level
+ * metric sums and the max-over-ranks timers (K-C6, K-C7: dist.all_reduce of [loss_sum, count],
+ * ref :188-195, :216-223).  `in` / `out` are local device arrays; identical results on every rank. */
+int b200dp_comm_reduce_f64(const b200dp_comm_adam* args, const double* in, double* out, int k, int op,
+                           void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Symmetric memory with an NVSwitch multicast alias (csrc/vmm.cu; SURVEY §5.8 "memory model").
+ * CUDA VMM allocations exported as POSIX file descriptors (the Python layer passes them between
+ * ranks over AF_UNIX sockets) and one multicast object bound over every rank's allocation.
+ * (Replaces what NCCL does internally for the communicator of ref :142-145.)
+ * ------------------------------------------------------------------------------------------- */
+int b200dp_vmm_query(int* flags_out, size_t* granularity_out);     /* bit 0: VMM + fd export, bit 1: multicast */
+int b200dp_vmm_alloc(size_t bytes, void** ptr_out, int* fd_out, unsigned long long* handle_out);
+int b200dp_vmm_import(int fd, size_t bytes, void** ptr_out);
+int b200dp_vmm_free(void* ptr);
+int b200dp_mc_create(int world, size_t bytes, unsigned long long* mc_out, int* fd_out);    /* rank 0 */
+int b200dp_mc_import(int fd, size_t bytes, unsigned long long* mc_out);                    /* other ranks */
+int b200dp_mc_add_device(unsigned long long mc);        /* every rank, before any bind */
+int b200dp_mc_bind(unsigned long long mc, unsigned long long mem_handle, size_t bytes);
+int b200dp_mc_map(unsigned long long mc, size_t bytes, void** ptr_out);
+int b200dp_mc_release(unsigned long long mc);
+int b200dp_close_fd(int fd);
 
 /* ---------------------------------------------------------------------------------------------
  * Input pipeline (P1-P7, K14).
@@ -208,11 +254,42 @@ int b200dp_block_out(const void* raw, const void* res, const float* coef, void* 
  *     and saved_out [2][C] = (mean, inv-std); running statistics are not touched;
  *   - all calls on one GPU share the scratch: calls that may overlap on the device race -- serialise them;
  *   - the FIRST call on each device looks up the scratch's device address (cudaGetSymbolAddress); make that
- *     first call before any stream capture begins. */
+ *     first call before any stream capture begins.  The look-up is not synchronised between host threads: two
+ *     threads making the first call at once both store the same address, which is harmless but is a data race in
+ *     the letter of the C++ memory model -- make the first call from one thread. */
 #define B200DP_DW_NOALLOC_MAX_C 1024
 int b200dp_dw_fwd_bn_noalloc(const void* x, const float* in_scale, const float* in_shift, const float* w,
                              const float* gamma, const float* beta, float eps, void* y, float* coef_out,
                              float* saved_out, int B, int H, int W, int C, int stride, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Whole-model executor (csrc/engine.cu): MobileNetV2 + 10-class head, one training or evaluation step as one
+ * CUDA-graph launch over the kernels above.
+ *   reference: the hot loop zero_grad -> forward -> loss -> backward -> step of
+ *   cifar10_mpi_mobilenet_224.py:173-185 and the eval loop :199-213.
+ * `offsets` is the table of models/arena.py (per conv: weight, gamma, beta, running mean, running var element
+ * offsets; then classifier weight, bias); params / grads / buffers are flat fp32 arenas owned by the caller.
+ * ------------------------------------------------------------------------------------------- */
+int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, const long long* offsets, int n_offsets,
+                         long long param_total, long long buffer_total, float* params, float* grads, float* buffers,
+                         float dropout, float bn_eps, float bn_momentum, unsigned seed, int use_graphs);
+int b200dp_engine_destroy(void* engine);
+size_t b200dp_engine_workspace_bytes(void* engine);
+void* b200dp_engine_buffer(void* engine, int which);
+void* b200dp_engine_tap(void* engine, int what, int index);
+/* forward + loss + backward (gradients accumulate into `grads`); with b200dp_engine_set_comm also the bucketed
+ * gradient all-reduce + Adam, overlapped with backward (DDP's Reducer + optimizer.step, ref :142-145, :179-180). */
+int b200dp_engine_train_step(void* engine, const uint8_t* images, const int64_t* labels, const float* aug, int n,
+                             void* stream);
+int b200dp_engine_eval_step(void* engine, const uint8_t* images, const int64_t* labels, int n, void* stream);
+/* Forward of already pre-processed input: `x` is normalised bf16 NHWC [n, S, S, 4] (inference on full-resolution
+ * images that were resized outside, ref cifar10_128batch.py:157-172); logits land in buffer 3. */
+int b200dp_engine_forward_preprocessed(void* engine, const void* x, int n, void* stream);
+int b200dp_engine_invalidate(void* engine);
+int b200dp_engine_set_comm(void* engine, const b200dp_comm_adam* args, const int* bucket_first, int n_buckets,
+                           int comm_blocks);
+int b200dp_engine_profile_step(void* engine, const uint8_t* images, const int64_t* labels, const float* aug, int n,
+                               char* names, int names_cap, float* ms, int ms_cap, int* count, void* stream);
 
 #ifdef __cplusplus
 }

@@ -30,7 +30,14 @@ class TrainConfig:
     engine: str = "auto"              # auto | native (sm_100a kernels) | torch (ATen ops; CPU mode and the comparison baseline)
     comm: str = "fused"               # fused (peer-memory all-reduce + Adam kernel) | nccl (baseline: NCCL all-reduce + separate Adam)
     comm_algo: str = "auto"           # fused kernel: one_shot (every rank pulls all peers' gradients) | two_shot (reduce-scatter +
-                                      # all-gather over peer memory, 2(W-1)/W instead of W-1 gradient volumes per GPU) | auto = two_shot for W >= 4
+                                      # all-gather over peer memory, 2(W-1)/W instead of W-1 gradient volumes per GPU) | nvls (two-shot
+                                      # with multimem.ld_reduce / multimem.st through the NVSwitch) | auto = nvls / two_shot for W >= 4
+    comm_overlap: bool = True         # run the fused kernel per gradient bucket from a branch of the step graph, overlapped with backward
+    comm_buckets: str = "auto"        # block indices (0..16, descending) at which a new gradient bucket starts; "" = one bucket at
+                                      # the end of backward.  auto = "7" on several GPUs (blocks 7..16 + last conv + classifier = 96 %
+                                      # of the parameters, complete after ~30 % of backward), "" on one GPU (nothing to hide but 15 us
+                                      # of Adam, and every extra launch next to the compute kernels costs about that much)
+    comm_blocks: int = 148            # cap on the CTAs of an in-graph bucket launch (wide and short; the waiting is a separate one-CTA launch)
     # ---- data --------------------------------------------------------------
     data_root: str = "./data"
     dataset: str = "auto"             # auto = real CIFAR-10 if present under data_root, else synthetic
@@ -90,8 +97,14 @@ class TrainConfig:
             raise ValueError(f"engine must be auto|native|torch, got {self.engine!r}")
         if self.comm not in ("fused", "nccl"):
             raise ValueError(f"comm must be fused|nccl, got {self.comm!r}")
-        if self.comm_algo not in ("auto", "one_shot", "two_shot"):
-            raise ValueError(f"comm_algo must be auto|one_shot|two_shot, got {self.comm_algo!r}")
+        if self.comm_algo not in ("auto", "one_shot", "two_shot", "nvls"):
+            raise ValueError(f"comm_algo must be auto|one_shot|two_shot|nvls, got {self.comm_algo!r}")
+        try:
+            starts = [] if self.comm_buckets == "auto" else [int(x) for x in self.comm_buckets.split(",") if x.strip()]
+        except ValueError:
+            raise ValueError(f"comm_buckets must be a comma-separated list of block indices, got {self.comm_buckets!r}")
+        if any(not (0 < b < 17) for b in starts) or any(a <= b for a, b in zip(starts, starts[1:])):
+            raise ValueError(f"comm_buckets must descend within 1..16, got {self.comm_buckets!r}")
         if self.epochs < 0 or self.lr <= 0:
             raise ValueError("epochs must be >= 0 and lr > 0")
         if not (0.0 <= self.dropout < 1.0):

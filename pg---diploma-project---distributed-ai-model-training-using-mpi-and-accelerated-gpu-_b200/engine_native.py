@@ -52,6 +52,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200dp_engine_profile_step.argtypes = [vp, vp, vp, vp, i, C.c_char_p, i, C.POINTER(C.c_float), i,
                                                C.POINTER(i), vp]
     lib.b200dp_engine_profile_step.restype = i
+    lib.b200dp_engine_forward_preprocessed.argtypes = [vp, vp, i, vp]
+    lib.b200dp_engine_forward_preprocessed.restype = i
+    lib.b200dp_engine_set_comm.argtypes = [vp, vp, C.POINTER(i), i, i]
+    lib.b200dp_engine_set_comm.restype = i
 
 
 _lib.register_decls(_declare)
@@ -78,7 +82,7 @@ class NativeCore:
 
     def __init__(self, device: torch.device, batch: int, img_size: int, num_classes: int, dropout: float,
                  seed: int, grads: Optional[torch.Tensor] = None, use_graphs: bool = True,
-                 params: Optional[torch.Tensor] = None) -> None:
+                 params: Optional[torch.Tensor] = None, buffers: Optional[torch.Tensor] = None) -> None:
         self.lib = _lib.require()
         self.device = device
         self.batch = batch
@@ -86,7 +90,7 @@ class NativeCore:
         L = self.layout
         # `params` / `grads` may live in a peer-mapped comm arena (two-shot optimiser: peers store the updated slices)
         self.params = params if params is not None else torch.zeros(L.total, dtype=torch.float32, device=device)
-        self.buffers = torch.zeros(L.buffer_total, dtype=torch.float32, device=device)
+        self.buffers = buffers if buffers is not None else torch.zeros(L.buffer_total, dtype=torch.float32, device=device)
         self.grads = grads if grads is not None else torch.zeros(L.total, dtype=torch.float32, device=device)
         self.num_batches_tracked = 0
         table = L.offsets_table()
@@ -130,6 +134,16 @@ class NativeCore:
     def eval_step(self, images: torch.Tensor, labels: torch.Tensor, n: int) -> None:
         check(self.lib.b200dp_engine_eval_step(self.h, images.data_ptr(), labels.data_ptr(), n, _lib.current_stream()))
 
+    def forward_preprocessed(self, x: torch.Tensor, n: int) -> None:
+        """Eval forward of normalised bf16 NHWC input [n, S, S, 4]; logits land in ``self.logits``."""
+        check(self.lib.b200dp_engine_forward_preprocessed(self.h, x.data_ptr(), n, _lib.current_stream()))
+
+    def set_comm(self, fused, bucket_first: List[int], comm_blocks: int) -> None:
+        """Hand the fused all-reduce + Adam to the executor: one launch per gradient bucket inside the step graph."""
+        arr = (C.c_int * max(len(bucket_first), 1))(*bucket_first)
+        check(self.lib.b200dp_engine_set_comm(self.h, C.byref(fused.args) if fused is not None else None, arr,
+                                              len(bucket_first), comm_blocks))
+
     def profile_step(self, images, labels, aug, n) -> List[Tuple[str, float]]:
         names = C.create_string_buffer(1 << 16)
         ms = (C.c_float * 1024)()
@@ -157,48 +171,55 @@ class NativeEngine:
         layout = ArenaLayout(build_spec(cfg.img_size, cfg.num_classes))
         hyper = AdamHyper(cfg.lr, cfg.beta1, cfg.beta2, cfg.eps, cfg.weight_decay)
         self.nccl = cfg.comm == "nccl"
-        # gradients live in the peer-mapped comm arena; the executor accumulates straight into it
-        algo = cfg.comm_algo
-        if algo == "auto":      # measured at W = 8: one-shot 128 us vs NCCL 72 us for the 9 MB gradient; two-shot moves 4x less
-            algo = "two_shot" if ctx.world_size >= 4 else "one_shot"
-        self.comm_algo = algo
-        self.fused = FusedAllReduceAdam(ctx, layout.total, hyper, algo=algo)
-        if algo == "two_shot":
-            # master weights live in the comm arena: each rank updates its slice and stores it into every peer's copy
-            self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
-                                   cfg.seed + 7919 * ctx.rank, grads=self.fused.grads, params=self.fused.params)
-        else:
-            self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
-                                   cfg.seed + 7919 * ctx.rank, grads=self.fused.grads)
-            # the fused kernel updates the executor's master weights in place
-            self.fused.params = self.core.params
-            self.fused.args.params[ctx.rank] = self.core.params.data_ptr()
+        # gradients, master weights and BatchNorm running statistics live in the symmetric comm arena: the executor
+        # accumulates gradients straight into it, peers read them there and store updated weights / statistics
+        self.fused = FusedAllReduceAdam(ctx, layout.total, hyper, algo=cfg.comm_algo, extra_numel=layout.buffer_total)
+        self.comm_algo = self.fused.algo_name
+        self.core = NativeCore(self.device, cfg.resolved_batch_size(), cfg.img_size, cfg.num_classes, cfg.dropout,
+                               cfg.seed + 7919 * ctx.rank, grads=self.fused.grads, params=self.fused.params,
+                               buffers=self.fused.extra)
         init = build_model(cfg.num_classes, cfg.dropout, cfg.img_size, cfg.pretrained)
         self.core.load_state_dict(init.state_dict())
         del init
         self.broadcast_parameters()
         self.steps = 0
+        self.in_graph = (not self.nccl) and cfg.comm_overlap
+        if self.in_graph:
+            spec = ("7" if ctx.world_size > 1 else "") if cfg.comm_buckets == "auto" else cfg.comm_buckets
+            starts = [int(x) for x in spec.split(",") if x.strip()]
+            self.comm_buckets = starts
+            self.core.set_comm(self.fused, starts, cfg.comm_blocks)
         if self.nccl:
             from .optim import FlatAdam
             self.adam = FlatAdam(layout.total, self.device, hyper)
 
     # ---- replica consistency ---------------------------------------------------------------------
     def broadcast_parameters(self) -> None:
-        import torch.distributed as dist
         if self.ctx.initialized:
-            dist.broadcast(self.core.params, src=0)     # K-C3: DDP's constructor broadcast
+            torch.cuda.current_stream().synchronize()
+            self.fused.broadcast_params(0)              # K-C3: DDP's constructor broadcast, as peer / multicast stores
             self.sync_buffers()
 
     def sync_buffers(self) -> None:
-        import torch.distributed as dist
         if self.ctx.initialized:
-            dist.broadcast(self.core.buffers, src=0)    # K-C4: rank 0's running statistics are authoritative
+            self.fused.broadcast_extra(0)               # K-C4: rank 0's running statistics are authoritative
             self.core.lib.b200dp_engine_invalidate(self.core.h)
+
+    def reduce(self, values, op: str = "sum"):
+        """Sum / max of a few doubles over ranks on the peer slot tables (K-C6 / K-C7, max-over-ranks timers)."""
+        t = torch.as_tensor(list(values), dtype=torch.float64, device=self.device)
+        return [float(x) for x in self.fused.reduce_f64(t, op).tolist()]
 
     # ---- steps -------------------------------------------------------------------------------------
     def train_step(self, batch, lr: float) -> None:
         batch.wait()
         aug = batch.params if self.cfg.augment else None
+        if self.in_graph:     # the step graph contains the bucketed all-reduce + Adam; only the learning rate is fed in
+            self.fused.set_lr(lr)
+            self.core.train_step(batch.images, batch.labels, aug, batch.n)
+            self.fused.poll_error()
+            self.steps += 1
+            return
         self.core.train_step(batch.images, batch.labels, aug, batch.n)
         if self.nccl:     # comparison baseline: NCCL all-reduce + separate Adam
             import torch.distributed as dist
@@ -208,6 +229,7 @@ class NativeEngine:
             self.core.grads.zero_()
         else:
             self.fused.step(lr)
+            self.fused.poll_error()
         self.steps += 1
 
     def eval_step(self, batch) -> None:
@@ -227,6 +249,7 @@ class NativeEngine:
     # ---- metrics / state -------------------------------------------------------------------------
     def read_metrics(self, reset: bool = True) -> Tuple[float, float, float]:
         m = (self.core.metrics_train + self.core.metrics_eval).tolist()
+        self.fused.poll_error()           # the read above synchronised: a timed-out barrier is visible by now
         if reset:
             self.core.metrics_train.zero_()
             self.core.metrics_eval.zero_()
@@ -252,8 +275,10 @@ class NativeEngine:
 
     def close(self) -> None:
         torch.cuda.synchronize()
-        self.fused.close()
+        self.fused.check_error()
         self.core.close()
+        self.core.params = self.core.grads = self.core.buffers = None     # views of the arena freed next
+        self.fused.close()
 
 
 class NativeInference:

@@ -65,8 +65,9 @@ class TorchEngine:
             from .parallel.comm import FusedAllReduceAdam
             self.fused = FusedAllReduceAdam(ctx, self.numel, hyper, params=self.flat_p,
                                             m=self.adam.m, v=self.adam.v)
-            # gradients must live in the peer-mapped arena: re-point the .grad views
+            # gradients and master weights must live in the peer-mapped arena: re-point the views
             self._rebind_grads(self.fused.grad_buffer(0))
+            self._rebind_params(self.fused.params)
         self.broadcast_parameters()
         self.steps = 0
 
@@ -78,6 +79,14 @@ class TorchEngine:
             p.grad = flat_g[off: off + n].view(p.shape)
             off += n
         self.flat_g = flat_g
+
+    def _rebind_params(self, flat_p: torch.Tensor) -> None:
+        off = 0
+        for p in self.model.parameters():
+            n = p.numel()
+            p.data = flat_p[off: off + n].view(p.shape)
+            off += n
+        self.flat_p = flat_p
 
     def broadcast_parameters(self) -> None:
         """DDP's constructor broadcast (K-C3): every replica starts from rank 0's values."""

@@ -12,6 +12,7 @@ from typing import Optional
 
 MAX_WORLD = 16
 COMM_MAX_BLOCKS = 256
+REDUCE_MAX = 32
 AUG_NPARAM = 12
 
 _PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -36,6 +37,11 @@ class CommAdamArgs(C.Structure):
         ("out_avg", C.c_void_p),
         ("spin_limit", C.c_ulonglong),
         ("max_blocks", C.c_int),
+        ("range_lo", C.c_longlong), ("range_hi", C.c_longlong),
+        ("bump_step", C.c_int), ("skip_barriers", C.c_int), ("exact_blocks", C.c_int),
+        ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p),
+        ("error_host", C.c_void_p),
+        ("slots", C.c_void_p * MAX_WORLD),
     ]
 
 
@@ -55,7 +61,19 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_comm_adam_step": [C.POINTER(CommAdamArgs), vp],
         "b200dp_comm_adam_grid": [C.POINTER(CommAdamArgs)],
         "b200dp_comm_barrier": [C.POINTER(CommAdamArgs), vp],
-        "b200dp_comm_broadcast": [C.POINTER(CommAdamArgs), i, C.POINTER(vp), vp, ll, vp],
+        "b200dp_comm_broadcast": [C.POINTER(CommAdamArgs), i, C.POINTER(vp), vp, vp, ll, vp],
+        "b200dp_comm_reduce_f64": [C.POINTER(CommAdamArgs), vp, vp, i, i, vp],
+        "b200dp_vmm_query": [C.POINTER(i), C.POINTER(C.c_size_t)],
+        "b200dp_vmm_alloc": [C.c_size_t, C.POINTER(vp), C.POINTER(i), C.POINTER(C.c_ulonglong)],
+        "b200dp_vmm_import": [i, C.c_size_t, C.POINTER(vp)],
+        "b200dp_vmm_free": [vp],
+        "b200dp_mc_create": [i, C.c_size_t, C.POINTER(C.c_ulonglong), C.POINTER(i)],
+        "b200dp_mc_import": [i, C.c_size_t, C.POINTER(C.c_ulonglong)],
+        "b200dp_mc_add_device": [C.c_ulonglong],
+        "b200dp_mc_bind": [C.c_ulonglong, C.c_ulonglong, C.c_size_t],
+        "b200dp_mc_map": [C.c_ulonglong, C.c_size_t, C.POINTER(vp)],
+        "b200dp_mc_release": [C.c_ulonglong],
+        "b200dp_close_fd": [i],
         "b200dp_preprocess": [vp, vp, vp, i, i, i, vp],
         "b200dp_softmax_xent": [vp, vp, vp, vp, vp, i, i, f, vp],
         "b200dp_softmax_topk": [vp, vp, vp, vp, i, i, i, vp],

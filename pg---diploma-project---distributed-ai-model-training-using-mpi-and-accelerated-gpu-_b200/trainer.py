@@ -24,7 +24,7 @@ from .parallel.bootstrap import DistContext, barrier, cleanup, rank_zero_first, 
 from .parallel.sampler import PartitionSampler
 from .utils.checkpoint import load_resume, save_model, save_resume
 from .utils.logging import RankLogger, format_epoch_line
-from .utils.timers import max_over_ranks, sum_over_ranks
+from .utils.timers import PhaseTimer, max_over_ranks, sum_over_ranks
 from .utils.watchdog import Watchdog
 
 
@@ -76,7 +76,8 @@ class Trainer:
         self.start_epoch = 0
         self.history: list = []
         self.watchdog = Watchdog(timeout_s=0.0, rank=self.ctx.rank)
-        if cfg.resume:
+        self.timer = PhaseTimer(enabled=True, cuda=self.ctx.device.type == "cuda")
+        if cfg.resume and os.path.exists(cfg.resume):      # a first run with --resume creates the file
             self._resume(cfg.resume)
 
     @staticmethod
@@ -108,17 +109,49 @@ class Trainer:
         lr = step_lr(cfg.lr, epoch, cfg.lr_step_size, cfg.lr_gamma)
         self.train_loader.set_epoch(epoch)                                # ref :165
         t0 = time.perf_counter()
-        for i, batch in enumerate(self.train_loader):                     # ref :173 hot loop
-            self.engine.train_step(batch, lr)
+        self.timer.reset()
+        it = iter(self.train_loader)
+        i = -1
+        while True:                                                       # ref :173 hot loop
+            i += 1
+            sampled = (i & 63) == 0          # device-time one step in 64: events are cheap, but not free
+            try:
+                if sampled:
+                    with self.timer.phase("data_wait"):
+                        batch = next(it)
+                        batch.wait()
+                else:
+                    batch = next(it)
+            except StopIteration:
+                break
+            if sampled:
+                with self.timer.phase("step"):
+                    self.engine.train_step(batch, lr)
+            else:
+                self.engine.train_step(batch, lr)
             self.watchdog.kick()
             if cfg.check_replicas_every and (i + 1) % cfg.check_replicas_every == 0:
                 self.check_replicas()
             if cfg.log_every and self.ctx.is_main and (i + 1) % cfg.log_every == 0:
                 self.log.print(f"  step {i + 1}/{len(self.train_loader)}")
         loss_sum, correct, count = self.engine.read_metrics()
-        g = sum_over_ranks([loss_sum, correct, count], self.ctx.device)   # K-C6 (ref :188-195), plus accuracy
+        g = self._sum([loss_sum, correct, count])                         # K-C6 (ref :188-195), plus accuracy
         dt = time.perf_counter() - t0
-        return {"loss": g[0] / max(g[2], 1), "acc": g[1] / max(g[2], 1), "images": g[2], "seconds": dt, "lr": lr}
+        ph = self.timer.collect()
+        nsamp = max((i + 63) // 64, 1)
+        return {"loss": g[0] / max(g[2], 1), "acc": g[1] / max(g[2], 1), "images": g[2], "seconds": dt, "lr": lr,
+                "step_ms": ph.get("step", 0.0) / nsamp, "data_wait_ms": ph.get("data_wait", 0.0) / nsamp}
+
+    # ---- small cross-rank reductions: on the engine's peer slot tables when it has them, else torch.distributed
+    def _sum(self, values):
+        if self.ctx.initialized and hasattr(self.engine, "reduce"):
+            return self.engine.reduce(values, "sum")
+        return sum_over_ranks(values, self.ctx.device)
+
+    def _max(self, value: float) -> float:
+        if self.ctx.initialized and hasattr(self.engine, "reduce"):
+            return self.engine.reduce([value], "max")[0]
+        return max_over_ranks(value, self.ctx.device)
 
     def evaluate(self) -> Dict[str, float]:
         self.engine.sync_buffers()                                        # K-C4 semantics (see engine)
@@ -126,20 +159,26 @@ class Trainer:
             self.engine.eval_step(batch)
             self.watchdog.kick()
         loss_sum, correct, count = self.engine.read_metrics()
-        g = sum_over_ranks([loss_sum, correct, count], self.ctx.device)   # K-C7 (ref :216-223)
+        g = self._sum([loss_sum, correct, count])                         # K-C7 (ref :216-223)
         return {"loss": g[0] / max(g[2], 1), "acc": g[1] / max(g[2], 1), "images": g[2]}
 
     def check_replicas(self) -> None:
         """Replicas must hold identical parameters after every fused step (hard part 4)."""
         if not self.ctx.initialized:
             return
-        import torch.distributed as dist
-        h = torch.tensor([self.engine.param_hash()], dtype=torch.float64, device=self.ctx.device)
-        lo, hi = h.clone(), h.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        if lo.item() != hi.item():
-            raise RuntimeError(f"replica divergence: parameter hash spans [{lo.item()!r}, {hi.item()!r}]")
+        h = self.engine.param_hash()
+        if hasattr(self.engine, "reduce"):
+            hi, neg_lo = self.engine.reduce([h, -h], "max")
+            lo = -neg_lo
+        else:
+            import torch.distributed as dist
+            t = torch.tensor([h], dtype=torch.float64, device=self.ctx.device)
+            lo_t, hi_t = t.clone(), t.clone()
+            dist.all_reduce(lo_t, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi_t, op=dist.ReduceOp.MAX)
+            lo, hi = lo_t.item(), hi_t.item()
+        if lo != hi:
+            raise RuntimeError(f"replica divergence: parameter hash spans [{lo!r}, {hi!r}]")
 
     # ---- full run ----------------------------------------------------------------------------
     def fit(self) -> Dict[str, Any]:
@@ -162,13 +201,18 @@ class Trainer:
             ev = self.evaluate()
             if ctx.device.type == "cuda":
                 torch.cuda.synchronize()
-            epoch_time = max_over_ranks(time.perf_counter() - epoch_start, ctx.device)
-            train_time = max_over_ranks(tr["seconds"], ctx.device)
+            epoch_time = self._max(time.perf_counter() - epoch_start)
+            train_time = self._max(tr["seconds"])
             log.print(format_epoch_line(cfg.mode, epoch + 1, cfg.epochs, epoch_time, tr["loss"], tr["acc"],
                                         ev["loss"], ev["acc"]))
             rec = {"epoch": epoch + 1, "epoch_seconds": epoch_time, "train_loss": tr["loss"],
                    "train_acc": tr["acc"], "test_loss": ev["loss"], "test_acc": ev["acc"], "lr": tr["lr"],
-                   "train_images_per_sec": tr["images"] / max(train_time, 1e-9), "world_size": ctx.world_size}
+                   "train_images_per_sec": tr["images"] / max(train_time, 1e-9), "world_size": ctx.world_size,
+                   "step_ms": tr["step_ms"], "data_wait_ms": tr["data_wait_ms"],
+                   # fraction of the measured HBM copy bandwidth the step sustains on its ~11.5 GB of unavoidable
+                   # activation traffic (profiles/step_roofline.md)
+                   "hbm_roofline_fraction": (11.5e9 * self.batch_size / 128 / 6.55e12) / max(tr["step_ms"] * 1e-3, 1e-9)
+                   if tr["step_ms"] > 0 and ctx.device.type == "cuda" else None}
             self.history.append(rec)
             log.json(rec)
             if ev["acc"] > self.best_acc:                                  # ref :238-240
@@ -176,10 +220,11 @@ class Trainer:
                 self.best_state = self.engine.state_dict()
                 if cfg.save_on_improve and ctx.is_main:
                     save_model(self.best_state, self._ckpt_path())
-            if cfg.save_on_improve and ctx.is_main and cfg.resume:
-                save_resume(cfg.resume, epoch=epoch + 1, best_acc=self.best_acc,
-                            optimizer=self.engine.optimizer_state(), model=self.engine.state_dict(),
-                            best_model=self.best_state)
+            if cfg.save_on_improve and cfg.resume:
+                opt_state = self.engine.optimizer_state()          # collective: sharded moments are summed over ranks
+                if ctx.is_main:
+                    save_resume(cfg.resume, epoch=epoch + 1, best_acc=self.best_acc, optimizer=opt_state,
+                                model=self.engine.state_dict(), best_model=self.best_state)
         total = time.perf_counter() - total_start
         self.watchdog.stop()
         log.print(f"\nBest test accuracy: {self.best_acc:.4f}")                # ref :244

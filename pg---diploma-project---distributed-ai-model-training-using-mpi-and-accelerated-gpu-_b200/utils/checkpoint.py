@@ -59,7 +59,7 @@ def save_resume(path: str, *, epoch: int, best_acc: float, optimizer: Dict[str, 
 
 
 def load_resume(path: str) -> Dict[str, Any]:
-    obj = torch.load(path, map_location="cpu", weights_only=False)
+    obj = torch.load(path, map_location="cpu", weights_only=True)      # tensors, numbers, strings, dicts only
     if not isinstance(obj, dict) or obj.get("format") != "b200dp-resume-v1":
         raise ValueError(f"{path} is not a b200dp resume file")
     return obj

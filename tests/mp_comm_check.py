@@ -33,10 +33,17 @@ def main() -> int:
     n = 2_242_624
     hyper = AdamHyper(lr=1e-3)
     p0 = torch.randn(n, device=dev)
-    for algo in ("one_shot", "two_shot"):
+    probe = FusedAllReduceAdam(ctx, 1024, hyper)
+    kind = probe.arena.kind
+    probe.close()
+    if r == 0:
+        print("arena:", kind)
+    algos = ("one_shot", "two_shot", "nvls") if kind == "vmm+nvls" else ("one_shot", "two_shot")
+    for algo in algos:
         for gdtype in (torch.float32, torch.bfloat16):
-            work = torch.zeros(n, dtype=torch.bfloat16, device=dev)
-            fused = FusedAllReduceAdam(ctx, n, hyper, params=p0.clone(), work_bf16=work, grad_dtype=gdtype, algo=algo)
+            if algo == "nvls" and gdtype != torch.float32:
+                continue
+            fused = FusedAllReduceAdam(ctx, n, hyper, params=p0.clone(), work_bf16=algo != "nvls", grad_dtype=gdtype, algo=algo)
             ref_p, ref = p0.clone(), FlatAdam(n, dev, hyper)
             gen = torch.Generator(device=dev).manual_seed(100 + r)
             for step in range(4):
@@ -44,7 +51,16 @@ def main() -> int:
                 fused.grads.copy_(g)
                 gsum = fused.grads.float().clone()
                 dist.all_reduce(gsum)
-                fused.step(1e-3)
+                if step == 3:      # bucketed form: three sub-range launches with a small fixed grid, counter bumps on the last
+                    cuts = [0, 1_000_000, 2_000_000, n]
+                    for i in (2, 1, 0):
+                        a = fused.args
+                        a.range_lo, a.range_hi, a.bump_step, a.exact_blocks = cuts[i], cuts[i + 1], int(i == 0), 16
+                        fused.step(1e-3)
+                    fused.args.range_lo = fused.args.range_hi = fused.args.exact_blocks = 0
+                    fused.args.bump_step = 1
+                else:
+                    fused.step(1e-3)
                 ref.step_torch(ref_p, gsum, 1e-3, grad_scale=1.0 / W)
                 torch.cuda.synchronize()
                 fused.check_error()
@@ -61,17 +77,30 @@ def main() -> int:
             fused.barrier()
             fused.close()
     # broadcast of a parameter-sized vector from rank 0 into every rank's arena
-    fused = FusedAllReduceAdam(ctx, n, hyper, params=p0.clone(), algo="two_shot")
-    src = torch.full((n,), 7.0, device=dev) if r == 0 else torch.zeros(n, device=dev)
-    fused.broadcast([a for a in [fused.args.params[i] for i in range(W)]], src, root=0)
+    fused = FusedAllReduceAdam(ctx, n, hyper, params=p0.clone(), algo="two_shot", extra_numel=4096)
+    fused.params.fill_(7.0 if r == 0 else float(r))
+    fused.extra.fill_(3.0 if r == 0 else -1.0)
+    torch.cuda.synchronize(); dist.barrier()
+    fused.broadcast_params(0)
+    fused.broadcast_extra(0)
     torch.cuda.synchronize()
-    assert torch.all(fused.params == 7.0)
+    assert torch.all(fused.params == 7.0) and torch.all(fused.extra == 3.0)
+    # small double reductions on the peer slot tables (K-C6 / K-C7, timers)
+    got = fused.reduce_f64(torch.tensor([float(r + 1), 10.0 * r, 0.5]), "sum").cpu()
+    assert torch.equal(got, torch.tensor([W * (W + 1) / 2.0, 10.0 * W * (W - 1) / 2, 0.5 * W], dtype=torch.float64))
+    got = fused.reduce_f64(torch.tensor([float(r), -float(r)]), "max").cpu()
+    assert torch.equal(got, torch.tensor([W - 1.0, 0.0], dtype=torch.float64))
+    fused.check_error()
+    fused.close()
     # bus-bandwidth sweep of the fused kernel vs NCCL all-reduce (device-timed, max over ranks)
     if r == 0:
-        print("bytes,fused_us,nccl_us")
-    for nbytes in (64 << 10, 1 << 20, 8 << 20, 64 << 20, 256 << 20):
+        print("bytes,algo,fused_us,nccl_us")
+    sweep = [(nb, al) for nb in (64 << 10, 1 << 20, 8970496, 64 << 20, 256 << 20) for al in algos]
+    if os.environ.get("B200DP_COMM_SWEEP", "1") == "0":
+        sweep = []
+    for nbytes, algo in sweep:
         m = nbytes // 4
-        f = FusedAllReduceAdam(ctx, m, hyper, algo="one_shot" if nbytes <= (16 << 20) else "two_shot")
+        f = FusedAllReduceAdam(ctx, m, hyper, algo=algo)
         t = torch.randn(m, device=dev)
 
         def timed(fn, iters=20):
@@ -89,7 +118,7 @@ def main() -> int:
         fu = timed(lambda: f.step(1e-3))
         nc = timed(lambda: dist.all_reduce(t))
         if r == 0:
-            print(f"{nbytes},{fu:.1f},{nc:.1f}")
+            print(f"{nbytes},{algo},{fu:.1f},{nc:.1f}")
         f.close()
     dist.barrier()
     if r == 0:

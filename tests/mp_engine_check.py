@@ -1,0 +1,89 @@
+"""Multi-rank check of the NATIVE ENGINE (run under b200dp.launch, one rank per GPU).
+
+mode "train": 30 real training steps (preprocess, forward, backward, bucketed all-reduce + Adam inside the step
+graph), each rank on its own data; after every step the parameter hash must be identical on all ranks, and the
+global mean loss per step must match a second run of the same steps with `--comm nccl` (NCCL all-reduce + flat
+Adam, fp32 sums in a different order) to 1e-3 relative.
+mode "fault": rank 1 stops itself (SIGSTOP) after a few steps; every other rank must leave with CommError -- never
+with silently updated weights -- within the barrier's spin limit.
+"""
+import os
+import signal
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from b200dp.config import TrainConfig  # noqa: E402
+from b200dp.data.datasets import SyntheticCIFAR10  # noqa: E402
+from b200dp.data.loader import Batch  # noqa: E402
+from b200dp.data.transforms import sample_aug_params  # noqa: E402
+from b200dp.parallel.bootstrap import cleanup, setup_distributed  # noqa: E402
+from b200dp.trainer import make_engine  # noqa: E402
+
+
+def batches(rank: int, steps: int, B: int, dev):
+    ds = SyntheticCIFAR10(steps * B, True, seed=100 + rank)
+    g = torch.Generator().manual_seed(7 + rank)
+    out = []
+    for i in range(steps):
+        sl = slice(i * B, (i + 1) * B)
+        out.append(Batch(ds.images[sl].to(dev), ds.labels[sl].to(dev), sample_aug_params(B, generator=g).to(dev), B))
+    return out
+
+
+def run(cfg, ctx, data, check_hash: bool):
+    eng = make_engine(cfg, ctx)
+    losses = []
+    for b in data:
+        eng.train_step(b, 1e-3)
+        ls, _, cnt = eng.read_metrics()
+        g = eng.reduce([ls, cnt], "sum")
+        losses.append(g[0] / g[1])
+        if check_hash:
+            h = eng.param_hash()
+            hi, neg_lo = eng.reduce([h, -h], "max")
+            assert hi == -neg_lo, f"replicas diverged at step {len(losses)}: [{-neg_lo!r}, {hi!r}]"
+    info = (eng.comm_algo, eng.fused.arena.kind, eng.in_graph)
+    eng.close()
+    return losses, info
+
+
+def main() -> int:
+    mode = sys.argv[1] if len(sys.argv) > 1 else "train"
+    ctx = setup_distributed()
+    dev, r = ctx.device, ctx.rank
+    B, steps = 16, 30
+    data = batches(r, steps, B, dev)
+    base = dict(mode="ddp", engine="native", batch_size=B, dataset="synthetic", dropout=0.0, seed=3)
+    if mode == "fault":
+        os.environ["B200DP_COMM_SPIN_LIMIT"] = str(20_000_000)
+        eng = make_engine(TrainConfig(**base), ctx)
+        for i, b in enumerate(data * 50):
+            if i == 5 and r == 1:
+                torch.cuda.synchronize()
+                os.kill(os.getpid(), signal.SIGSTOP)      # a stalled rank: its host stops launching steps
+            eng.train_step(b, 1e-3)
+            if i % 8 == 7:
+                eng.read_metrics()
+        print("FAULT NOT DETECTED", flush=True)
+        return 0
+    algos = ["auto", "one_shot", "two_shot"]
+    ref, _ = run(TrainConfig(comm="nccl", **base), ctx, data, False)
+    for algo in algos:
+        got, info = run(TrainConfig(comm="fused", comm_algo=algo, **base), ctx, data, True)
+        worst = max(abs(a - b) / max(abs(b), 1e-6) for a, b in zip(got, ref))
+        if r == 0:
+            print(f"algo={algo} -> {info}: loss {got[0]:.4f} -> {got[-1]:.4f}, max rel diff vs nccl {worst:.2e}", flush=True)
+        assert worst < 1e-3, (algo, worst, got, ref)
+        assert info[2], "the fused optimiser must run inside the step graph"
+    if r == 0:
+        print("ENGINE CHECK OK", flush=True)
+    cleanup(ctx)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

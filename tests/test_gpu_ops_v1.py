@@ -95,8 +95,7 @@ def test_fused_adam_world1_matches_flat_adam(ops, gdtype):
     n = 2_242_624
     hyper = AdamHyper(lr=1e-3, weight_decay=0.01)
     p0 = torch.randn(n, device="cuda")
-    work = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
-    fused = FusedAllReduceAdam(_single_ctx(), n, hyper, params=p0.clone(), work_bf16=work, grad_dtype=gdtype)
+    fused = FusedAllReduceAdam(_single_ctx(), n, hyper, params=p0.clone(), work_bf16=True, grad_dtype=gdtype)
     ref_p = p0.clone()
     ref = FlatAdam(n, "cuda", hyper)
     for step in range(5):
@@ -109,8 +108,22 @@ def test_fused_adam_world1_matches_flat_adam(ops, gdtype):
         assert torch.allclose(fused.params, ref_p, rtol=2e-5, atol=2e-6), step
         assert torch.count_nonzero(fused.grads) == 0              # zero_grad fused in
     assert torch.allclose(fused.m, ref.m, rtol=1e-5, atol=1e-7) and torch.allclose(fused.v, ref.v, rtol=2e-5, atol=1e-9)
-    assert torch.equal(work, fused.params.to(torch.bfloat16))
+    assert torch.equal(fused.work, fused.params.to(torch.bfloat16))
     assert fused.steps == 5
+    # bucketed form: three launches over sub-ranges, the step counter advances on the last one only
+    g = torch.randn(n, device="cuda")
+    fused.grads.copy_(g)
+    gq = fused.grads.float().clone()
+    cuts = [0, 1_000_000, 2_000_000, n]
+    for i in (2, 1, 0):
+        fused.args.range_lo, fused.args.range_hi, fused.args.bump_step, fused.args.exact_blocks = cuts[i], cuts[i + 1], int(i == 0), 8
+        fused.step(1e-4)
+    fused.args.range_lo = fused.args.range_hi = fused.args.exact_blocks = 0
+    fused.args.bump_step = 1
+    ref.step_torch(ref_p, gq, 1e-4)
+    assert torch.allclose(fused.params, ref_p, rtol=2e-5, atol=2e-6) and fused.steps == 6
+    assert torch.count_nonzero(fused.grads) == 0
+    assert torch.equal(fused.reduce_f64(torch.tensor([1.5, 2.0]), "sum").cpu(), torch.tensor([1.5, 2.0], dtype=torch.float64))
     fused.check_error()
     avg = None
     fused.grads.copy_(torch.arange(n, device="cuda") % 7)
@@ -137,7 +150,7 @@ def test_torch_engine_step_on_gpu_uses_native_kernels(ops):
         eng.train_step(b, 1e-3)
         l, c, n = eng.read_metrics()
         losses.append(l / n)
-    assert ops.launch_count() == 16                     # preprocess + fused Adam per step
+    assert ops.launch_count() == 24                     # preprocess + fused Adam + step-count bump per step
     assert not torch.equal(before, eng.flat_p) and losses[-1] < losses[0]
     sd = eng.state_dict()
     assert len(sd) == 314
