@@ -39,9 +39,11 @@ def main() -> int:
     if r == 0:
         print("arena:", kind)
     algos = ("one_shot", "two_shot", "nvls") if kind == "vmm+nvls" else ("one_shot", "two_shot")
-    for algo in algos:
-        for gdtype in (torch.float32, torch.bfloat16):
-            if algo == "nvls" and gdtype != torch.float32:
+    # bucketed = every step as three sub-range launches (the in-graph form).  Ownership of the two-shot slices -- and
+    # with it which rank holds the moments of an element -- depends on the ranges, so a run uses one form throughout.
+    for algo, gdtype, bucketed in [(a, g, b) for a in algos for g in (torch.float32, torch.bfloat16) for b in (False, True)]:
+        if True:
+            if (algo == "nvls" or bucketed) and gdtype != torch.float32:
                 continue
             fused = FusedAllReduceAdam(ctx, n, hyper, params=p0.clone(), work_bf16=algo != "nvls", grad_dtype=gdtype, algo=algo)
             ref_p, ref = p0.clone(), FlatAdam(n, dev, hyper)
@@ -51,7 +53,7 @@ def main() -> int:
                 fused.grads.copy_(g)
                 gsum = fused.grads.float().clone()
                 dist.all_reduce(gsum)
-                if step == 3:      # bucketed form: three sub-range launches with a small fixed grid, counter bumps on the last
+                if bucketed:       # three sub-range launches with a small fixed grid, the step counter bumps after the last
                     cuts = [0, 1_000_000, 2_000_000, n]
                     for i in (2, 1, 0):
                         a = fused.args
@@ -64,9 +66,9 @@ def main() -> int:
                 ref.step_torch(ref_p, gsum, 1e-3, grad_scale=1.0 / W)
                 torch.cuda.synchronize()
                 fused.check_error()
-                assert torch.allclose(fused.params, ref_p, rtol=3e-5, atol=3e-6), (algo, gdtype, step)
+                assert torch.allclose(fused.params, ref_p, rtol=3e-5, atol=3e-6), (algo, gdtype, bucketed, step)
                 assert torch.count_nonzero(fused.grads) == 0
-                assert same_on_all_ranks(fused.params), f"replicas diverged ({algo}, {gdtype}, step {step})"
+                assert same_on_all_ranks(fused.params), f"replicas diverged ({algo}, {gdtype}, {bucketed}, step {step})"
             if fused.work is not None:
                 assert torch.equal(fused.work, fused.params.to(torch.bfloat16))
             # plain all-reduce
