@@ -162,7 +162,7 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
   const long long n4_all = P.numel >> 2;
   const long long r_lo = P.range_hi > 0 ? (P.range_lo >> 2) : 0;
   const long long r_hi = P.range_hi > 0 ? (P.range_hi >> 2) : n4_all;
-  const int step = P.step_state[0];     // advanced by a separate one-thread launch after the LAST launch of a step
+  const int step = P.step_state[0];     // advanced by the last block of the step's LAST launch (bump_step)
   const bool barriers = W > 1 && !P.skip_barriers;
   const unsigned long long limit = P.spin_limit ? P.spin_limit : kDefaultSpin;
   if (already_failed(P)) return;
@@ -263,23 +263,33 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
       }
     }
   }
-  if (threadIdx.x == 0 && barriers) P.epoch_state[blockIdx.x] = epoch + 2;
+  if (P.zero_hi > P.zero_lo) {      // gradients of earlier buckets of this step: every peer is done with them by now
+    float* mine = reinterpret_cast<float*>(const_cast<void*>(P.grads[rank]));
+    for (long long i = (P.zero_lo >> 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (P.zero_hi >> 2); i += stride)
+      zero_grad<GD>(mine, i);
+  }
+  if (threadIdx.x == 0) {
+    if (barriers) P.epoch_state[blockIdx.x] = epoch + 2;
+    if (P.apply_adam && P.bump_step) {
+      // the step count advances when the LAST block of the step's last launch is done: every block has read it by then
+      __threadfence();
+      if (atomicAdd(&P.step_state[1], 1) == (int)gridDim.x - 1) {
+        P.step_state[1] = 0;
+        P.step_state[0] = step + 1;
+      }
+    }
+  }
 }
 
-__global__ void comm_bump_kernel(int* step_state) { step_state[0] += 1; }
-
-// Barrier across ranks; `bump` != 0 also advances the Adam step count (the step's last launch).  With one CTA this
-// is how the in-graph buckets wait: the waiting costs one CTA slot, not the grid of the data launch that follows.
+// Barrier across ranks.  With one CTA this is how the early in-graph buckets wait: the waiting costs one CTA slot,
+// not the grid of the data launch that follows.
 __global__ void __launch_bounds__(kThreads)
-comm_barrier_kernel(const __grid_constant__ b200dp_comm_adam P, int bump) {
+comm_barrier_kernel(const __grid_constant__ b200dp_comm_adam P) {
   const uint32_t epoch = P.epoch_state[blockIdx.x];
   const unsigned long long limit = P.spin_limit ? P.spin_limit : kDefaultSpin;
   if (already_failed(P)) return;
   if (P.world > 1 && !flag_barrier(P, epoch + 2, limit)) return;
-  if (threadIdx.x == 0) {
-    P.epoch_state[blockIdx.x] = epoch + 2;
-    if (bump && blockIdx.x == 0) P.step_state[0] += 1;
-  }
+  if (threadIdx.x == 0) P.epoch_state[blockIdx.x] = epoch + 2;
 }
 
 struct BcastArgs {
@@ -361,7 +371,7 @@ int threads_for(const b200dp_comm_adam& a) {
 int grid_for(const b200dp_comm_adam& a);
 int validate(const b200dp_comm_adam* a);
 }  // namespace
-int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, int bump, cudaStream_t s);
+int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, cudaStream_t s);
 namespace {
 
 int grid_for(const b200dp_comm_adam& a) {
@@ -387,6 +397,9 @@ int validate(const b200dp_comm_adam* a) {
                  "comm_adam: range [%lld, %lld) must be a non-empty multiple-of-4 sub-range of [0, %lld)", a->range_lo,
                  a->range_hi, a->numel);
   B200DP_REQUIRE(a->epoch_state && a->step_state && a->error_flag, "comm_adam: state pointers missing");
+  B200DP_REQUIRE(a->zero_hi == 0 || (a->zero_lo >= 0 && a->zero_lo < a->zero_hi && a->zero_hi <= a->numel &&
+                                     (a->zero_lo & 3) == 0 && (a->zero_hi & 3) == 0 && a->grad_dtype == 0),
+                 "comm_adam: bad extra zero range [%lld, %lld)", a->zero_lo, a->zero_hi);
   for (int r = 0; r < a->world; ++r) {
     B200DP_REQUIRE(a->grads[r] != nullptr, "comm_adam: grads[%d] is null", r);
     if (a->world > 1) B200DP_REQUIRE(a->flags[r] != nullptr, "comm_adam: flags[%d] is null", r);
@@ -436,17 +449,12 @@ int comm_adam_launch(const b200dp_comm_adam& a, cudaStream_t s) {
   } else {
     rc = algo == 0 ? launch_w<1, 0>(a, grid, s) : launch_w<1, 1>(a, grid, s);
   }
-  if (rc != B200DP_OK) return rc;
-  if (a.apply_adam && a.bump_step) {
-    comm_bump_kernel<<<1, 1, 0, s>>>(a.step_state);
-    B200DP_CHECK_LAUNCH();
-  }
-  return B200DP_OK;
+  return rc;
 }
 
-int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, int bump, cudaStream_t s) {
+int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, cudaStream_t s) {
   if (int rc = validate(&a)) return rc;
-  comm_barrier_kernel<<<blocks, kThreads, 0, s>>>(a, bump);
+  comm_barrier_kernel<<<blocks, kThreads, 0, s>>>(a);
   B200DP_CHECK_LAUNCH();
   return B200DP_OK;
 }
@@ -467,7 +475,7 @@ extern "C" int b200dp_comm_adam_step(const b200dp_comm_adam* a, void* stream) {
 
 extern "C" int b200dp_comm_barrier(const b200dp_comm_adam* a, void* stream) {
   if (int rc = validate(a)) return rc;
-  return comm_barrier_launch(*a, grid_for(*a), 0, static_cast<cudaStream_t>(stream));
+  return comm_barrier_launch(*a, grid_for(*a), static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int b200dp_comm_broadcast(const b200dp_comm_adam* a, int root, float* const* dst_by_rank, float* mc_dst,

@@ -23,7 +23,7 @@ extern "C" int b200dp_preprocess(const uint8_t* images, const float* params, voi
                                  int out_channels, void* stream);
 namespace b200dp {
 int comm_adam_launch(const b200dp_comm_adam& a, cudaStream_t s);
-int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, int bump, cudaStream_t s);
+int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, cudaStream_t s);
 }
 extern "C" int b200dp_softmax_xent(const float* logits, const int64_t* labels, float* loss_out, float* dlogits_out,
                                    double* metrics, int batch, int classes, float mean_over, void* stream);
@@ -491,26 +491,30 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       if (se_used) ENG_TRY(order_after(e, se_side, sc));
       sc_used = true;
     }
-    // Waiting and moving data are separate launches: a ONE-CTA barrier kernel absorbs the skew between ranks while
-    // the compute kernels keep every other SM, then a wide, short launch reduces + updates the bucket without
-    // waiting for anybody.  After the last bucket one more barrier tells every rank that its weights are complete
-    // and its gradients have been read; only then are the gradients cleared.
+    // Early buckets: waiting and moving data are separate launches -- a ONE-CTA barrier kernel absorbs the skew
+    // between ranks while the compute kernels keep every other SM, then a wide, short launch reduces + updates the
+    // bucket without waiting for anybody.  The LAST bucket is one launch with both barriers inside: its second
+    // barrier tells every rank that all its weights are complete and all its gradients have been read, so it also
+    // clears the gradients of the earlier buckets and advances the step count.
     b200dp_comm_adam a = e.comm;
     const bool multi = a.world > 1;
-    if (multi) ENG_TRY(comm_barrier_launch(a, 1, 0, sc));
     a.range_lo = lo;
     a.range_hi = bucket_hi;
-    a.skip_barriers = multi ? 1 : 0;
-    a.zero_grads = multi ? 0 : 1;
-    a.bump_step = (last && !multi) ? 1 : 0;
     a.exact_blocks = 0;
     a.max_blocks = e.comm_blocks;
+    if (!last) {
+      if (multi) ENG_TRY(comm_barrier_launch(a, 1, sc));
+      a.skip_barriers = multi ? 1 : 0;
+      a.zero_grads = multi ? 0 : 1;
+      a.bump_step = 0;
+    } else {
+      a.skip_barriers = 0;
+      a.zero_grads = 1;
+      a.bump_step = 1;
+      if (multi && bucket_hi < e.param_total) { a.zero_lo = bucket_hi; a.zero_hi = e.param_total; }
+    }
     ENG_TRY(comm_adam_launch(a, sc));
     mark(e, s, "comm_adam");
-    if (last && multi) {
-      ENG_TRY(comm_barrier_launch(a, 1, 1, sc));
-      B200DP_CUDA(cudaMemsetAsync(e.grads, 0, (size_t)e.param_total * sizeof(float), sc));
-    }
     bucket_hi = lo;
     return B200DP_OK;
   };

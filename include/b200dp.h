@@ -79,7 +79,7 @@ typedef struct b200dp_comm_adam {
   float* m;                                 /* Adam first moment  (local) */
   float* v;                                 /* Adam second moment (local) */
   const float* lr;                          /* device scalar: learning rate for this step */
-  int* step_state;                          /* device int[>= 1]: step_state[0] = completed Adam steps */
+  int* step_state;                          /* device int[2]: [0] = completed Adam steps, [1] = block ticket (0 between launches) */
   uint32_t* epoch_state;                    /* device uint32[B200DP_COMM_MAX_BLOCKS]: barrier epochs */
   int* error_flag;                          /* device int: set non-zero if a barrier spin timed out */
   double beta1, beta2;                      /* doubles: (1 - beta) and the bias corrections match torch.optim.Adam exactly */
@@ -93,12 +93,14 @@ typedef struct b200dp_comm_adam {
   /* ---- bucketed launches (engine.cu launches one per gradient bucket from a branch of the step graph) ---- */
   long long range_lo, range_hi;             /* element sub-range handled by this launch, multiples of 4;
                                                range_hi == 0 means the whole vector */
-  int bump_step;                            /* advance the Adam step count after this launch (the LAST launch of a
-                                               step sets it; done by a one-thread follow-up launch) */
+  int bump_step;                            /* advance the Adam step count when this launch is done (the LAST launch
+                                               of a step sets it) */
   int skip_barriers;                        /* the caller has already waited for the peers with a one-CTA
                                                b200dp_comm_barrier ahead of this launch (in-graph buckets): do not
                                                wait again (zero_grads must then be 0 unless world == 1) */
   int exact_blocks;                         /* > 0: use exactly this grid */
+  long long zero_lo, zero_hi;               /* extra range of this rank's fp32 gradients to clear at the end (after the second
+                                               barrier): the ranges of the step's earlier skip_barriers launches */
   /* ---- NVLS ---- */
   const void* mc_grads;                     /* multicast address of the gradient vector (algo 2) */
   float* mc_params;                         /* multicast address of the master weights (algo 2) */

@@ -39,6 +39,7 @@ class CommAdamArgs(C.Structure):
         ("max_blocks", C.c_int),
         ("range_lo", C.c_longlong), ("range_hi", C.c_longlong),
         ("bump_step", C.c_int), ("skip_barriers", C.c_int), ("exact_blocks", C.c_int),
+        ("zero_lo", C.c_longlong), ("zero_hi", C.c_longlong),
         ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p),
         ("error_host", C.c_void_p),
         ("slots", C.c_void_p * MAX_WORLD),
