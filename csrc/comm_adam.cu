@@ -376,9 +376,11 @@ namespace {
 
 int grid_for(const b200dp_comm_adam& a) {
   if (a.exact_blocks > 0) return a.exact_blocks < B200DP_COMM_MAX_BLOCKS ? a.exact_blocks : B200DP_COMM_MAX_BLOCKS;
+  // sized by the whole range, not by the 1/W slice a rank reduces: the gradient clearing at the end covers the whole
+  // range on every rank, and with one 16-byte element per thread the reduce + Adam loop is a single latency chain
   long long n4 = (a.range_hi > 0 ? a.range_hi - a.range_lo : a.numel) >> 2;
-  if (a.algo >= 1 && a.world > 1) n4 = (n4 + a.world - 1) / a.world;
-  long long blocks = (n4 + (long long)kThreads * 2 - 1) / ((long long)kThreads * 2);
+  if (a.zero_hi > a.zero_lo) n4 += (a.zero_hi - a.zero_lo) >> 2;
+  long long blocks = (n4 + (long long)kThreads * 8 - 1) / ((long long)kThreads * 8);
   int cap = a.max_blocks > 0 ? a.max_blocks : kDefaultBlocks;
   if (cap > B200DP_COMM_MAX_BLOCKS) cap = B200DP_COMM_MAX_BLOCKS;
   if (blocks > cap) blocks = cap;

@@ -33,10 +33,10 @@ class TrainConfig:
                                       # all-gather over peer memory, 2(W-1)/W instead of W-1 gradient volumes per GPU) | nvls (two-shot
                                       # with multimem.ld_reduce / multimem.st through the NVSwitch) | auto = nvls / two_shot for W >= 4
     comm_overlap: bool = True         # run the fused kernel per gradient bucket from a branch of the step graph, overlapped with backward
-    comm_buckets: str = "auto"        # block indices (0..16, descending) at which a new gradient bucket starts; "" = one bucket at
-                                      # the end of backward.  auto = "7" on several GPUs (blocks 7..16 + last conv + classifier = 96 %
-                                      # of the parameters, complete after ~30 % of backward), "" on one GPU (nothing to hide but 15 us
-                                      # of Adam, and every extra launch next to the compute kernels costs about that much)
+    comm_buckets: str = ""            # block indices (0..16, descending) at which a new gradient bucket starts; "" = one bucket,
+                                      # launched at the end of backward.  Measured on 8x B200 (ms/step): one bucket 5.167, buckets
+                                      # "7" (96 % of the parameters reduced after ~30 % of backward) 5.224 -- a bucket launch next to
+                                      # the persistent compute kernels costs more than the 60 us of exposed communication it hides
     comm_blocks: int = 148            # cap on the CTAs of an in-graph bucket launch (wide and short; the waiting is a separate one-CTA launch)
     # ---- data --------------------------------------------------------------
     data_root: str = "./data"
@@ -100,7 +100,7 @@ class TrainConfig:
         if self.comm_algo not in ("auto", "one_shot", "two_shot", "nvls"):
             raise ValueError(f"comm_algo must be auto|one_shot|two_shot|nvls, got {self.comm_algo!r}")
         try:
-            starts = [] if self.comm_buckets == "auto" else [int(x) for x in self.comm_buckets.split(",") if x.strip()]
+            starts = [int(x) for x in self.comm_buckets.split(",") if x.strip()]
         except ValueError:
             raise ValueError(f"comm_buckets must be a comma-separated list of block indices, got {self.comm_buckets!r}")
         if any(not (0 < b < 17) for b in starts) or any(a <= b for a, b in zip(starts, starts[1:])):

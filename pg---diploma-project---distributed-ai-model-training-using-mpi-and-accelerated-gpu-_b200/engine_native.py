@@ -185,8 +185,7 @@ class NativeEngine:
         self.steps = 0
         self.in_graph = (not self.nccl) and cfg.comm_overlap
         if self.in_graph:
-            spec = ("7" if ctx.world_size > 1 else "") if cfg.comm_buckets == "auto" else cfg.comm_buckets
-            starts = [int(x) for x in spec.split(",") if x.strip()]
+            starts = [int(x) for x in cfg.comm_buckets.split(",") if x.strip()]
             self.comm_buckets = starts
             self.core.set_comm(self.fused, starts, cfg.comm_blocks)
         if self.nccl:
