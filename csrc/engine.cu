@@ -25,6 +25,9 @@ namespace b200dp {
 int comm_adam_launch(const b200dp_comm_adam& a, cudaStream_t s);
 int comm_barrier_launch(const b200dp_comm_adam& a, int blocks, cudaStream_t s);
 }
+extern "C" int b200dp_preprocess_col(const uint8_t* images, const float* params, void* col_bf16, float* asum, int batch,
+                                     int size, void* stream);
+extern "C" int b200dp_preprocess_col_supported(int size);
 extern "C" int b200dp_softmax_xent(const float* logits, const int64_t* labels, float* loss_out, float* dlogits_out,
                                    double* metrics, int batch, int classes, float mean_over, void* stream);
 
@@ -84,6 +87,7 @@ struct Engine {
   // stem as a GEMM (B200DP_STEM=simt: the CUDA-core stem kernels): im2col matrix, bf16 weights (plain + block
   // diagonal), column sums of the im2col matrix, [32][32] gradient scratch
   bool stem_gemm = true;
+  bool fuse_col = true;     // preprocess writes the im2col matrix directly (B200DP_FUSE_COL=0: image, then an im2col pass)
   int stem_pack = 1;
   __nv_bfloat16 *x0col = nullptr, *stem_w = nullptr;
   float *stem_asum = nullptr, *stem_dw = nullptr;
@@ -388,11 +392,17 @@ int forward(Engine& e, Plans& pl, int n, bool train, bool has_aug, cudaStream_t 
                                   e.eps, c.coef_f, c.coutp, s));
     mark(e, s, "bn_eval_coef");
   }
-  if (!pre) ENG_TRY(b200dp_preprocess(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0, n, e.S, 4, s));
+  // input pipeline: straight into the stem's im2col matrix when the stem is a GEMM (no 224x224 image in between)
+  const bool fused_col = !pre && e.stem_gemm && e.fuse_col;
+  if (fused_col)
+    ENG_TRY(b200dp_preprocess_col(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0col, train ? e.stem_asum : nullptr,
+                                  n, e.S, s));
+  else if (!pre)
+    ENG_TRY(b200dp_preprocess(e.in_images, (train && has_aug) ? e.in_aug : nullptr, e.x0, n, e.S, 4, s));
   mark(e, s, "preprocess");
   Conv& st = e.convs[0];
   if (e.stem_gemm) {
-    ENG_TRY(stem_im2col_launch(e.x0, e.x0col, train ? e.stem_asum : nullptr, n, e.S, e.S, s));
+    if (!fused_col) ENG_TRY(stem_im2col_launch(e.x0, e.x0col, train ? e.stem_asum : nullptr, n, e.S, e.S, s));
     mark(e, s, "stem_im2col", 0);
     ENG_TRY(order_after(e, sw, s));
     ENG_TRY(pw_gemm_launch(train ? pl.fwd[0] : pl.fwd_eval[0], s));
@@ -706,6 +716,8 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
     const char* st = getenv("B200DP_STEM");
     e->stem_gemm = !(st != nullptr && std::string(st) == "simt");
     e->stem_pack = e->pw_pack ? 2 : 1;        // K = N = 32: two pixels per 128-byte row
+    e->fuse_col = b200dp_preprocess_col_supported(img_size) != 0 &&
+                  !(getenv("B200DP_FUSE_COL") != nullptr && atoi(getenv("B200DP_FUSE_COL")) == 0);
   }
   if (e->pw_pack) {
     for (auto& c : e->convs) {

@@ -162,6 +162,17 @@ int b200dp_close_fd(int fd);
 int b200dp_preprocess(const uint8_t* images, const float* params, void* out_bf16, int batch,
                       int size, int out_channels, void* stream);
 
+/* The same pipeline fused with the stem convolution's im2col: col = bf16 [batch * (size/2)^2][32] rows of the 27 taps
+ * (ky, kx, channel) of the 3x3 stride-2 stem + 5 zeros, never materialising the image; asum (may be NULL) fp32 [32] +=
+ * column sums of the matrix.  b200dp_preprocess_col_supported(size) says whether the working set fits (size <= 224). */
+int b200dp_preprocess_col(const uint8_t* images, const float* params, void* col_bf16, float* asum, int batch, int size,
+                          void* stream);
+int b200dp_preprocess_col_supported(int size);
+/* Inference on full-resolution photographs: PIL-style anti-aliased bilinear Resize((size, size)) + ToTensor + Normalize of
+ * uint8 [batch][H][W][3] -> bf16 [batch][size][size][4] (what cifar10_128batch.py:157-165 and the Gradio app of
+ * GROUP03.pdf p.26-27 do on the CPU with torchvision.transforms). */
+int b200dp_resize_normalize(const uint8_t* src, int batch, int H, int W, void* out_bf16, int size, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Classifier head (K7-K11, K15).
  *   reference: adaptive_avg_pool2d -> Dropout(0.2) -> Linear(1280,10) -> CrossEntropyLoss ->

@@ -281,7 +281,12 @@ class NativeEngine:
 
 
 class NativeInference:
-    """Eval-mode forward on the native kernels (BatchNorm folded into scale/shift on load)."""
+    """Eval-mode forward on the native kernels (BatchNorm folded into scale/shift on load).
+
+    Two inputs: ``logits(uint8 [B,32,32,3])`` -- CIFAR-sized images through the fused resize / im2col kernel, the
+    evaluation path of training -- and ``logits_preprocessed(bf16 [B,224,224,4])`` for photographs that were resized
+    from their ORIGINAL resolution by ``ops.resize_normalize`` (what the reference's predict helper and Gradio app do,
+    cifar10_128batch.py:157-165, GROUP03.pdf p.26-27).  Both replay a CUDA graph per batch size."""
 
     def __init__(self, num_classes: int, device: torch.device, state_dict: Optional[dict], batch: int = 256) -> None:
         if not available():
@@ -292,6 +297,7 @@ class NativeInference:
             state_dict = build_model(num_classes).state_dict()
         self.core.load_state_dict(state_dict)
         self.batch = batch
+        self._labels = torch.zeros(batch, dtype=torch.int64, device=device)
 
     @torch.no_grad()
     def logits(self, images_u8: torch.Tensor) -> torch.Tensor:
@@ -299,7 +305,20 @@ class NativeInference:
         for s in range(0, images_u8.shape[0], self.batch):
             chunk = images_u8[s: s + self.batch].contiguous()
             n = chunk.shape[0]
-            labels = torch.zeros(n, dtype=torch.int64, device=self.device)
-            self.core.eval_step(chunk, labels, n)
+            self.core.eval_step(chunk, self._labels, n)
             outs.append(self.core.logits[:n].clone())
         return torch.cat(outs)
+
+    @torch.no_grad()
+    def logits_preprocessed(self, x: torch.Tensor, clone: bool = True) -> torch.Tensor:
+        """x: normalised bf16 NHWC [B,224,224,4] on the device."""
+        outs = []
+        for s in range(0, x.shape[0], self.batch):
+            chunk = x[s: s + self.batch].contiguous()
+            n = chunk.shape[0]
+            self.core.forward_preprocessed(chunk, n)
+            outs.append(self.core.logits[:n].clone() if clone else self.core.logits[:n])
+        return outs[0] if len(outs) == 1 else torch.cat(outs)
+
+    def close(self) -> None:
+        self.core.close()

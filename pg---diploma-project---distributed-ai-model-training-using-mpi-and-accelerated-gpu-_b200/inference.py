@@ -7,11 +7,14 @@
   ``torch.load`` the checkpoint, strict ``load_state_dict``, ``eval()``; then ``predict(PIL image)
   -> {class: prob}`` for the top 3.
 
-Differences on purpose: ImageNet normalisation (the Gradio app uses CIFAR statistics although the
-model was trained with ImageNet ones -- SURVEY §2.1 quirks); any image size is accepted (it is
-resampled to the 32x32 source grid the training pipeline upsamples from when larger, matching how
-CIFAR images reach the network).  On a GPU the forward runs on the native engine in eval mode
-(BatchNorm folded into scale/shift), else on ATen ops.
+The image goes through the reference's inference transform: ``Resize((224, 224))`` of the ORIGINAL
+image (PIL's anti-aliased bilinear), ``ToTensor``, ``Normalize`` (cifar10_128batch.py:42-47, :157).
+On a GPU that is one kernel (``ops.resize_normalize``), the forward runs on the native engine in
+eval mode (BatchNorm folded into scale/shift) and softmax + top-k is the ``softmax_topk`` kernel;
+on the CPU it is PIL + ATen, i.e. the reference's own path.
+
+Difference on purpose: ImageNet normalisation everywhere (the Gradio app uses CIFAR statistics
+although the model was trained with ImageNet ones -- SURVEY §2.1 quirks).
 """
 from __future__ import annotations
 
@@ -24,28 +27,34 @@ from .models.mobilenetv2 import MobileNetV2
 from .utils.checkpoint import load_model
 
 
-def _to_u8_32(img) -> torch.Tensor:
-    """PIL image / ndarray / tensor -> uint8 [32,32,3] (RGB)."""
+def _to_u8_hwc(img) -> torch.Tensor:
+    """PIL image / ndarray / tensor -> uint8 [H,W,3] (RGB) at its own resolution."""
     import numpy as np
     try:
         from PIL import Image
     except Exception:  # pragma: no cover
         Image = None
     if Image is not None and isinstance(img, Image.Image):
-        img = img.convert("RGB")                                  # ref 128batch:164
-        if img.size != (32, 32):
-            img = img.resize((32, 32), Image.BILINEAR)
-        arr = np.asarray(img, dtype=np.uint8)
+        arr = np.asarray(img.convert("RGB"), dtype=np.uint8)      # ref 128batch:164
     else:
-        arr = np.asarray(img)
+        arr = np.asarray(img.cpu() if isinstance(img, torch.Tensor) else img)
         if arr.ndim == 2:
             arr = np.stack([arr] * 3, axis=-1)
-        if arr.shape[:2] != (32, 32):
-            t = torch.from_numpy(arr.astype("float32")).permute(2, 0, 1)[None]
-            t = torch.nn.functional.interpolate(t, size=(32, 32), mode="bilinear", align_corners=False)
-            arr = t[0].permute(1, 2, 0).round().clamp(0, 255).to(torch.uint8).numpy()
         arr = arr.astype(np.uint8)[..., :3]
     return torch.from_numpy(np.ascontiguousarray(arr))
+
+
+_MEAN = torch.tensor([0.485, 0.456, 0.406]).view(3, 1, 1)
+_STD = torch.tensor([0.229, 0.224, 0.225]).view(3, 1, 1)
+
+
+def reference_transform(img_hwc_u8: torch.Tensor, size: int = 224) -> torch.Tensor:
+    """The reference's test transform on the CPU: PIL ``Resize((size, size))`` + ToTensor + Normalize -> fp32 [3,S,S]."""
+    from PIL import Image
+    pil = Image.fromarray(img_hwc_u8.numpy()).resize((size, size), Image.BILINEAR)
+    import numpy as np
+    x = torch.from_numpy(np.asarray(pil, dtype=np.uint8).copy()).permute(2, 0, 1).float() / 255.0
+    return (x - _MEAN) / _STD
 
 
 class Predictor:
@@ -71,7 +80,7 @@ class Predictor:
 
     @torch.no_grad()
     def logits(self, images_u8: torch.Tensor) -> torch.Tensor:
-        """uint8 [B,32,32,3] -> fp32 logits [B, classes]."""
+        """uint8 [B,32,32,3] (CIFAR-sized) -> fp32 logits [B, classes]: the evaluation path of training."""
         if self._native is not None:
             return self._native.logits(images_u8.to(self.device))
         from .data.transforms import apply_pipeline_torch
@@ -79,13 +88,33 @@ class Predictor:
         return self.model(x).float()
 
     @torch.no_grad()
+    def image_logits(self, img) -> torch.Tensor:
+        """One image of any size -> fp32 logits [classes], through Resize((224, 224)) of the original."""
+        hwc = _to_u8_hwc(img)
+        if self._native is not None:
+            from . import ops
+            x = ops.resize_normalize(hwc[None].to(self.device), 224)
+            return self._native.logits_preprocessed(x)[0]
+        x = reference_transform(hwc)[None].to(self.device)
+        return self.model(x).float()[0]
+
+    @torch.no_grad()
     def probabilities(self, img) -> torch.Tensor:
-        x = _to_u8_32(img)[None]
-        return torch.softmax(self.logits(x)[0], dim=0).cpu()         # ref 128batch:170
+        lg = self.image_logits(img)
+        if self._native is not None:
+            from . import ops
+            return ops.softmax_topk(lg[None].contiguous(), 1)[0][0].cpu()
+        return torch.softmax(lg, dim=0).cpu()                        # ref 128batch:170
 
     def topk(self, img, k: int = 3) -> List[Tuple[str, float]]:
-        p = self.probabilities(img)
-        conf, idx = torch.topk(p, k=min(k, p.numel()))               # ref 128batch:172
+        lg = self.image_logits(img)
+        k = min(k, lg.numel())
+        if self._native is not None:                                 # softmax + top-k on the device (K15)
+            from . import ops
+            _, conf, idx = ops.softmax_topk(lg[None].contiguous(), k)
+            conf, idx = conf[0].cpu(), idx[0].cpu()
+        else:
+            conf, idx = torch.topk(torch.softmax(lg, dim=0).cpu(), k=k)     # ref 128batch:170-172
         return [(self.classes[i], float(c)) for c, i in zip(conf.tolist(), idx.tolist())]
 
     def predict(self, img) -> Dict[str, float]:
@@ -102,15 +131,14 @@ def predict_cifar10_image(img_path: Union[str, "object"], topk: int = 3, conf_th
     img = Image.open(img_path).convert("RGB") if isinstance(img_path, (str, bytes)) else img_path
     results = predictor.topk(img, topk)
     best_label, best_conf = results[0]
-    if not quiet:
-        print(f"\nImage: {img_path}")
-        print("Top predictions:")
+    if not quiet:                                                    # the reference's printout, ref 128batch:176-186
+        print("Top-{} predictions:".format(topk))
         for label, conf in results:
-            print(f"  {label:10s}: {conf:.3f}")
+            print(f"  {label}: {conf:.3f}")
         if best_conf < conf_threshold:
-            print(f"Model is uncertain (max confidence {best_conf:.3f} < {conf_threshold}).")
+            print(f"Prediction uncertain (best_conf={best_conf:.3f} < {conf_threshold})")
         else:
-            print(f"Predicted: {best_label} (confidence {best_conf:.3f})")
+            print(f"Predicted: {best_label} confidence: {best_conf:.3f}")
     return results
 
 

@@ -61,6 +61,35 @@ def preprocess(images_u8: torch.Tensor, params: Optional[torch.Tensor] = None, s
     return out
 
 
+def preprocess_col(images_u8: torch.Tensor, params: Optional[torch.Tensor] = None, size: int = 224,
+                   want_sums: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """uint8 [B,32,32,3] -> the stem's im2col matrix, bf16 [B*(size/2)^2, 32] (27 taps in (ky, kx, channel) order + 5
+    zeros), without materialising the image; optionally the fp32 [32] column sums."""
+    lib = _lib.require()
+    _chk(images_u8, torch.uint8, "images")
+    B = images_u8.shape[0]
+    if params is not None:
+        _chk(params, torch.float32, "params")
+    col = torch.empty((B * (size // 2) ** 2, 32), dtype=torch.bfloat16, device=images_u8.device)
+    sums = torch.zeros(32, dtype=torch.float32, device=images_u8.device) if want_sums else None
+    check(lib.b200dp_preprocess_col(ptr(images_u8), ptr(params), ptr(col), ptr(sums), B, size, current_stream()))
+    return col, sums
+
+
+def resize_normalize(images_u8: torch.Tensor, size: int = 224, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 [B,H,W,3] of any size -> normalised bf16 NHWC [B,size,size,4]: PIL-style anti-aliased bilinear resize,
+    ToTensor, Normalize (the reference's inference transform on the original image)."""
+    lib = _lib.require()
+    _chk(images_u8, torch.uint8, "images")
+    if images_u8.dim() != 4 or images_u8.shape[-1] != 3:
+        raise ValueError(f"images: expected [B,H,W,3], got {tuple(images_u8.shape)}")
+    B, H, W = images_u8.shape[:3]
+    if out is None:
+        out = torch.empty((B, size, size, 4), dtype=torch.bfloat16, device=images_u8.device)
+    check(lib.b200dp_resize_normalize(ptr(images_u8), B, H, W, ptr(out), size, current_stream()))
+    return out
+
+
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, metrics: Optional[torch.Tensor] = None,
                  want_grad: bool = True, mean_over: Optional[float] = None
                  ) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:

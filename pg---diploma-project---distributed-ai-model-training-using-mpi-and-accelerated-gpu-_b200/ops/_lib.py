@@ -76,6 +76,9 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_mc_release": [C.c_ulonglong],
         "b200dp_close_fd": [i],
         "b200dp_preprocess": [vp, vp, vp, i, i, i, vp],
+        "b200dp_preprocess_col": [vp, vp, vp, vp, i, i, vp],
+        "b200dp_preprocess_col_supported": [i],
+        "b200dp_resize_normalize": [vp, i, i, i, vp, i, vp],
         "b200dp_softmax_xent": [vp, vp, vp, vp, vp, i, i, f, vp],
         "b200dp_softmax_topk": [vp, vp, vp, vp, i, i, i, vp],
         "b200dp_pw_gemm": [i, i, i, i, i, vp, i, vp, vp, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],

@@ -207,3 +207,56 @@ def test_engine_odd_shapes(env, batch, n, img):
     assert all(v == v for v in m) and m[2] == n
     assert torch.isfinite(core.grads).all() and float(core.grads.abs().sum()) > 0
     core.close()
+
+
+def test_resize_normalize_matches_pil(env):
+    """Full-resolution inference input: the device resize against PIL Resize((224,224)) + ToTensor + Normalize
+    (the reference's transform, cifar10_128batch.py:42-47), for shrinking, stretching and enlarging."""
+    ops, _ = env
+    from b200dp.inference import reference_transform
+    g = torch.Generator().manual_seed(0)
+    for H, W in ((375, 500), (224, 224), (32, 32), (600, 97), (100, 333)):
+        # smooth image + noise: anti-aliasing matters
+        yy, xx = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+        base = torch.stack([(yy * 3 + xx) % 256, (xx * 2) % 256, (yy + xx * 5) % 256], -1).float()
+        img = (base * 0.7 + 80 * torch.rand(H, W, 3, generator=g)).clamp(0, 255).to(torch.uint8)
+        ref = reference_transform(img)                                           # fp32 [3,224,224]
+        got = ops.resize_normalize(img[None].cuda())[0, ..., :3].permute(2, 0, 1).float().cpu()
+        std = torch.tensor([0.229, 0.224, 0.225]).view(3, 1, 1) * 255
+        d = (got - ref).abs() * std                                              # in 8-bit levels
+        assert d.mean() < 0.6 and (d > 2.5).float().mean() < 2e-3, (H, W, float(d.mean()), float(d.max()))
+
+
+def test_predictor_full_resolution_top3_matches_torchvision(env):
+    """A 500x375 photograph: native Predictor (device resize, native eval forward, device softmax+top-k) against
+    torchvision Resize((224,224)) + the fp32 torch model, top-3 classes and probabilities."""
+    import torchvision
+    from PIL import Image
+    from b200dp.inference import Predictor, reference_transform
+    torch.manual_seed(11)
+    tv = torchvision.models.mobilenet_v2(weights=None)
+    tv.classifier[1] = torch.nn.Linear(tv.last_channel, 10)                      # ref :138-139
+    with torch.no_grad():
+        for m in tv.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.uniform_(-0.2, 0.2); m.running_var.uniform_(0.6, 1.4)
+        tv.classifier[1].weight.mul_(8.0)                                        # a peaked, non-degenerate softmax
+    tv.eval()
+    pred = Predictor(state_dict=tv.state_dict(), device="cuda", engine="native")
+    g = torch.Generator().manual_seed(2)
+    yy, xx = torch.meshgrid(torch.arange(375), torch.arange(500), indexing="ij")
+    img = torch.stack([(yy + 2 * xx) % 256, (3 * yy) % 256, (yy * xx // 50) % 256], -1).float()
+    img = (img * 0.6 + 100 * torch.rand(375, 500, 3, generator=g)).clamp(0, 255).to(torch.uint8)
+    pil = Image.fromarray(img.numpy())
+    got = pred.topk(pil, 3)
+    with torch.no_grad():
+        ref_p = torch.softmax(tv(reference_transform(img)[None])[0], 0)
+    rc, ri = torch.topk(ref_p, 3)
+    assert [n for n, _ in got][0] == pred.classes[int(ri[0])]
+    got_d = dict(got)
+    for c, i in zip(rc.tolist(), ri.tolist()):
+        name = pred.classes[i]
+        if c > 0.05:
+            assert name in got_d and abs(got_d[name] - c) < 2e-2, (name, c, got)
+    full = pred.probabilities(pil)
+    assert abs(float(full.sum()) - 1) < 1e-4 and (full - ref_p).abs().max() < 2e-2

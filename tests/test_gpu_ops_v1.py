@@ -55,6 +55,33 @@ def test_preprocess_augment_matches_torch(ops):
     assert d.mean() < 0.5
 
 
+def _im2col_ref(x):
+    """NHWC bf16 image [B,S,S,4] -> rows of the 3x3 stride-2 pad-1 taps in (ky, kx, channel) order, 27 + 5 zeros."""
+    B, S = x.shape[0], x.shape[1]
+    xp = torch.nn.functional.pad(x[..., :3].float(), (0, 0, 1, 1, 1, 1))            # pad W and H by one
+    taps = [xp[:, ky:ky + S:2, kx:kx + S:2, :] for ky in range(3) for kx in range(3)]  # 9 x [B, S/2, S/2, 3]
+    col = torch.cat(taps, dim=-1).reshape(B * (S // 2) ** 2, 27)
+    return torch.nn.functional.pad(col, (0, 5))
+
+
+@pytest.mark.parametrize("size", [224, 64])
+def test_preprocess_col_equals_im2col_of_preprocess(ops, size):
+    """The fused input kernel (image never materialised) against the unfused pair: preprocess, then im2col in torch."""
+    from b200dp.data.datasets import SyntheticCIFAR10
+    from b200dp.data.transforms import identity_params, sample_aug_params
+    img = SyntheticCIFAR10(24, True).images.cuda()
+    p = sample_aug_params(24, torch.Generator().manual_seed(5), size=size)
+    p[3] = identity_params(1)[0]
+    for params in (None, p.cuda()):
+        ref = _im2col_ref(ops.preprocess(img, params, size=size, channels=4))
+        col, sums = ops.preprocess_col(img, params, size=size, want_sums=True)
+        d = (col.float() - ref).abs()
+        assert (d > 0).float().mean() < 2e-4, (float(d.max()), float((d > 0).float().mean()))   # fused-multiply-add ties
+        assert d.max() < 0.2
+        assert torch.allclose(sums, col.float().sum(0), rtol=1e-3, atol=0.5)
+        assert torch.all(col[:, 27:] == 0)
+
+
 def test_softmax_xent_matches_torch(ops):
     torch.manual_seed(0)
     for B, C in ((128, 10), (40, 10), (7, 1000)):
