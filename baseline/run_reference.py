@@ -44,7 +44,9 @@ def main(ns) -> dict:
                 return {"impl": "reference", "unavailable": "no reference scripts: baseline/_ref, /root/reference and baseline/reference_scripts.tar.gz all absent"}
         except Exception as e:
             return {"impl": "reference", "unavailable": f"reference install failed: {e}"}
-    script = os.path.join(ref, "cifar10_128batch.py" if ns.gpus == 1 else "cifar10_mpi_mobilenet_224.py")
+    cpu_mode = bool(getattr(ns, "cpu", False))       # BASELINE.json config 1: the serial CPU script, batch 64
+    script = os.path.join(ref, "cifar10_serial_mobilenet_224.py" if cpu_mode else
+                          ("cifar10_128batch.py" if ns.gpus == 1 else "cifar10_mpi_mobilenet_224.py"))
     try:
         import torch
         import torchvision
@@ -52,11 +54,11 @@ def main(ns) -> dict:
         import numpy as np
     except Exception as e:
         return {"impl": "reference", "unavailable": f"missing dependency: {e}"}
-    if not torch.cuda.is_available():
+    if not cpu_mode and not torch.cuda.is_available():
         return {"impl": "reference", "unavailable": "no CUDA device"}
     import torch.distributed as dist
 
-    W, K, B = max(ns.warmup, 3), ns.steps, 128
+    W, K, B = max(ns.warmup, 3), ns.steps, (64 if cpu_mode else 128)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     if world != ns.gpus:
@@ -111,7 +113,11 @@ def main(ns) -> dict:
     state = {"n": 0, "e0": None, "e1": None}
     _orig_step = torch.optim.Adam.step
 
+    import time as _time
+
     def sync_all():
+        if cpu_mode:
+            return
         torch.cuda.synchronize()
         if dist.is_initialized():
             dist.barrier()
@@ -122,11 +128,17 @@ def main(ns) -> dict:
         state["n"] += 1
         if state["n"] == W:
             sync_all()
-            state["e0"] = torch.cuda.Event(enable_timing=True)
-            state["e0"].record()
+            if cpu_mode:
+                state["e0"] = _time.perf_counter()
+            else:
+                state["e0"] = torch.cuda.Event(enable_timing=True)
+                state["e0"].record()
         elif state["n"] == W + K:
-            state["e1"] = torch.cuda.Event(enable_timing=True)
-            state["e1"].record()
+            if cpu_mode:
+                state["e1"] = _time.perf_counter()
+            else:
+                state["e1"] = torch.cuda.Event(enable_timing=True)
+                state["e1"].record()
             sync_all()
             raise _Done()
         return out
@@ -147,7 +159,7 @@ def main(ns) -> dict:
         torch.optim.Adam.step = _orig_step
     if state["e1"] is None:
         return {"impl": "reference", "unavailable": f"reference stopped after {state['n']} optimiser steps"}
-    ms = state["e0"].elapsed_time(state["e1"])
+    ms = (state["e1"] - state["e0"]) * 1e3 if cpu_mode else state["e0"].elapsed_time(state["e1"])
     if dist.is_initialized():
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -165,5 +177,5 @@ def main(ns) -> dict:
         "config": {"model": "MobileNetV2 (10-class head) @224", "global_batch": B * world, "per_rank_batch": B,
                    "parallelism": f"dp{world}", "script": os.path.basename(script), "optimizer": "Adam lr=1e-4"},
         "e2e": {"value": value, "unit": "images/sec", "note": "the reference's own loop body is end to end (CPU transforms + pageable H2D + .item() reads)"},
-        "vs_baseline": None,
+        "vs_baseline": None, "device": "cpu" if cpu_mode else "cuda",
     }

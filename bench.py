@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--comm-blocks", type=int, default=0, help="CTAs per in-graph bucket launch")
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu", action="store_true",
+                    help="BASELINE.json config 1 (serial CPU, batch 64): --impl reference runs cifar10_serial_mobilenet_224.py, "
+                         "the default impl runs `--mode cpu` of this framework; host wall clock, no GPU needed")
     return ap.parse_args()
 
 
@@ -164,6 +167,41 @@ def run_b200dp(ns) -> dict:
     return out if ctx.is_main else {}
 
 
+def run_cpu(ns) -> dict:
+    """Mode 1 of this framework (serial CPU, ATen ops, batch 64) on the same synthetic data as the reference arm."""
+    import torch
+
+    from b200dp.config import TrainConfig
+    from b200dp.data.datasets import SyntheticCIFAR10
+    from b200dp.data.loader import BatchLoader
+    from b200dp.parallel.bootstrap import RankInfo, setup_distributed
+    from b200dp.parallel.sampler import PartitionSampler
+    from b200dp.trainer import make_engine
+
+    W, K, B = max(ns.warmup, 3), ns.steps, 64
+    cfg = TrainConfig(mode="cpu", engine="torch", batch_size=B, dataset="synthetic")
+    ctx = setup_distributed(info=RankInfo(0, 1, 0, "single"), use_cuda=False)
+    ds = SyntheticCIFAR10((W + K) * B, train=True)
+    engine = make_engine(cfg, ctx)
+    loader = BatchLoader(ds, PartitionSampler(len(ds), 1, 0, shuffle=True), B, ctx.device, train=True, augment=True, seed=cfg.seed,
+                         cpu_pipeline=cfg.img_size)
+    it = iter(loader)
+    for _ in range(W):
+        engine.train_step(next(it), cfg.lr)
+        engine.read_metrics(reset=False)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        engine.train_step(next(it), cfg.lr)
+        engine.read_metrics(reset=False)
+    dt = time.perf_counter() - t0
+    return {"metric": "MobileNetV2@224 serial-CPU train images/sec", "value": K * B / dt, "unit": "images/sec", "n_gpus": 0,
+            "steps": K, "warmup": W, "ms_per_step": dt / K * 1e3, "higher_is_better": True, "dtype": "fp32", "impl": "b200dp",
+            "engine": engine.name, "device": "cpu", "threads": torch.get_num_threads(),
+            "data": "synthetic CIFAR-10-shaped uint8 32x32x3, random-init weights",
+            "config": {"model": "MobileNetV2 (10-class head) @224", "global_batch": B, "per_rank_batch": B, "parallelism": "serial"},
+            "vs_baseline": (K * B / dt) / 32.4}      # BASELINE.md section 2: the reference's logged serial-CPU train images/sec (upper bound)
+
+
 def run_reference(ns) -> dict:
     try:
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
@@ -175,7 +213,7 @@ def run_reference(ns) -> dict:
 
 def main() -> int:
     ns = parse_args()
-    out = run_reference(ns) if ns.impl == "reference" else run_b200dp(ns)
+    out = run_reference(ns) if ns.impl == "reference" else (run_cpu(ns) if ns.cpu else run_b200dp(ns))
     if out:
         print(json.dumps(out), flush=True)
     return 0

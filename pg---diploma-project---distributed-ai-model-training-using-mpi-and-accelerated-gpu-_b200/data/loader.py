@@ -34,6 +34,7 @@ class Batch:
     params: torch.Tensor      # float32 [n,12] augmentation parameters
     n: int
     ready: Optional["torch.cuda.Event"] = None   # recorded on the copy stream; wait before use
+    x: Optional[torch.Tensor] = None             # CPU mode: the transformed fp32 [n,3,S,S] input, made by the loader thread
 
     def wait(self, stream: Optional["torch.cuda.Stream"] = None) -> "Batch":
         """Make ``stream`` (default: current) wait for the H2D copies, and tell the caching allocator that the
@@ -52,7 +53,7 @@ class Batch:
 class BatchLoader:
     def __init__(self, dataset: ArrayDataset, sampler: PartitionSampler, batch_size: int,
                  device: torch.device, train: bool, augment: bool = True, drop_last: bool = False,
-                 seed: int = 0, prefetch: int = 2, max_batches: int = 0) -> None:
+                 seed: int = 0, prefetch: int = 2, max_batches: int = 0, cpu_pipeline: int = 0) -> None:
         self.ds = dataset
         self.sampler = sampler
         self.batch_size = int(batch_size)
@@ -63,6 +64,9 @@ class BatchLoader:
         self.seed = seed
         self.prefetch = max(1, prefetch)
         self.max_batches = max_batches
+        # CPU mode: image size for which a background thread runs the transform pipeline one batch ahead of the
+        # training step -- the role of the reference's DataLoader workers (ref :126-133); 0 = leave it to the engine
+        self.cpu_pipeline = int(cpu_pipeline) if self.device.type == "cpu" else 0
         self.resident = dataset.images.device.type == "cuda"
         self._copy_stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
         self._staging: List[dict] = []
@@ -90,6 +94,9 @@ class BatchLoader:
             batches = batches[: self.max_batches]
         gen = self._gen()
         if self.device.type != "cuda":
+            if self.cpu_pipeline:
+                yield from self._iter_cpu_ahead(batches, gen)
+                return
             for idx in batches:
                 yield Batch(self.ds.images.index_select(0, idx), self.ds.labels.index_select(0, idx),
                             self._params(idx.numel(), gen), idx.numel())
@@ -101,6 +108,44 @@ class BatchLoader:
                             self._params(idx.numel(), gen).to(self.device, non_blocking=True), idx.numel())
             return
         yield from self._iter_pinned(batches, gen)
+
+    def _iter_cpu_ahead(self, batches: List[torch.Tensor], gen: torch.Generator) -> Iterator[Batch]:
+        """CPU mode: a producer thread gathers AND transforms the next batches while the model trains on this one."""
+        from .transforms import apply_pipeline_torch
+        q: "queue.Queue" = queue.Queue(maxsize=self.prefetch)
+        stop = threading.Event()
+
+        def produce():
+            try:
+                for idx in batches:
+                    if stop.is_set():
+                        return
+                    n = idx.numel()
+                    img, lab = self.ds.images.index_select(0, idx), self.ds.labels.index_select(0, idx)
+                    par = self._params(n, gen)
+                    x = apply_pipeline_torch(img, par if self.train else None, self.cpu_pipeline)
+                    q.put(Batch(img, lab, par, n, None, x))
+                q.put(None)
+            except BaseException as e:
+                q.put(e)
+
+        th = threading.Thread(target=produce, name="b200dp-cpu-loader", daemon=True)
+        th.start()
+        try:
+            while True:
+                item = q.get()
+                if item is None:
+                    break
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+        finally:
+            stop.set()
+            while not q.empty():
+                try:
+                    q.get_nowait()
+                except queue.Empty:
+                    break
 
     def _ensure_staging(self) -> None:
         want = self.prefetch + 1

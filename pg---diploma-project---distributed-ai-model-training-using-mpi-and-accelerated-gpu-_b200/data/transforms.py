@@ -177,15 +177,26 @@ def color_jitter(x: torch.Tensor, p: torch.Tensor) -> torch.Tensor:
     fc = p[:, P_CONTRAST].view(-1, 1, 1, 1)
     fs = p[:, P_SAT].view(-1, 1, 1, 1)
     fh = p[:, P_HUE].view(-1, 1, 1)
+    x = x.clone()
     for pos in range(4):
-        op = order[:, pos].view(-1, 1, 1, 1)
-        xb = (x * fb).clamp(0, 255)
-        mean = torch.floor(_gray(x).mean(dim=(1, 2, 3), keepdim=True) + 0.5)
-        xc = _blend(mean.expand_as(x), x, fc)
-        xs = _blend(_gray(x).expand_as(x), x, fs)
-        h, s, v = _rgb_to_hsv(x)
-        xh = _hsv_to_rgb(h + fh, s, v)
-        x = torch.where(op == 0, xb, torch.where(op == 1, xc, torch.where(op == 2, xs, xh)))
+        # each op only on the samples that have it at this position (a quarter of the batch on average): same values as
+        # evaluating all four on everything and selecting, a quarter of the work
+        for op in range(4):
+            idx = (order[:, pos] == op).nonzero(as_tuple=True)[0]
+            if idx.numel() == 0:
+                continue
+            xi = x[idx]
+            if op == 0:
+                xo = (xi * fb[idx]).clamp(0, 255)
+            elif op == 1:
+                mean = torch.floor(_gray(xi).mean(dim=(1, 2, 3), keepdim=True) + 0.5)
+                xo = _blend(mean.expand_as(xi), xi, fc[idx])
+            elif op == 2:
+                xo = _blend(_gray(xi).expand_as(xi), xi, fs[idx])
+            else:
+                h, sat, v = _rgb_to_hsv(xi)
+                xo = _hsv_to_rgb(h + fh[idx], sat, v)
+            x[idx] = xo
     return x
 
 

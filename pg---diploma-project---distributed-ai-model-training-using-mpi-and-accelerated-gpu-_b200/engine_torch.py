@@ -115,6 +115,8 @@ class TorchEngine:
                 return x.permute(0, 3, 1, 2)                                  # NCHW view, channels_last memory
             x = apply_pipeline_torch(batch.images, batch.params if train else None, self.cfg.img_size)
             return x.contiguous(memory_format=torch.channels_last)
+        if batch.x is not None:        # the loader thread already ran the pipeline (CPU mode)
+            return batch.x
         return apply_pipeline_torch(batch.images, batch.params if train else None, self.cfg.img_size)
 
     def _forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -66,10 +66,10 @@ class Trainer:
         self.test_sampler = PartitionSampler(len(test_set), W, r, shuffle=False)     # ref :122-124
         self.train_loader = BatchLoader(train_set, self.train_sampler, self.batch_size, self.ctx.device,
                                         train=True, augment=cfg.augment, drop_last=cfg.drop_last,
-                                        seed=cfg.seed, max_batches=cfg.max_steps_per_epoch)
+                                        seed=cfg.seed, max_batches=cfg.max_steps_per_epoch, cpu_pipeline=cfg.img_size)
         self.test_loader = BatchLoader(test_set, self.test_sampler, self.batch_size, self.ctx.device,
                                        train=False, augment=False, seed=cfg.seed,
-                                       max_batches=cfg.max_eval_steps)
+                                       max_batches=cfg.max_eval_steps, cpu_pipeline=cfg.img_size)
         self.engine = make_engine(cfg, self.ctx)
         self.best_acc = 0.0
         self.best_state = self.engine.state_dict()        # ref :159-160
