@@ -79,6 +79,20 @@ def _no_alloc_form(lib, x, in_coef, w, gamma, beta, stride, stream):
     return y, coef, saved
 
 
+def _torch_oracle(x, in_coef, w, gamma, beta, stride, eps=1e-5):
+    """fp32 PyTorch statement of the op: y = dwconv3x3(relu6(scale * x + shift)); BatchNorm coefficients of y."""
+    Cn = x.shape[-1]
+    a = torch.clamp(x.float() * in_coef[0] + in_coef[1], 0, 6).to(torch.bfloat16).float()     # the kernel rounds the activation
+    wt = w.t().reshape(Cn, 1, 3, 3)
+    y = torch.nn.functional.conv2d(a.permute(0, 3, 1, 2), wt, stride=stride, padding=1, groups=Cn)
+    yq = y.to(torch.bfloat16).float()            # statistics are taken over the values that are stored
+    mean = yq.mean((0, 2, 3))
+    var = yq.var((0, 2, 3), unbiased=False)
+    inv = torch.rsqrt(var + eps)
+    scale = gamma * inv
+    return y.permute(0, 2, 3, 1), torch.stack([scale, beta - mean * scale]), torch.stack([mean, inv])
+
+
 def test_two_calls_in_a_row_match_the_two_call_form(lib):
     stream = torch.cuda.current_stream().cuda_stream
     # first call: wide tensor; second call: fewer channels and another stride, so stale sums from call one sit in
@@ -91,6 +105,12 @@ def test_two_calls_in_a_row_match_the_two_call_form(lib):
         assert torch.equal(y1, y0)                                   # same kernel, same inputs
         assert torch.allclose(coef1, coef0, rtol=2e-3, atol=1e-3)    # sums are atomically accumulated: order differs
         assert torch.allclose(saved1, saved0, rtol=2e-3, atol=1e-3)
+        # and against a plain fp32 PyTorch statement of the same op (the two forms share a kernel, so agreeing with
+        # each other alone would not catch an error in it)
+        y_ref, coef_ref, saved_ref = _torch_oracle(*args, stride)
+        assert torch.allclose(y1.float(), y_ref, rtol=2e-2, atol=3e-2)
+        assert torch.allclose(saved1, saved_ref, rtol=5e-3, atol=5e-3)
+        assert torch.allclose(coef1, coef_ref, rtol=5e-3, atol=5e-3)
 
 
 def test_rejects_sizes_beyond_the_static_scratch(lib):
