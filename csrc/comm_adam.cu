@@ -197,10 +197,9 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
   float* __restrict__ mm = P.m;
   float* __restrict__ vv = P.v;
 
-  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  // one 16-byte element: (already summed) gradient -> average -> Adam -> store
+  auto update = [&](long long i, float4 acc) {
     if constexpr (ALGO == 2) {
-      acc = mc_ld_reduce_f4(reinterpret_cast<const float*>(P.mc_grads) + i * 4);   // summed inside the switch
     } else if constexpr (WT > 0) {
       float4 g[WT];
 #pragma unroll
@@ -218,7 +217,7 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
     acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
     if (!P.apply_adam) {
       *reinterpret_cast<float4*>(P.out_avg + i * 4) = acc;
-      continue;
+      return;
     }
     float4 p = *reinterpret_cast<const float4*>(myp + i * 4);
     float4 m = *reinterpret_cast<const float4*>(mm + i * 4);
@@ -244,6 +243,21 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
           st_peer_u2(reinterpret_cast<__nv_bfloat16*>(P.work_bf16[r]) + i * 4, w01, w23);
       }
     }
+  };
+  const long long first = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if constexpr (ALGO == 2) {
+    // four independent switch reductions in flight per thread before any of the (dependent) Adam chains starts
+    for (long long i = first; i < hi; i += 4 * stride) {
+      float4 acc[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i + u * stride < hi) acc[u] = mc_ld_reduce_f4(reinterpret_cast<const float*>(P.mc_grads) + (i + u * stride) * 4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (i + u * stride < hi) update(i + u * stride, acc[u]);
+    }
+  } else {
+    for (long long i = first; i < hi; i += stride) update(i, make_float4(0.f, 0.f, 0.f, 0.f));
   }
 
   if (W > 1) __threadfence_system();   // my stores into the peers' weights are performed before anything that follows
