@@ -254,6 +254,30 @@ class NativeEngine:
             self.core.metrics_eval.zero_()
         return m[0], m[1], m[2]
 
+    # Per-step metric read-back without stalling the pipeline: `post_metrics()` enqueues a device -> pinned-host copy of
+    # the running (loss sum, correct, count) after the step just launched, `fetch_metrics()` waits for the OLDEST posted
+    # copy and returns it.  A loop that posts every step and fetches one step behind reads every step's result while
+    # the host stays one step ahead of the GPU (the reference's `loss.item()` at ref :183 stalls both every step).
+    def post_metrics(self) -> None:
+        if not hasattr(self, "_mring"):
+            self._mring = torch.zeros(8, 3, dtype=torch.float64).pin_memory()
+            self._mev = [torch.cuda.Event() for _ in range(8)]
+            self._mhead = self._mtail = 0
+        slot = self._mhead % 8
+        self._mring[slot].copy_(self.core.metrics_train[:3], non_blocking=True)
+        self._mev[slot].record()
+        self._mhead += 1
+
+    def fetch_metrics(self) -> Tuple[float, float, float]:
+        if not hasattr(self, "_mring") or self._mtail == self._mhead:
+            raise RuntimeError("fetch_metrics without a pending post_metrics")
+        slot = self._mtail % 8
+        self._mev[slot].synchronize()
+        self._mtail += 1
+        self.fused.poll_error()
+        v = self._mring[slot].tolist()
+        return v[0], v[1], v[2]
+
     def state_dict(self):
         return self.core.state_dict()
 
