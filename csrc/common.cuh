@@ -65,7 +65,14 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
+// SM budget: launches made while a budget is set size their grids for that many SMs instead of the whole device, so that
+// two branches of the step graph can share the machine without queueing behind each other's persistent CTAs.
+inline int& sm_budget() {
+  static thread_local int b = 0;
+  return b;
+}
 inline int num_sms() {
+  if (sm_budget() > 0) return sm_budget();
   static int n = 0;
   if (n == 0) {
     int dev = 0;

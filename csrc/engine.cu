@@ -117,6 +117,7 @@ struct Engine {
   bool fork = true;
   bool fork_wgrad = false;
   int fork_max_h = 14;       // only blocks whose input is at most this tall fork their weight gradients
+  int fork_sms = 40;         // SMs given to the weight-gradient branches of a forked block; the main chain sizes for the rest
   cudaStream_t side[3] = {nullptr, nullptr, nullptr};
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_next = 0;
@@ -291,6 +292,8 @@ int build_plans(Engine& e, Plans& pl, int n) {
   // forward / data-gradient weights of a conv: the plain bf16 copy, or its block-diagonal copy when the layer is packed
   auto wf = [&](const Conv& c) { return c.pack_f > 1 ? e.w_pack + c.off_pf : e.w_bf16 + c.off_w; };
   auto wd = [&](const Conv& c) { return c.pack_d > 1 ? e.w_pack + c.off_pd : e.wt_bf16 + c.off_w; };
+  // data-gradient GEMMs of blocks whose weight gradients run on side branches leave fork_sms SMs to those branches
+  auto main_ctas = [&](int h) { return (e.fork && e.fork_wgrad && h <= e.fork_max_h) ? num_sms() - e.fork_sms : 0; };
   if (e.stem_gemm) {
     const Conv& st = e.convs[0];
     const int M = n * st.hout * st.hout;
@@ -315,7 +318,7 @@ int build_plans(Engine& e, Plans& pl, int n) {
       // dgrad: dx[M, cin] = BNgrad(dze, e_raw)[M, hidden] * W[hidden, cin]   (weights transposed: [cin][hidden])
       ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp,
                            e.dze[dze_idx(e, b.index - 1)], ce.raw, ce.coef_b, 0, wd(ce), e.gx[0], ce.cinp, nullptr, nullptr,
-                           nullptr, 0, 0, ce.pack_d));
+                           nullptr, 0, main_ctas(b.hin), ce.pack_d));
       if (e.fork && e.fork_wgrad && e.bn_fuse) pl.dgrad[b.ce].gsrc = src_b(e, ce, (float)Min);
     }
     for (int ev = 0; ev < 2; ++ev)
@@ -325,7 +328,7 @@ int build_plans(Engine& e, Plans& pl, int n) {
     if (e.bn_fuse) pl.fwd[b.cp].asrc = src_f(e, cd, (float)Mout);     // training plan only: eval reads running-stat coefficients
     // project dgrad: dzd[M, hidden] = mask(dp[M, cout] * W[cout, hidden])   (weights transposed: [hidden][cout])
     ENG_TRY(pw_gemm_plan(&pl.dgrad[b.cp], A_TMA, E_MASKSTATS, Mout, cp.cinp, cp.coutp, e.dp[dp_idx(b.index - 1)], cp.coutp, nullptr, nullptr,
-                         nullptr, 0, wd(cp), e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, 0, cp.pack_d));
+                         nullptr, 0, wd(cp), e.dzd, cp.cinp, cd.raw, cd.coef_f, cd.sums_b, cd.coutp, main_ctas(b.hout), cp.pack_d));
   }
   {
     const int li = nc - 1;
@@ -561,6 +564,14 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     // from the critical path there (measured), so they stay on the main chain
     sp = b.hout <= e.fork_max_h ? sp_side : s;
     se = b.hin <= e.fork_max_h ? se_side : s;
+    // SM budgets of a forked block: the weight-gradient launches size their grids for fork_sms SMs, everything on
+    // the main chain for the rest (RAII: back to the whole device at the end of the iteration)
+    struct Budget { int saved; Budget() : saved(sm_budget()) {} ~Budget() { sm_budget() = saved; } } budget_guard;
+    const int total_sms = num_sms();
+    const int side_sms = (sp != s || se != s) ? e.fork_sms : 0;
+    auto budget_main = [&]() { sm_budget() = side_sms ? total_sms - side_sms : 0; };
+    auto budget_side = [&]() { sm_budget() = side_sms; };
+    budget_main();
     __nv_bfloat16* dp = e.dp[dp_idx(bi)];
     __nv_bfloat16* dze = e.dze[dze_idx(e, bi)];
     const long long rows_out = (long long)n * b.hout * b.hout;
@@ -582,10 +593,12 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     // ---- projection conv: weight gradient (side branch), data gradient (+ReLU6 mask, statistics for the dw BatchNorm)
     ENG_TRY(order_after(e, s, sp));
     sp_used |= sp != s;
+    if (sp != s) budget_side();
     ENG_TRY(pw_wgrad_launch(1, (int)rows_out, cp.coutp, cp.cinp, dp, cp.coutp, cd.raw, nullptr, cp.cinp, cd.coef_f,
                             nullptr, e.grads + cp.off_w, cp.cinp, 0, sp,
                             e.pw_pack ? pw_wgrad_pick_pack(1, (int)rows_out, cp.coutp, cp.cinp) : 1));
     mark(e, s, "pw_wgrad_project", b.cp);
+    budget_main();
     ENG_TRY(mark_free(dp_free[dp_idx(bi)], sp));
     ENG_TRY(pw_gemm_launch(pl.dgrad[b.cp], s));
     mark(e, s, "pw_dgrad_project", b.cp);
@@ -613,6 +626,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
     const BnBwdSrc in_src = src_b(e, cin_raw, (float)rows_in);
     ENG_TRY(order_after(e, s, se));
     se_used |= se != s;
+    if (se != s) budget_side();
     if (b.ce >= 0) {
       Conv& ce = e.convs[b.ce];
       const __nv_bfloat16* xin = e.blocks[bi - 1].xout;
@@ -621,6 +635,7 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
                               e.pw_pack ? pw_wgrad_pick_pack(0, (int)rows_in, ce.coutp, ce.cinp) : 1,
                               in_fused ? &in_src : nullptr));
       mark(e, s, "pw_wgrad_expand", b.ce);
+      budget_main();
       ENG_TRY(mark_free(dze_free[dze_idx(e, bi)], se));
       gxi ^= 1;
       ENG_TRY(retarget_out(pl.dgrad[b.ce], e.gx[gxi]));
@@ -712,6 +727,7 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   e->fork = !(getenv("B200DP_FORK") != nullptr && atoi(getenv("B200DP_FORK")) == 0);
   e->fork_wgrad = getenv("B200DP_FORK_WGRAD") != nullptr && atoi(getenv("B200DP_FORK_WGRAD")) != 0;
   if (getenv("B200DP_FORK_MAXH") != nullptr) e->fork_max_h = atoi(getenv("B200DP_FORK_MAXH"));
+  if (getenv("B200DP_FORK_SMS") != nullptr) e->fork_sms = atoi(getenv("B200DP_FORK_SMS"));
   {
     const char* st = getenv("B200DP_STEM");
     e->stem_gemm = !(st != nullptr && std::string(st) == "simt");
