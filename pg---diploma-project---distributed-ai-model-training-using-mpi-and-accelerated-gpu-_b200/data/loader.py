@@ -53,7 +53,8 @@ class Batch:
 class BatchLoader:
     def __init__(self, dataset: ArrayDataset, sampler: PartitionSampler, batch_size: int,
                  device: torch.device, train: bool, augment: bool = True, drop_last: bool = False,
-                 seed: int = 0, prefetch: int = 2, max_batches: int = 0, cpu_pipeline: int = 0) -> None:
+                 seed: int = 0, prefetch: int = 2, max_batches: int = 0, cpu_pipeline: int = 0,
+                 img_size: int = 224) -> None:
         self.ds = dataset
         self.sampler = sampler
         self.batch_size = int(batch_size)
@@ -67,6 +68,7 @@ class BatchLoader:
         # CPU mode: image size for which a background thread runs the transform pipeline one batch ahead of the
         # training step -- the role of the reference's DataLoader workers (ref :126-133); 0 = leave it to the engine
         self.cpu_pipeline = int(cpu_pipeline) if self.device.type == "cpu" else 0
+        self.img_size = int(cpu_pipeline) if cpu_pipeline else int(img_size)     # crop boxes are drawn in output-pixel units
         self.resident = dataset.images.device.type == "cuda"
         self._copy_stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
         self._staging: List[dict] = []
@@ -80,7 +82,7 @@ class BatchLoader:
 
     # -- parameter rows ----------------------------------------------------------------------
     def _params(self, n: int, gen: torch.Generator) -> torch.Tensor:
-        return sample_aug_params(n, gen) if self.augment else identity_params(n)
+        return sample_aug_params(n, gen, size=self.img_size) if self.augment else identity_params(n)
 
     def _gen(self) -> torch.Generator:
         g = torch.Generator()

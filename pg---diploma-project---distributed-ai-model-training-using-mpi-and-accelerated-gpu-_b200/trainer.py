@@ -66,7 +66,8 @@ class Trainer:
         self.test_sampler = PartitionSampler(len(test_set), W, r, shuffle=False)     # ref :122-124
         self.train_loader = BatchLoader(train_set, self.train_sampler, self.batch_size, self.ctx.device,
                                         train=True, augment=cfg.augment, drop_last=cfg.drop_last,
-                                        seed=cfg.seed, max_batches=cfg.max_steps_per_epoch, cpu_pipeline=cfg.img_size)
+                                        seed=cfg.seed, max_batches=cfg.max_steps_per_epoch, cpu_pipeline=cfg.img_size,
+                                        img_size=cfg.img_size)
         self.test_loader = BatchLoader(test_set, self.test_sampler, self.batch_size, self.ctx.device,
                                        train=False, augment=False, seed=cfg.seed,
                                        max_batches=cfg.max_eval_steps, cpu_pipeline=cfg.img_size)
