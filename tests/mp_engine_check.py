@@ -6,6 +6,8 @@ global mean loss per step must match a run of the same steps with `--comm nccl` 
 Gradients are accumulated with fp32 atomics, so no two runs are bit-equal and a randomly initialised network
 amplifies the difference step by step: the first step (same weights) must agree to 2e-3, and the whole curve to within three
 times the distance between two NCCL runs of the same steps (the measured noise floor).
+mode "resume": the default multi-GPU optimiser shards Adam's moments (each rank updates the slices it owns); the saved
+optimiser state must nevertheless be the FULL moments, and a run resumed from it must continue like the uninterrupted one.
 mode "fault": rank 1 stops itself (SIGSTOP) after a few steps; every other rank must leave with CommError -- never
 with silently updated weights -- within the barrier's spin limit.
 """
@@ -71,6 +73,53 @@ def main() -> int:
             if i % 8 == 7:
                 eng.read_metrics()
         print("FAULT NOT DETECTED", flush=True)
+        return 0
+    if mode == "resume":
+        cfg = TrainConfig(comm="fused", comm_algo="two_shot", **base)
+        a = make_engine(cfg, ctx)
+        for b in data[:6]:
+            a.train_step(b, 1e-3)
+        sd_model, sd_opt = a.state_dict(), a.optimizer_state()         # collective: moments are summed over ranks
+        local_m = a.fused.m.clone()
+        for b in data[6:10]:
+            a.train_step(b, 1e-3)
+        torch.cuda.synchronize()
+        want = a.core.params.clone()
+        # this rank only ever touched its own slices of m; the saved state covers everything that has a gradient
+        own = (local_m != 0).float().mean().item()
+        full = (sd_opt["m"] != 0).float().mean().item()
+        assert full > 1.5 * own and sd_opt["step"] == 6 and sd_opt["algo"] == "two_shot" and sd_opt["world"] == ctx.world_size, (own, full)
+        a.close()
+
+        def resumed(opt_state):
+            e = make_engine(cfg, ctx)
+            e.load_state_dict(sd_model)
+            e.broadcast_parameters()
+            e.load_optimizer_state(opt_state)
+            for b in data[6:10]:
+                e.train_step(b, 1e-3)
+            torch.cuda.synchronize()
+            return e, ((e.core.params - want).norm() / want.norm()).item()
+
+        # gradients are accumulated with fp32 atomics and Adam normalises them, so two identical continuations differ:
+        # the second continuation from the same state is the noise floor.  A state that has lost the peers' moments
+        # (what a rank holds locally -- the round-1 bug) must land clearly further away.
+        c, noise = resumed(sd_opt)
+        c.close()
+        lossy = dict(sd_opt, m=local_m.cpu(), v=torch.zeros_like(sd_opt["v"]))
+        d, bad = resumed(lossy)
+        d.close()
+        b2, rel = resumed(sd_opt)
+        assert rel < max(3 * noise, 1e-3) and bad > 3 * max(rel, noise), (rel, noise, bad)
+        h = b2.param_hash()
+        hi, neg_lo = b2.reduce([h, -h], "max")
+        assert hi == -neg_lo
+        if r == 0:
+            print(f"resume: moments nonzero {own:.2f} locally, {full:.2f} in the saved state; distance to the uninterrupted run "
+                  f"{rel:.1e} (second continuation {noise:.1e}, with the peers' moments lost {bad:.1e})")
+            print("RESUME CHECK OK", flush=True)
+        b2.close()
+        cleanup(ctx)
         return 0
     algos = ["auto", "one_shot", "two_shot"]
     rel = lambda x, y: [abs(a - b) / max(abs(b), 1e-6) for a, b in zip(x, y)]

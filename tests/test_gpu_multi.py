@@ -35,3 +35,11 @@ def test_stalled_peer_is_a_comm_error():
     assert r.returncode != 0, r.stdout[-2000:]
     assert "FAULT NOT DETECTED" not in r.stdout
     assert "did not reach a device barrier" in r.stderr or "CommError" in r.stderr, r.stderr[-3000:]
+
+
+def test_sharded_optimiser_state_resumes_like_an_uninterrupted_run():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("not enough GPUs")
+    r = _launch(2, "resume", timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RESUME CHECK OK" in r.stdout
