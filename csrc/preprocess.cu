@@ -270,7 +270,9 @@ preprocess_aug_kernel(const uint8_t* __restrict__ images, const float* __restric
 //   * one CTA per image, 1024 threads; source and resized image live in shared memory as PACKED pixels (one 32-bit word
 //     r | g << 8 | b << 16 per pixel: a bilinear tap is one LDS.32 + three byte->float conversions instead of three
 //     byte loads), 4 KB + 196 KB;
-//   * pixel coordinates advance incrementally (no integer division by the runtime image size);
+//   * pixel coordinates advance incrementally (no integer division by the runtime image size), and both interpolation
+//     chains are separable, so their taps (two indices + a fraction per output row / column) are tabulated once per
+//     image instead of being recomputed per pixel;
 //   * the output is produced in bands of 4 im2col rows = 8 new image rows: the augmented, normalised pixels of a band go
 //     to a 9-row ring in shared memory (the row shared with the previous band is kept), then every thread assembles
 //     half an im2col row (32 bytes) from it -- a warp stores 1 KB contiguous;
@@ -288,32 +290,41 @@ __device__ __forceinline__ uint32_t pack_rgb(float3 v) {
   return (uint32_t)v.x | ((uint32_t)v.y << 8) | ((uint32_t)v.z << 16);
 }
 // rows blended first, then columns, each channel rounded to an 8-bit level (same association as resized_px / crop_px)
+// (a convex combination of 8-bit levels stays inside [0, 255]: the clamp of round_u8 is not needed here)
+__device__ __forceinline__ float round_level(float v) { return floorf(v + 0.5f); }
 __device__ __forceinline__ float3 bilerp_u8(uint32_t q00, uint32_t q01, uint32_t q10, uint32_t q11, float fx, float fy) {
   const float3 a = unpack_rgb(q00), b = unpack_rgb(q01), c = unpack_rgb(q10), d = unpack_rgb(q11);
   const float gx = 1.f - fx, gy = 1.f - fy;
-  return make_float3(round_u8((a.x * gx + b.x * fx) * gy + (c.x * gx + d.x * fx) * fy),
-                     round_u8((a.y * gx + b.y * fx) * gy + (c.y * gx + d.y * fx) * fy),
-                     round_u8((a.z * gx + b.z * fx) * gy + (c.z * gx + d.z * fx) * fy));
+  return make_float3(round_level((a.x * gx + b.x * fx) * gy + (c.x * gx + d.x * fx) * fy),
+                     round_level((a.y * gx + b.y * fx) * gy + (c.y * gx + d.y * fx) * fy),
+                     round_level((a.z * gx + b.z * fx) * gy + (c.z * gx + d.z * fx) * fy));
 }
-__device__ __forceinline__ float3 resized_px32(const uint32_t* s_src, int y, int x, float scale) {
-  int y0, y1, x0, x1;
-  float fy, fx;
-  src_tap(y, scale, y0, y1, fy);
-  src_tap(x, scale, x0, x1, fx);
-  return bilerp_u8(s_src[y0 * SRC + x0], s_src[y0 * SRC + x1], s_src[y1 * SRC + x0], s_src[y1 * SRC + x1], fx, fy);
+// A bilinear tap along one axis, tabulated per output coordinate: both interpolation chains of this pipeline are
+// separable (resize: source row / column per output row / column; crop: row of the resized image per crop row, column
+// per crop column with the flip folded in), so the coordinate arithmetic is done S times per axis instead of per pixel.
+struct Tap { int i0, i1; float f; };
+__device__ __forceinline__ uint2 tap_pack(int i0, int i1, float f) { return make_uint2((uint32_t)i0 | ((uint32_t)i1 << 16), __float_as_uint(f)); }
+__device__ __forceinline__ Tap tap_unpack(uint2 t) { return Tap{(int)(t.x & 0xffffu), (int)(t.x >> 16), __uint_as_float(t.y)}; }
+__device__ __forceinline__ float3 sample_tab(const uint32_t* img, int pitch, uint2 ty, uint2 tx) {
+  const Tap y = tap_unpack(ty), x = tap_unpack(tx);
+  return bilerp_u8(img[y.i0 * pitch + x.i0], img[y.i0 * pitch + x.i1], img[y.i1 * pitch + x.i0], img[y.i1 * pitch + x.i1], x.f, y.f);
 }
-__device__ __forceinline__ float3 crop_px32(const uint32_t* s_res, int S, const AugP& a, int v, int u) {
-  if (a.flip > 0.f) u = S - 1 - u;
-  float py = a.top + ((float)v + 0.5f) * (a.h / (float)S) - 0.5f;
-  float px = a.left + ((float)u + 0.5f) * (a.w / (float)S) - 0.5f;
-  const float ylo = a.top, yhi = a.top + a.h - 1.f, xlo = a.left, xhi = a.left + a.w - 1.f;
-  py = fminf(fmaxf(py, ylo), yhi);
-  px = fminf(fmaxf(px, xlo), xhi);
-  const float y0f = floorf(py), x0f = floorf(px);
-  const float fy = py - y0f, fx = px - x0f;
-  const int y0 = (int)y0f, x0 = (int)x0f;
-  const int y1 = (int)fminf(y0f + 1.f, yhi), x1 = (int)fminf(x0f + 1.f, xhi);
-  return bilerp_u8(s_res[y0 * S + x0], s_res[y0 * S + x1], s_res[y1 * S + x0], s_res[y1 * S + x1], fx, fy);
+// the colour chain with the permutation held in a register (four 2-bit op codes) instead of constant-memory look-ups
+__device__ __forceinline__ float3 color_chain_r(float3 v, const AugP& a, uint32_t perm, int upto, float mean) {
+  for (int pos = 0; pos < upto; ++pos) {
+    const uint32_t op = (perm >> (2 * pos)) & 3u;
+    if (op == 0) {
+      v = make_float3(clamp255(v.x * a.fb), clamp255(v.y * a.fb), clamp255(v.z * a.fb));
+    } else if (op == 1) {
+      v = blend(make_float3(mean, mean, mean), v, a.fc);
+    } else if (op == 2) {
+      const float g = gray_of(v);
+      v = blend(make_float3(g, g, g), v, a.fs);
+    } else {
+      v = hue_shift(v, a.fh);
+    }
+  }
+  return v;
 }
 __device__ __forceinline__ uint2 norm_px(float3 v) {
   return make_uint2(pack_bf16x2((v.x - c_mean[0]) * c_istd[0], (v.y - c_mean[1]) * c_istd[1]),
@@ -337,6 +348,8 @@ preprocess_col_kernel(const ColParams P) {
   uint32_t* s_src = reinterpret_cast<uint32_t*>(smem);                       // 32 x 32 packed pixels
   uint32_t* s_res = s_src + SRC * SRC;                                       // S x S packed pixels (augmenting images)
   uint2* s_ring = reinterpret_cast<uint2*>(s_res + (size_t)S * S);           // RING x S normalised bf16 pixels (r, g, b, 0)
+  uint2* s_tab = s_ring + (size_t)RING * S;                                  // [4][S]: resize y / x taps, crop y / x taps
+  uint2 *t_ry = s_tab, *t_rx = s_tab + S, *t_cy = s_tab + 2 * S, *t_cx = s_tab + 3 * S;
   __shared__ float s_red[32];
   __shared__ float s_mean;
   __shared__ float s_sum[32];
@@ -359,8 +372,30 @@ preprocess_col_kernel(const ColParams P) {
     a.angle = pr[10];
     enabled = pr[11] > 0.f;
   }
-  __syncthreads();
   const float scale = (float)SRC / (float)S;
+  for (int i = tid; i < 2 * S; i += NT) {           // resize taps (the same along both axes)
+    int i0, i1;
+    float f;
+    src_tap(i < S ? i : i - S, scale, i0, i1, f);
+    s_tab[i] = tap_pack(i0, i1, f);
+  }
+  if (enabled) {
+    for (int i = tid; i < 2 * S; i += NT) {         // crop taps: rows of the box, columns of the box (flip folded in)
+      const bool isx = i >= S;
+      int o = isx ? i - S : i;
+      if (isx && a.flip > 0.f) o = S - 1 - o;
+      const float start = isx ? a.left : a.top, len = isx ? a.w : a.h;
+      float pos = start + ((float)o + 0.5f) * (len / (float)S) - 0.5f;
+      const float lo = start, hi = start + len - 1.f;
+      pos = fminf(fmaxf(pos, lo), hi);
+      const float p0 = floorf(pos);
+      s_tab[2 * S + i] = tap_pack((int)p0, (int)fminf(p0 + 1.f, hi), pos - p0);
+    }
+  }
+  uint32_t perm = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) perm |= (uint32_t)c_perm[a.order][i] << (2 * i);
+  __syncthreads();
   const int npx = S * S;
   // (y, x) of pixel index tid, advanced by NT pixels per iteration without dividing
   const int dy = NT / S, dx = NT - dy * S;
@@ -370,7 +405,7 @@ preprocess_col_kernel(const ColParams P) {
     {
       int y = tid / S, x = tid - y * S;
       for (int p = tid; p < npx; p += NT) {
-        s_res[p] = pack_rgb(resized_px32(s_src, y, x, scale));
+        s_res[p] = pack_rgb(sample_tab(s_src, SRC, t_ry[y], t_rx[x]));
         y += dy; x += dx;
         if (x >= S) { x -= S; ++y; }
       }
@@ -385,7 +420,7 @@ preprocess_col_kernel(const ColParams P) {
     {
       int y = tid / S, x = tid - y * S;
       for (int p = tid; p < npx; p += NT) {
-        part += gray_of(color_chain(crop_px32(s_res, S, a, y, x), a, cpos, 0.f));
+        part += gray_of(color_chain_r(sample_tab(s_res, S, t_cy[y], t_cx[x]), a, perm, cpos, 0.f));
         y += dy; x += dx;
         if (x >= S) { x -= S; ++y; }
       }
@@ -409,12 +444,12 @@ preprocess_col_kernel(const ColParams P) {
   const float rc = cx - (ra * cx + rb * cx);
   const float rf = cx - (rd * cx + re * cx);
   auto final_px = [&](int y, int x) -> uint2 {          // normalised output pixel (y, x) of this image
-    if (!enabled) return norm_px(resized_px32(s_src, y, x, scale));
+    if (!enabled) return norm_px(sample_tab(s_src, SRC, t_ry[y], t_rx[x]));
     const float xin = ra * ((float)x + 0.5f) + rb * ((float)y + 0.5f) + rc;
     const float yin = rd * ((float)x + 0.5f) + re * ((float)y + 0.5f) + rf;
     const int u = (int)floorf(xin), v = (int)floorf(yin);
     float3 val = make_float3(0.f, 0.f, 0.f);
-    if (u >= 0 && u < S && v >= 0 && v < S) val = color_chain(crop_px32(s_res, S, a, v, u), a, 4, mean);
+    if (u >= 0 && u < S && v >= 0 && v < S) val = color_chain_r(sample_tab(s_res, S, t_cy[v], t_cx[u]), a, perm, 4, mean);
     return norm_px(val);
   };
   // ---- bands: 2*BAND new image rows -> ring, then BAND im2col rows of Wo pixels out of the ring
@@ -541,7 +576,7 @@ resize_normalize_kernel(const ResizeParams P) {
   *reinterpret_cast<uint2*>(P.out + ((size_t)img * S * S + p) * 4) = norm_px(v);
 }
 
-size_t col_smem_bytes(int S) { return (size_t)SRC * SRC * 4 + (size_t)S * S * 4 + (size_t)RING * S * 8; }
+size_t col_smem_bytes(int S) { return (size_t)SRC * SRC * 4 + (size_t)S * S * 4 + (size_t)RING * S * 8 + (size_t)4 * S * 8; }
 
 }  // namespace
 }  // namespace b200dp

@@ -72,10 +72,16 @@ def test_train_step_matches_teacher_forced_torch(env, graphs):
             assert a.norm() < 5e-2, (k, a.norm().item())
             continue
         err = (a - b).norm().item()
-        assert err < 0.1 * b.norm().item() + 5e-4, (k, err, b.norm().item())    # cos >= 0.995 <=> relative error <= 0.1
+        # Convolution weights: cos >= 0.995 <=> relative error <= 0.1.  BatchNorm gains / biases are sums of ~1e6 signed
+        # bf16-rounded terms per channel that largely cancel; their run-to-run spread (fp32 atomics order the sums
+        # differently every run, and the teacher-forced reference moves with the native activations) is a few per cent
+        # of the norm, so they get a wider band -- a tight one fails about one run in ten on noise alone.
+        vec = p.dim() == 1
+        assert err < (0.15 if vec else 0.1) * b.norm().item() + (1e-3 if vec else 5e-4), (k, err, b.norm().item())
         if b.norm() > 5e-3:                      # tiny BatchNorm-gain gradients are dominated by bf16 noise
-            assert cos(a, b) > 0.995, (k, cos(a, b))
-            assert 0.95 < (a.norm() / b.norm()).item() < 1.05, (k, a.norm().item(), b.norm().item())
+            assert cos(a, b) > (0.985 if vec else 0.995), (k, cos(a, b))
+            lo, hi = (0.9, 1.1) if vec else (0.97, 1.03)
+            assert lo < (a.norm() / b.norm()).item() < hi, (k, a.norm().item(), b.norm().item())
     # running statistics after one step against torch's own update on the fp32 forward
     ref2, _ = None, None
     sd = core.state_dict()
