@@ -25,7 +25,7 @@
 // is then a plain (row, column) offset inside one plane; the chunk width is chosen per layer.
 // The BatchNorm of the producer can be finalised in the prologue (bn_inline.cuh): this kernel is its first consumer.
 //
-// The tensor-core formulation of the same conv (dw_tc.cu) is kept as an experiment: ~100-200 cycles per
+// The tensor-core formulation of the same conv (experiments/dw_tc.cu, not part of the library) was measured: ~100-200 cycles per
 // tcgen05.mma make nine tap-shifted N=16 MMAs per 128 pixels slower than 18 packed FMAs per thread.
 //
 // Reference behaviour replaced: cuDNN/ATen depthwise conv + cuDNN batch-norm + hardtanh as separate passes

@@ -15,10 +15,6 @@ int dw_fwd_launch(const void* x, const float* scale, const float* shift, const f
 int dw_bwd_launch(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,
                   const float* dcoef, const float* w, void* dze, float* stats, int stats_stride, float* dw, int B,
                   int H, int W, int C, int stride, cudaStream_t s, const BnBwdSrc* src = nullptr);
-// dw_tc.cu: the same forward contract on the tensor cores (nine tap-shifted MMAs with diagonal weight matrices)
-bool dw_tc_supported(int B, int H, int W, int C, int stride);
-int dw_tc_fwd_launch(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
-                     int stats_stride, int B, int H, int W, int C, int stride, cudaStream_t s);
 // dw_tile.cu: stride-1 forward, TMA halo tiles in shared memory + register-window stencil on the CUDA cores
 bool dw_tile_supported(int B, int H, int W, int C, int stride);
 bool dw_tile_fwd_supported(int B, int H, int W, int C, int stride);    // the forward kernel also does stride 2

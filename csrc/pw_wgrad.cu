@@ -199,7 +199,7 @@ pw_wgrad_kernel(const __grid_constant__ WgradParams P, const __grid_constant__ B
           const uint64_t dh2 = umma_desc_mnmajor_sw128(st + h_bytes, (uint32_t)MK * 128);   // MODE 0: y_raw tile
           const uint64_t dq = umma_desc_mnmajor_sw128(sq, (uint32_t)MK * 128);
           // 16 m-rows per MMA = 2048 B of 128-byte lines.  All MMAs of one accumulator back to back: alternating
-          // between two accumulators costs about twice as much per instruction (measured in dw_tc.cu).
+          // between two accumulators costs about twice as much per instruction (measured in experiments/dw_tc.cu).
           for (int k = 0; k < (MK >> 4); ++k)
             umma_bf16(d_tmem, dh + (uint64_t)(128 * k), dq + (uint64_t)(128 * k), idesc, (c > c_lo) | (k > 0));
           if (MODE == 0 && !P.fuse_g)

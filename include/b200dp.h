@@ -221,11 +221,6 @@ int b200dp_pw_gemm_pick_pack(int M, int N, int K);
  * stats (may be NULL) [2][stats_stride] += sum(y), sum(y^2): a scratch accumulator that must be zero on entry. */
 int b200dp_dw_fwd(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
                   int stats_stride, int B, int H, int W, int C, int stride, void* stream);
-/* Same contract on the tensor cores (csrc/dw_tc.cu): TMA halo tiles, BatchNorm+ReLU6 rewritten in shared memory,
- * nine tap-shifted tcgen05 MMAs against 16x16 diagonal weight matrices (weights and activations rounded to bf16,
- * fp32 accumulation in TMEM). */
-int b200dp_dw_fwd_tc(const void* x, const float* scale, const float* shift, const float* w, void* y, float* stats,
-                     int stats_stride, int B, int H, int W, int C, int stride, void* stream);
 /* Depthwise backward: data gradient (masked by ReLU6' of the input activation), weight gradient and the sums the
  * producer's BatchNorm backward needs, in one pass (csrc/dwconv.cu). */
 int b200dp_dw_bwd(const void* e_raw, const float* escale, const float* eshift, const void* dzd, const void* d_raw,

@@ -209,9 +209,9 @@ def dw_fwd(x: torch.Tensor, coef: torch.Tensor, w: torch.Tensor, stride: int,
     """Depthwise 3x3 on NHWC bf16 ``x`` [B,H,W,C] with relu6(coef[0]*x+coef[1]) applied on load; ``w`` fp32 [9,C].
 
     ``impl``: "simt" = register sliding-window kernel (dwconv.cu), "tile" = TMA halo tiles + shared-memory stencil
-    (dw_tile.cu, stride 1), "tc" = tcgen05 tap-shifted MMAs (dw_tc.cu, experiment)."""
+    (dw_tile.cu)."""
     lib = _lib.require()
-    fn = {"tc": lib.b200dp_dw_fwd_tc, "tile": lib.b200dp_dw_fwd_tile, "simt": lib.b200dp_dw_fwd}[impl]
+    fn = {"tile": lib.b200dp_dw_fwd_tile, "simt": lib.b200dp_dw_fwd}[impl]
     _chk(x, torch.bfloat16, "x"); _chk(coef, torch.float32, "coef"); _chk(w, torch.float32, "w")
     B, H, W, Cn = x.shape
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1

@@ -87,7 +87,6 @@ def _declare(lib: C.CDLL) -> None:
         "b200dp_pw_wgrad_packed": [i, i, i, i, vp, vp, vp, vp, vp, vp, i, i, vp],
         "b200dp_pw_wgrad": [i, i, i, i, vp, i, vp, vp, i, vp, vp, vp, i, i, vp],
         "b200dp_dw_fwd": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
-        "b200dp_dw_fwd_tc": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "b200dp_dw_fwd_tile": [vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
         "b200dp_dw_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, i, i, i, i, i, vp],
         "b200dp_dw_bwd_tile": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, vp, i, i, i, i, i, vp],

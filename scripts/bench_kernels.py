@@ -125,16 +125,6 @@ cases = {
     "dw_fwd_56_144_s1": lambda: dw_fwd(56, 144, 1),
     "dw_fwd_112_96_s2": lambda: dw_fwd(112, 96, 2),
     "dw_fwd_14_384_s1": lambda: dw_fwd(14, 384, 1),
-    "dw_fwd_tc_112_32_s1": lambda: dw_fwd(112, 32, 1, "tc"),
-    "dw_fwd_tc_112_96_s2": lambda: dw_fwd(112, 96, 2, "tc"),
-    "dw_fwd_tc_56_144_s1": lambda: dw_fwd(56, 144, 1, "tc"),
-    "dw_fwd_tc_56_144_s2": lambda: dw_fwd(56, 144, 2, "tc"),
-    "dw_fwd_tc_28_192_s1": lambda: dw_fwd(28, 192, 1, "tc"),
-    "dw_fwd_tc_28_192_s2": lambda: dw_fwd(28, 192, 2, "tc"),
-    "dw_fwd_tc_14_384_s1": lambda: dw_fwd(14, 384, 1, "tc"),
-    "dw_fwd_tc_14_576_s1": lambda: dw_fwd(14, 576, 1, "tc"),
-    "dw_fwd_tc_14_576_s2": lambda: dw_fwd(14, 576, 2, "tc"),
-    "dw_fwd_tc_7_960_s1": lambda: dw_fwd(7, 960, 1, "tc"),
     "dw_fwd_simt_112_32_s1": lambda: dw_fwd(112, 32, 1),
     "dw_fwd_simt_56_144_s2": lambda: dw_fwd(56, 144, 2),
     "dw_fwd_simt_28_192_s1": lambda: dw_fwd(28, 192, 1),

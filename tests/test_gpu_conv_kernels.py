@@ -23,7 +23,7 @@ def _relerr(a, b):
     return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
 
 
-@pytest.mark.parametrize("impl", ["simt", "tc", "tile"])
+@pytest.mark.parametrize("impl", ["simt", "tile"])
 @pytest.mark.parametrize("B,H,C,stride", [(4, 28, 192, 1), (3, 56, 96, 2), (2, 14, 576, 1), (5, 7, 960, 1),
                                           (2, 112, 32, 1), (3, 15, 144, 2), (130, 14, 384, 1), (2, 28, 144, 2),
                                           (7, 7, 960, 1), (3, 14, 576, 2), (2, 112, 96, 2), (1, 56, 144, 1)])
