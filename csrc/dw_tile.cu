@@ -19,7 +19,7 @@
 //
 // Channels are split into equal chunks of w <= 64 (144 -> 3 x 48, 960 -> 15 x 64); CTA b owns chunk b % nchunks for
 // its whole life (weights and sums stay in registers) and neighbouring CTAs work on the chunks of the SAME tile at the
-// same time, so the 128-byte lines of a pixel are fetched from HBM once (measured with scripts/exp_tma_bw.cu:
+// same time, so the 128-byte lines of a pixel are fetched from HBM once (measured with experiments/exp_tma_bw.cu:
 // streaming one 64-channel chunk of a 144-channel tensor costs as much DRAM time as streaming all of it).
 // Stride 2: four parity planes of the input per tile (TMA element strides {1, 2, 2, 1}); every tap of every output
 // is then a plain (row, column) offset inside one plane; the chunk width is chosen per layer.

@@ -8,7 +8,7 @@
 // A_t is the SAME shared-memory tile for every tap, only started `shift_t` pixel rows later: with pixels as rows
 // (one 2w-byte row per pixel for a chunk of w channels, TMA-swizzled) a tcgen05 shared-memory descriptor may start
 // at any row, because the hardware swizzle is a function of the absolute shared-memory address
-// (scripts/exp_desc_shift.cu verifies this for the 128/64/32-byte swizzles and the unswizzled layout).  So:
+// (experiments/exp_desc_shift.cu verifies this for the 128/64/32-byte swizzles and the unswizzled layout).  So:
 //
 //   TMA   one 4-D box {w channels, Wt+2, Ht+2, NI images} of the RAW producer output, halo zero-filled
 //   8 warps  rewrite it in place: relu6(scale*x + shift), and 0 where the halo is outside the image (padding is

@@ -5,7 +5,7 @@
 //   layout 2: no swizzle, 8-channel planes of 16-byte rows (core matrix = 8 rows x 16 B), LBO = plane pitch, SBO = 128
 //   layout 3: as 2 with LBO / SBO swapped
 // B is the 64x64 identity, so D[r][n] must equal A[r + s][n].
-// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -std=c++17 -Icsrc scripts/exp_desc_shift.cu -o /tmp/exp_desc_shift
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -std=c++17 -Icsrc experiments/exp_desc_shift.cu -o /tmp/exp_desc_shift
 #include <cstdio>
 #include <cstdlib>
 #include <cuda_bf16.h>

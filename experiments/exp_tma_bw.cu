@@ -4,7 +4,7 @@
 //   mode 0: rank-2 view [B*H*W][C], boxes {w, rows}
 //   mode 1: rank-4 view, halo boxes {w, Wt+2, Ht+2, 1} at (x0-1, y0-1)
 // usage: exp_tma_bw mode C w stages rows|Ht [Wt] [H]
-// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -std=c++17 -Icsrc scripts/exp_tma_bw.cu -o build/exp_tma_bw -lcuda
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -std=c++17 -Icsrc experiments/exp_tma_bw.cu -o build/exp_tma_bw -lcuda
 #include <cstdio>
 #include <cstdlib>
 #include <cuda.h>
