@@ -88,6 +88,8 @@ __device__ __forceinline__ void mc_st_f4(float* p, const float4& v) {
 
 __device__ __forceinline__ void raise_error(const b200dp_comm_adam& P, int code) {
   atomicExch(P.error_flag, code);
+  for (int q = 0; q < P.world; ++q)          // tell everybody: a peer that arrives late must not update anything either
+    if (P.abort_words[q] != nullptr) st_release_sys(P.abort_words[q], (uint32_t)code);
   if (P.error_host != nullptr) {
     *reinterpret_cast<volatile int*>(P.error_host) = code;
     __threadfence_system();
@@ -118,9 +120,24 @@ __device__ __forceinline__ bool flag_barrier(const b200dp_comm_adam& P, uint32_t
   return __syncthreads_or(failed) == 0;
 }
 
-// sticky failure: once any launch has raised the flag, later launches do nothing
+// sticky failure: once any launch on this rank has raised the flag, or any PEER has given up on a barrier (its abort
+// word in this rank's arena), launches do nothing.  Checked at the start and again after the first barrier.
 __device__ __forceinline__ bool already_failed(const b200dp_comm_adam& P) {
-  const int bad = threadIdx.x == 0 ? *reinterpret_cast<volatile int*>(P.error_flag) : 0;
+  int bad = 0;
+  if (threadIdx.x == 0) {
+    bad = *reinterpret_cast<volatile int*>(P.error_flag);
+    if (bad == 0 && P.world > 1 && P.abort_words[P.rank] != nullptr) {
+      const uint32_t a = ld_acquire_sys(P.abort_words[P.rank]);
+      if (a != 0) {
+        bad = (int)a;
+        atomicExch(P.error_flag, bad);
+        if (P.error_host != nullptr) {
+          *reinterpret_cast<volatile int*>(P.error_host) = bad;
+          __threadfence_system();
+        }
+      }
+    }
+  }
   return __syncthreads_or(bad) != 0;
 }
 
@@ -176,6 +193,7 @@ comm_adam_kernel(const __grid_constant__ b200dp_comm_adam P) {
   }
   if (barriers) {
     if (!flag_barrier(P, epoch + 1, limit)) return;  // every peer has finished producing this range
+    if (already_failed(P)) return;                   // ... unless one of them gave up waiting for us in the meantime
   } else {
     __syncthreads();      // (skip_barriers: a one-CTA barrier launch ahead of this one did the waiting)
   }

@@ -109,6 +109,10 @@ typedef struct b200dp_comm_adam {
                                                without synchronising the device */
   double* slots[B200DP_MAX_WORLD];          /* slots[r] = rank r's table double[B200DP_MAX_WORLD][B200DP_REDUCE_MAX]
                                                as mapped HERE (b200dp_comm_reduce_f64) */
+  uint32_t* abort_words[B200DP_MAX_WORLD];  /* optional: abort_words[r] = one word in rank r's arena as mapped HERE.  A
+                                               rank whose barrier times out sets it on EVERY rank; a rank that finds its
+                                               own word set after a barrier returns without updating anything, so a
+                                               late peer cannot store weights into a rank that has already given up */
 } b200dp_comm_adam;
 
 /* Launch the fused step on `stream`.  All ranks must call it the same number of times with the

@@ -43,6 +43,7 @@ class CommAdamArgs(C.Structure):
         ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p),
         ("error_host", C.c_void_p),
         ("slots", C.c_void_p * MAX_WORLD),
+        ("abort_words", C.c_void_p * MAX_WORLD),
     ]
 
 

@@ -4,7 +4,7 @@ The reference synchronises gradients with DDP's bucketed NCCL all-reduce and the
 ``torch.optim.Adam`` (cifar10_mpi_mobilenet_224.py:142-148, :179-180).  Here each rank owns one
 symmetric device arena
 
-    [ flag pad | reduction slots | gradients | master weights | optional bf16 weights | extra fp32 ]
+    [ flag pad | abort word | reduction slots | gradients | master weights | optional bf16 weights | extra fp32 ]
 
 that every peer on the node maps, and the kernels of ``csrc/comm_adam.cu`` work on it directly over
 NVLink / NVSwitch: barrier on the flag pads, sum all ranks' gradients, average, Adam on the fp32
@@ -275,6 +275,7 @@ class FusedAllReduceAdam:
     """
 
     FLAG_BYTES = COMM_MAX_BLOCKS * MAX_WORLD * 4
+    ABORT_BYTES = 256            # one word per rank: set by any peer whose barrier timed out
     SLOT_BYTES = MAX_WORLD * REDUCE_MAX * 8
 
     def __init__(self, ctx, numel: int, hyper: Optional[AdamHyper] = None, *,
@@ -292,6 +293,8 @@ class FusedAllReduceAdam:
         gsize = 4 if grad_dtype == torch.float32 else 2
         dev = ctx.device
         off = self.FLAG_BYTES
+        self._abort_off = off
+        off += self.ABORT_BYTES
         self._slot_off = off
         off += self.SLOT_BYTES
         self._grad_off = off
@@ -340,6 +343,7 @@ class FusedAllReduceAdam:
         for r in range(ctx.world_size):
             base = self.arena.ptrs[r]
             a.flags[r] = base
+            a.abort_words[r] = base + self._abort_off
             a.slots[r] = base + self._slot_off
             a.grads[r] = base + self._grad_off
             a.params[r] = base + self._param_off
