@@ -44,6 +44,25 @@ def make_engine(cfg: TrainConfig, ctx: DistContext):
     return TorchEngine(cfg, ctx)
 
 
+class _Range:
+    """NVTX range around a phase when B200DP_NVTX=1 (shows up in Nsight timelines; free otherwise)."""
+
+    on = os.environ.get("B200DP_NVTX", "0") == "1"
+
+    def __init__(self, name: str) -> None:
+        self.name = name
+
+    def __enter__(self):
+        if _Range.on and torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *exc):
+        if _Range.on and torch.cuda.is_available():
+            torch.cuda.nvtx.range_pop()
+        return False
+
+
 class Trainer:
     def __init__(self, cfg: TrainConfig, ctx: Optional[DistContext] = None,
                  train_set: Optional[ArrayDataset] = None, test_set: Optional[ArrayDataset] = None,
@@ -198,8 +217,10 @@ class Trainer:
         total_start = time.perf_counter()
         for epoch in range(self.start_epoch, cfg.epochs):
             epoch_start = time.perf_counter()
-            tr = self.train_epoch(epoch)
-            ev = self.evaluate()
+            with _Range(f"epoch {epoch + 1} train"):
+                tr = self.train_epoch(epoch)
+            with _Range(f"epoch {epoch + 1} eval"):
+                ev = self.evaluate()
             if ctx.device.type == "cuda":
                 torch.cuda.synchronize()
             epoch_time = self._max(time.perf_counter() - epoch_start)
@@ -210,6 +231,8 @@ class Trainer:
                    "train_acc": tr["acc"], "test_loss": ev["loss"], "test_acc": ev["acc"], "lr": tr["lr"],
                    "train_images_per_sec": tr["images"] / max(train_time, 1e-9), "world_size": ctx.world_size,
                    "step_ms": tr["step_ms"], "data_wait_ms": tr["data_wait_ms"],
+                   "engine": self.engine.name, "comm": getattr(self.engine, "comm_algo", cfg.comm),
+                   "comm_memory": getattr(getattr(getattr(self.engine, "fused", None), "arena", None), "kind", None),
                    # fraction of the measured HBM copy bandwidth the step sustains on its ~11.5 GB of unavoidable
                    # activation traffic (profiles/step_roofline.md)
                    "hbm_roofline_fraction": (11.5e9 * self.batch_size / 128 / 6.55e12) / max(tr["step_ms"] * 1e-3, 1e-9)
