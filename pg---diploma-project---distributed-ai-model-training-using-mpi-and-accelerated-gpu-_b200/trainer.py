@@ -70,6 +70,9 @@ class Trainer:
         self.cfg = cfg.validate()
         self.own_ctx = ctx is None
         self.ctx = ctx or self._bootstrap(cfg)
+        for d in (cfg.out_dir, os.path.dirname(cfg.metrics_jsonl), os.path.dirname(cfg.resume)):
+            if d:
+                os.makedirs(d, exist_ok=True)        # every rank: harmless, and rank 0 must not race the others to it
         self.log = logger or RankLogger(self.ctx.is_main, jsonl_path=cfg.metrics_jsonl)
         self.batch_size = cfg.resolved_batch_size()
         if train_set is None or test_set is None:
