@@ -87,19 +87,32 @@ def run_b200dp(ns) -> dict:
     W, K, B, N = ns.warmup, ns.steps, ns.batch, ctx.world_size
     if W < 3:
         W = 3
-    per_rank = (W + K) * B
+    # Synthetic data: at most 64 batches per rank are generated (every rank builds the whole set, and a million-image
+    # set takes minutes); longer runs walk it again with a new epoch = a new permutation and new augmentation draws.
+    per_rank = min(W + K, 64) * B
     ds = SyntheticCIFAR10(per_rank * N, train=True)
     ds.pin()
     engine = make_engine(cfg, ctx)
     lr = cfg.lr
 
+    def stream(loader, sampler, first_epoch):
+        epoch = first_epoch
+        while True:
+            sampler.set_epoch(epoch)
+            for b in loader:
+                yield b
+            epoch += 1
+
     # ---------------- device-timed arm: inputs resident ------------------------------------
     sampler = PartitionSampler(len(ds), N, ctx.rank, shuffle=True)
     loader = BatchLoader(ds, sampler, B, ctx.device, train=True, augment=True, seed=cfg.seed)
     resident = []
-    for b in loader:
+    src = stream(loader, sampler, 0)
+    while len(resident) < W + K:
+        b = next(src)
         b.wait()
         resident.append(Batch(b.images.clone(), b.labels.clone(), b.params.clone(), b.n))
+    src.close()
     torch.cuda.synchronize()
     for i in range(W):
         engine.train_step(resident[i], lr)
@@ -125,8 +138,7 @@ def run_b200dp(ns) -> dict:
     e2e = None
     if not ns.no_e2e:
         loader2 = BatchLoader(ds, sampler, B, ctx.device, train=True, augment=True, seed=cfg.seed + 1)
-        sampler.set_epoch(1)
-        it = iter(loader2)
+        it = stream(loader2, sampler, 1000)
         for _ in range(W):
             engine.train_step(next(it), lr)
             engine.read_metrics(reset=False)
@@ -149,8 +161,7 @@ def run_b200dp(ns) -> dict:
         torch.cuda.synchronize()
         dt = max_over_ranks(time.perf_counter() - t0, ctx.device)
         assert last is not None and last[2] > 0
-        for _ in it:
-            pass
+        it.close()
         e2e = {"value": N * K * B / dt, "unit": "images/sec",
                "h2d_bytes_per_step": loader2.h2d_bytes_per_batch(B), "d2h_bytes_per_step": 3 * 8,
                "d2h": "running (loss sum, correct, count) of every step, copied to pinned memory and read one step behind"

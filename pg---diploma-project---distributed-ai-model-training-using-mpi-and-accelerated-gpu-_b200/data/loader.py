@@ -143,11 +143,12 @@ class BatchLoader:
                 yield item
         finally:
             stop.set()
-            while not q.empty():
+            while th.is_alive():                   # unblock a producer that is waiting on the full queue, then join it
                 try:
-                    q.get_nowait()
+                    q.get(timeout=0.05)
                 except queue.Empty:
-                    break
+                    pass
+            th.join()
 
     def _ensure_staging(self) -> None:
         want = self.prefetch + 1
@@ -175,6 +176,8 @@ class BatchLoader:
                     if stop.is_set():
                         return
                     s = free.get()
+                    if s is None or stop.is_set():     # the consumer went away (generator closed mid-epoch)
+                        return
                     if s["free"] is not None:
                         s["free"].synchronize()
                     n = idx.numel()
@@ -206,12 +209,16 @@ class BatchLoader:
                 free.put(s)
                 yield Batch(img, lab, par, n, ev)
         finally:
+            # Stop the producer for good: it may be blocked putting into the full queue or waiting for a free staging
+            # buffer.  A daemon thread that is still inside native code when the interpreter exits aborts the process.
             stop.set()
-            while not q.empty():
+            free.put(None)
+            while th.is_alive():
                 try:
-                    q.get_nowait()
+                    q.get(timeout=0.05)
                 except queue.Empty:
-                    break
+                    pass
+            th.join()
 
     def h2d_bytes_per_batch(self, n: Optional[int] = None) -> int:
         n = self.batch_size if n is None else n

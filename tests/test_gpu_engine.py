@@ -272,3 +272,22 @@ def test_predictor_full_resolution_top3_matches_torchvision(env):
             assert name in got_d and abs(got_d[name] - c) < 2e-2, (name, c, got)
     full = pred.probabilities(pil)
     assert abs(float(full.sum()) - 1) < 1e-4 and (full - ref_p).abs().max() < 2e-2
+
+
+def test_closing_the_pinned_loader_mid_epoch_joins_its_thread(env):
+    """A loader iterator abandoned mid-epoch (bench.py streams epochs and stops at K batches) must stop its producer
+    thread; a daemon thread left inside native code at interpreter exit aborts the process."""
+    import threading
+    from b200dp.data.datasets import SyntheticCIFAR10
+    from b200dp.data.loader import BatchLoader
+    from b200dp.parallel.sampler import PartitionSampler
+    ds = SyntheticCIFAR10(64 * 16, True)
+    ds.pin()
+    loader = BatchLoader(ds, PartitionSampler(len(ds), 1, 0, shuffle=True), 16, torch.device("cuda", 0), train=True)
+    for stop_after in (1, 3, 40):
+        it = iter(loader)
+        for _ in range(stop_after):
+            next(it).wait()
+        it.close()
+        torch.cuda.synchronize()
+        assert not [t for t in threading.enumerate() if t.name == "b200dp-loader"]
