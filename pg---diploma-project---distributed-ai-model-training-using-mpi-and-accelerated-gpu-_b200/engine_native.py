@@ -298,10 +298,12 @@ class NativeEngine:
 
     def close(self) -> None:
         torch.cuda.synchronize()
-        self.fused.check_error()
-        self.core.close()
-        self.core.params = self.core.grads = self.core.buffers = None     # views of the arena freed next
-        self.fused.close()
+        try:
+            self.fused.check_error()          # a timed-out barrier must not go unnoticed, but must not leak the arena either
+        finally:
+            self.core.close()
+            self.core.params = self.core.grads = self.core.buffers = None     # views of the arena freed next
+            self.fused.close()
 
 
 class NativeInference:
