@@ -117,3 +117,15 @@ def test_resume_file_is_created_on_first_run_and_loads_weights_only(tmp_path):
     t2 = Trainer(TrainConfig(**{**cfg.to_dict(), "epochs": 2}))
     assert t2.start_epoch == 1
     t2.close()
+
+
+def test_bench_cpu_arm_prints_one_json_line():
+    """`bench.py --cpu` (BASELINE.json config 1 on this framework's mode 1) runs without a GPU and reports images/sec."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--cpu", "--steps", "1", "--warmup", "3"],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.strip().splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["device"] == "cpu" and d["config"]["per_rank_batch"] == 64 and d["value"] > 0 and d["steps"] == 1
