@@ -677,7 +677,7 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   if (int rc = make_tmap_2d_bf16(&pl->tmBt, w, N, K, K, p.tail_w, p.block_n, p.tail_w * 2)) return rc;
   if (int rc = make_tmap_2d_bf16(&pl->tmO, out, M, N, ldo, 64, 32, 128)) return rc;     // each epilogue warp stores its 32 rows
   if (emode == E_MASKSTATS) {
-    B200DP_REQUIRE(amode == A_TMA, "pw_gemm: E_MASKSTATS is implemented for the TMA A path only");
+    B200DP_REQUIRE(amode == A_TMA || amode == A_BNGRAD, "pw_gemm: E_MASKSTATS is implemented for the TMA and BN-backward A paths");
     if (int rc = make_tmap_2d_bf16(&pl->tmX, aux, M, N, ldo, 64, BM, 128)) return rc;
   } else {
     pl->tmX = CUtensorMap{};

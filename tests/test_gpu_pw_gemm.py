@@ -154,3 +154,23 @@ def test_packed_dgrad_maskstats(ops, M, K, N, pack):
     o = out.float()
     assert torch.allclose(stats[0], o.sum(0), rtol=2e-3, atol=0.5)
     assert torch.allclose(stats[1], (o * aux.float()).sum(0), rtol=2e-3, atol=1.0)
+
+
+@pytest.mark.parametrize("M,K,N", [(640, 96, 16), (1000, 144, 32), (2048, 576, 96), (128 * 9 + 5, 960, 160)])
+def test_dgrad_bngrad_with_stats_epilogue(ops, M, K, N):
+    """A_BNGRAD prologue (dx = ca*dz + cb*x + cc on the A tile) together with the E_MASKSTATS epilogue, as the executor uses
+    it with an always-open mask (scale 0, shift 3) to take the sums of the next BatchNorm backward inside the GEMM."""
+    torch.manual_seed(5)
+    dz, x, w = _rand((M, K)), _rand((M, K), 2.0), _rand((N, K), 0.2)
+    coef = torch.randn(3, K, device="cuda").contiguous()
+    aux = _rand((M, N), 2.0)
+    ecoef = torch.stack([torch.zeros(N, device="cuda"), torch.full((N,), 3.0, device="cuda")]).contiguous()
+    stats = torch.zeros(2, N, device="cuda")
+    out = ops.pw_gemm(w, a_dz=dz, a_raw=x, acoef=coef, emode=ops.E_MASKSTATS, aux=aux, ecoef=ecoef, stats=stats)
+    a = (coef[0] * dz.float() + coef[1] * x.float() + coef[2]).to(torch.bfloat16).float()
+    ref = a @ w.float().t()
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 0.02 * ref.abs().max().item() + 1e-2, err
+    o = out.float()
+    assert torch.allclose(stats[0], o.sum(0), rtol=2e-3, atol=0.5)
+    assert torch.allclose(stats[1], (o * aux.float()).sum(0), rtol=2e-3, atol=1.0)
