@@ -238,7 +238,15 @@ def run_reference(ns) -> dict:
 
 def main() -> int:
     ns = parse_args()
-    out = run_reference(ns) if ns.impl == "reference" else (run_cpu(ns) if ns.cpu else run_b200dp(ns))
+    try:
+        out = run_reference(ns) if ns.impl == "reference" else (run_cpu(ns) if ns.cpu else run_b200dp(ns))
+    except BaseException:
+        # loader / clock-sampler threads may still be inside native code: a normal interpreter shutdown would abort
+        # ("terminate called without an active exception") and hide the real error.  Print it and leave at once.
+        import traceback
+        traceback.print_exc()
+        sys.stderr.flush()
+        os._exit(1)
     if out:
         print(json.dumps(out), flush=True)
     return 0
