@@ -54,6 +54,7 @@ struct Block {
   int ce, cd, cp;      // conv indices (ce = -1 when expand == 1)
   __nv_bfloat16* xout = nullptr;   // finished block output [B, hout, hout, coutp]
   float* xsum = nullptr;           // per-channel column sums of xout (for the consumer's factored weight gradient)
+  float* mask1 = nullptr;          // [2][coutp]: scale 0, shift 3 -> ReLU6'(0 * aux + 3) = 1 for every element
 };
 
 struct WPrepEntry { long long off; int n, k; int rf, rd; long long off_pf, off_pd; };
@@ -100,6 +101,10 @@ struct Engine {
   float *pooled = nullptr, *drop = nullptr, *logits = nullptr, *dlogits = nullptr, *dpool = nullptr;
   double *metrics_train = nullptr, *metrics_eval = nullptr;
   int* step_dev = nullptr;
+  // B200DP_JOIN_IN_DGRAD=1: where a block's output gradient is the consumer's data gradient alone (no residual branch
+  // joins it), the two sums of its projection BatchNorm backward come out of that data-gradient GEMM's epilogue
+  // (E_MASKSTATS with an always-open mask: Block::mask1) and the grad_join_stats launch disappears
+  bool join_in_dgrad = false;
   WPrepEntry* wprep_dev = nullptr;
   int n_pw = 0;
   bool use_graphs = true;
@@ -245,6 +250,7 @@ size_t layout_workspace(Engine& e, char* base) {
   e.metrics_train = carve<double>(p, 4);
   e.metrics_eval = carve<double>(p, 4);
   e.step_dev = carve<int>(p, 4);
+  for (auto& b : e.blocks) b.mask1 = carve<float>(p, 2 * b.coutp);
   e.wprep_dev = carve<WPrepEntry>(p, 64);
   return (size_t)(p - base);
 }
@@ -316,9 +322,14 @@ int build_plans(Engine& e, Plans& pl, int n) {
                              ce.cinp, xin, ce.cinp, nullptr, nullptr, nullptr, 0, wf(ce), ce.raw, ce.coutp,
                              nullptr, nullptr, ce.sums_f, ce.coutp, 0, ce.pack_f));
       // dgrad: dx[M, cin] = BNgrad(dze, e_raw)[M, hidden] * W[hidden, cin]   (weights transposed: [cin][hidden])
-      ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp,
-                           e.dze[dze_idx(e, b.index - 1)], ce.raw, ce.coef_b, 0, wd(ce), e.gx[0], ce.cinp, nullptr, nullptr,
-                           nullptr, 0, main_ctas(b.hin), ce.pack_d));
+      // the gradient this GEMM produces belongs to the previous block's output; without a residual branch it IS that
+      // gradient, and the sums of that block's projection BatchNorm backward can be taken here
+      const bool stats_here = e.join_in_dgrad && !b.use_res && b.index >= 2;
+      const Conv* cpp = b.index >= 2 ? &e.convs[e.blocks[b.index - 2].cp] : nullptr;
+      ENG_TRY(pw_gemm_plan(&pl.dgrad[b.ce], A_BNGRAD, stats_here ? E_MASKSTATS : E_PLAIN, Min, ce.cinp, ce.coutp, nullptr, ce.coutp,
+                           e.dze[dze_idx(e, b.index - 1)], ce.raw, ce.coef_b, 0, wd(ce), e.gx[0], ce.cinp,
+                           stats_here ? cpp->raw : nullptr, stats_here ? e.blocks[b.index - 2].mask1 : nullptr,
+                           stats_here ? cpp->sums_b : nullptr, stats_here ? cpp->coutp : 0, main_ctas(b.hin), ce.pack_d));
       if (e.fork && e.fork_wgrad && e.bn_fuse) pl.dgrad[b.ce].gsrc = src_b(e, ce, (float)Min);
     }
     for (int ev = 0; ev < 2; ++ev)
@@ -339,8 +350,11 @@ int build_plans(Engine& e, Plans& pl, int n) {
       ENG_TRY(pw_gemm_plan(ev ? &pl.fwd_eval[li] : &pl.fwd[li], A_TMA, ev ? E_PLAIN : E_STATS, M, cl.coutp, cl.cinp,
                            lb.xout, cl.cinp, nullptr, nullptr, nullptr, 0, e.w_bf16 + cl.off_w, cl.raw, cl.coutp, nullptr,
                            nullptr, cl.sums_f, cl.coutp, 0));
-    ENG_TRY(pw_gemm_plan(&pl.dgrad[li], A_BNGRAD, E_PLAIN, M, cl.cinp, cl.coutp, nullptr, cl.coutp, e.dze[0], cl.raw,
-                         cl.coef_b, 0, e.wt_bf16 + cl.off_w, e.gx[0], cl.cinp, nullptr, nullptr, nullptr, 0, 0));
+    const Conv& cpl = e.convs[lb.cp];
+    const bool jd = e.join_in_dgrad;
+    ENG_TRY(pw_gemm_plan(&pl.dgrad[li], A_BNGRAD, jd ? E_MASKSTATS : E_PLAIN, M, cl.cinp, cl.coutp, nullptr, cl.coutp, e.dze[0], cl.raw,
+                         cl.coef_b, 0, e.wt_bf16 + cl.off_w, e.gx[0], cl.cinp, jd ? cpl.raw : nullptr, jd ? lb.mask1 : nullptr,
+                         jd ? cpl.sums_b : nullptr, jd ? cpl.coutp : 0, 0));
     if (e.fork && e.fork_wgrad && e.bn_fuse) pl.dgrad[li].gsrc = src_b(e, cl, (float)M);
   }
   return B200DP_OK;
@@ -581,9 +595,9 @@ int backward(Engine& e, Plans& pl, int n, cudaStream_t s) {
       ENG_TRY(grad_join_stats_launch(g1, dnext, cp.raw, e.dout[doi], cp.sums_b, cp.coutp, rows_out, cp.coutp, s));
       dcur = e.dout[doi];
       doi ^= 1;
-    } else {
+    } else if (!(e.join_in_dgrad && (bi == (int)e.blocks.size() - 1 || e.blocks[bi + 1].ce >= 0))) {
       ENG_TRY(grad_join_stats_launch(g1, nullptr, cp.raw, nullptr, cp.sums_b, cp.coutp, rows_out, cp.coutp, s));
-    }
+    }   // else: the data-gradient GEMM that produced g1 has already accumulated the two sums (E_MASKSTATS epilogue)
     mark(e, s, "grad_join", b.cp);
     if (!fuse) ENG_TRY(bn_fin_b(e, cp, (float)rows_out, s));
     const BnBwdSrc cp_src = src_b(e, cp, (float)rows_out);
@@ -725,6 +739,7 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
   e->pw_pack = !(getenv("B200DP_PW_PACK") != nullptr && atoi(getenv("B200DP_PW_PACK")) == 0);
   e->bn_fuse = !(getenv("B200DP_BN_FUSE") != nullptr && atoi(getenv("B200DP_BN_FUSE")) == 0);
   e->fork = !(getenv("B200DP_FORK") != nullptr && atoi(getenv("B200DP_FORK")) == 0);
+  e->join_in_dgrad = getenv("B200DP_JOIN_IN_DGRAD") != nullptr && atoi(getenv("B200DP_JOIN_IN_DGRAD")) != 0;
   e->fork_wgrad = getenv("B200DP_FORK_WGRAD") != nullptr && atoi(getenv("B200DP_FORK_WGRAD")) != 0;
   if (getenv("B200DP_FORK_MAXH") != nullptr) e->fork_max_h = atoi(getenv("B200DP_FORK_MAXH"));
   if (getenv("B200DP_FORK_SMS") != nullptr) e->fork_sms = atoi(getenv("B200DP_FORK_SMS"));
@@ -759,6 +774,11 @@ int b200dp_engine_create(void** out, int batch, int img_size, int num_classes, c
     if (c.kind == 2) table.push_back(WPrepEntry{c.off_w, c.coutp, c.cinp, c.pack_f, c.pack_d, c.off_pf, c.off_pd});
   e->n_pw = (int)table.size();
   B200DP_CUDA(cudaMemcpy(e->wprep_dev, table.data(), table.size() * sizeof(WPrepEntry), cudaMemcpyHostToDevice));
+  for (auto& b : e->blocks) {
+    std::vector<float> one(2 * b.coutp, 0.f);
+    for (int i = b.coutp; i < 2 * b.coutp; ++i) one[i] = 3.f;
+    B200DP_CUDA(cudaMemcpy(b.mask1, one.data(), one.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
   B200DP_CUDA(cudaStreamCreateWithFlags(&e->cap_stream, cudaStreamNonBlocking));
   {
     int prio_lo = 0, prio_hi = 0;     // numerically lowest = highest priority

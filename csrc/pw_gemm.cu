@@ -629,6 +629,8 @@ int pw_gemm_plan(PwGemmPlan* pl, int amode, int emode, int M, int N, int K, cons
   // few row tiles (7x7 layers): 128-wide column blocks leave SMs idle and make every CTA stream a 128-column weight
   // tile per K chunk through its own ~27 B/clk of L2 bandwidth; 64-wide blocks use more SMs and halve that tile
   if (N > 64 && p.m_tiles * ((N + 127) / 128) < num_sms()) p.block_n = 64;
+  // two raw A tiles per stage plus four epilogue buffers per 64 columns: this combination only fits with 64-wide blocks
+  if (N > 64 && amode == A_BNGRAD && emode == E_MASKSTATS) p.block_n = 64;
   p.n_tiles = (N + p.block_n - 1) / p.block_n;
   p.kc = (K + KCH - 1) / KCH;
   p.a0 = static_cast<const __nv_bfloat16*>(a0);
